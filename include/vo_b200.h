@@ -1,0 +1,132 @@
+/*
+ * vo_b200.h — C-ABI of libvo_b200.so: the B200 (sm_100a) two-view visual-odometry hot path.
+ *
+ * The reference (Samirez/Visual_odometry) has no FFI: its hot path is a handful of cv2 calls
+ * made from Python (src/image_pair.py:234,280,304,332; src/visual_slam.py:231,243).  Each entry
+ * point below replaces the arithmetic of one of those call sites; the Python mirror of the
+ * reference's ImagePair (visual_odometry_b200/image_pair.py) binds them with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _h (host);
+ *   - the caller owns every buffer, including the workspace (query *_workspace_bytes first);
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it and never
+ *     synchronise the device;
+ *   - return value: 0 = VO_OK, negative = error (vo_last_error_string() has the text).
+ *   - batched layout ("pairs of a sequence"): frames are rows of fixed capacity `n_cap`
+ *     keypoints; pair b joins frames pairs[2b] (query, frame1) and pairs[2b+1] (train, frame2).
+ */
+#ifndef VO_B200_H
+#define VO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VO_OK 0
+#define VO_ERR_INVALID_ARG (-1)
+#define VO_ERR_TOO_FEW_POINTS (-2)
+#define VO_ERR_CUDA (-3)
+#define VO_ERR_WORKSPACE (-4)
+
+#define VO_MATCH_MUTUAL 0 /* BFMatcher(crossCheck=True).match  — src/image_pair.py:234 */
+#define VO_MATCH_KNN2_RATIO 1 /* knnMatch(k=2)+Lowe ratio — src/feature_detection.py:20-26 */
+
+int vo_version(void);
+const char* vo_last_error_string(void);
+
+/* ---- K1: ORB/Hamming matching (replaces BFMatcher(NORM_HAMMING).match, image_pair.py:234) ----
+ * desc  : uint8 [n_frames, n_cap, 32]   256-bit descriptors
+ * nkp   : int32 [n_frames]              valid keypoints per frame (<= n_cap)
+ * kp    : float32 [n_frames, n_cap, 2]  KeyPoint.pt (may be NULL -> pts not written)
+ * pairs : int32 [n_pairs, 2]
+ * out   : q,t int32 [n_pairs, n_cap]; dist float32 [n_pairs, n_cap] (integer valued);
+ *         t2/dist2 second neighbour (mode KNN2_RATIO; may be NULL);
+ *         pts float64 [n_pairs, n_cap, 4] = (x1,y1,x2,y2) of each match (image_pair.py:294-299);
+ *         n_out int32 [n_pairs] number of matches, rows sorted by queryIdx.
+ */
+size_t vo_match_workspace_bytes(int n_pairs, int n_cap);
+int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
+                           const int32_t* pairs, int n_pairs, int mode, float ratio,
+                           int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
+                           double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+/* single pair convenience: d1 [n1,32], d2 [n2,32]; outputs sized n1 */
+int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode, float ratio,
+                     int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
+                     int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- K6: SIFT/L2 matching on tensor cores (BFMatcher(NORM_L2), visual_slam.py:19) ----
+ * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2). */
+size_t vo_match_l2_workspace_bytes(int n_pairs, int n_cap, int dim);
+int vo_match_l2_batch(const float* desc, const int32_t* nkp, const float* kp, int n_cap, int dim,
+                      const int32_t* pairs, int n_pairs, int mode, float ratio,
+                      int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
+                      double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- K2/K3: essential matrix 5-point RANSAC (cv2.findEssentialMat, image_pair.py:280-286) ----
+ * pts   : float64 [n_pairs, n_cap, 4] pixel correspondences, m[b] of them valid
+ * K     : float64 [9] row-major camera matrix (device)
+ * Replays cv::RNG(2^64-1) minimal samples, OpenCV's strict-greater best update and adaptive
+ * iteration bound (max_iters; adaptive=0 -> exactly max_iters hypotheses sets, config C3).
+ * out   : E float64 [n_pairs,9] (||E||_F = 1), mask uint8 [n_pairs,n_cap] in {0,1},
+ *         n_inl int32 [n_pairs], n_iters int32 [n_pairs] (iterations OpenCV would have run),
+ *         status int32 [n_pairs] (0 ok, VO_ERR_TOO_FEW_POINTS when m<5 / no model).
+ */
+size_t vo_essential_workspace_bytes(int n_pairs, int n_cap, int max_iters);
+int vo_essential_ransac_batch(const double* pts, const int32_t* m, int n_cap, int n_pairs,
+                              const double* K, double conf, double thr_px, int max_iters,
+                              int adaptive, double* E, uint8_t* mask, int32_t* n_inl,
+                              int32_t* n_iters, int32_t* status, void* ws, size_t ws_bytes,
+                              void* stream);
+/* five-point minimal solver alone: samples int32 [n_samples,5] index into pts_n [m,4]
+ * (normalised coords). out E [n_samples,10,9], n_models int32 [n_samples]. */
+int vo_fivept_solve(const double* pts_n, int m, const int32_t* samples, int n_samples,
+                    double* E, int32_t* n_models, void* stream);
+/* Sampson scoring alone (EMEstimatorCallback::computeError restated): E [H,9];
+ * pts_n [m,4] normalised; thr2 = float32 squared threshold; counts int32 [H];
+ * masks uint8 [H,m] or NULL. */
+int vo_sampson_score(const double* E, int H, const double* pts_n, int m, float thr2,
+                     int32_t* counts, uint8_t* masks, void* stream);
+/* cv::RNG replay of RANSACPointSetRegistrator::getSubset: samples int32 [n_iters,5] */
+int vo_ransac_samples(int count, int n_iters, int32_t* samples, void* stream);
+
+/* ---- K5: recoverPose (cv2.recoverPose, image_pair.py:304-308) ----
+ * uses the inliers of `mask` (mask may be NULL = all m[b] points). dist_thresh = 50.
+ * out R [n_pairs,9], t [n_pairs,3], pose_mask uint8 [n_pairs,n_cap] in {0,255} (may be NULL),
+ * n_good int32 [n_pairs]. */
+size_t vo_pose_workspace_bytes(int n_pairs, int n_cap);
+int vo_recover_pose_batch(const double* E, const double* pts, const int32_t* m,
+                          const uint8_t* mask, int n_cap, int n_pairs, const double* K,
+                          double dist_thresh, double* R, double* t, uint8_t* pose_mask,
+                          int32_t* n_good, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- K4: DLT triangulation (cv2.triangulatePoints, image_pair.py:332-339) ----
+ * P1,P2 float64 [12] row-major 3x4; x1,x2 float64 [n,2]; X float64 [n,4]
+ * (unit-norm null vector; dehomog!=0 -> divided by w as image_pair.py:339). */
+int vo_triangulate(const double* P1, const double* P2, const double* x1, const double* x2,
+                   int n, double* X, int dehomog, void* stream);
+/* batched reference flavour: for each pair, inliers (mask) of pts are triangulated with
+ * P_first = K [R^T | -R^T t] (paired with frame-1 points), P_second = K [I|0]
+ * (image_pair.py:319-336). X [n_pairs,n_cap,4] compacted in match order, n_x [n_pairs]. */
+int vo_triangulate_pairs(const double* R, const double* t, const double* pts, const int32_t* m,
+                         const uint8_t* mask, int n_cap, int n_pairs, const double* K,
+                         double* X, int32_t* n_x, void* stream);
+
+/* ---- trajectory chaining (north_star): P_0 = I, P_k = rel_k * P_{k-1},
+ * rel_k = [R_k | t_k] of pair k-1. poses float64 [n_pairs+1,16]. */
+int vo_chain_poses(const double* R, const double* t, int n_pairs, const double* P0,
+                   double* poses, void* stream);
+
+/* ---- K7: PnP-RANSAC (cv2.solvePnPRansac defaults, visual_slam.py:231-235) ----
+ * X [n,3], x [n,2]; out rvec[3], tvec[3], inliers int32 [n], n_inl, ok (device ints). */
+size_t vo_pnp_workspace_bytes(int n, int iters);
+int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int iters,
+                  double reproj_px, double conf, double* rvec, double* tvec, int32_t* inliers,
+                  int32_t* n_inl, int32_t* ok, void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VO_B200_H */

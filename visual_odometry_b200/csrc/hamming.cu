@@ -1,0 +1,300 @@
+// hamming.cu — K1: 256-bit ORB descriptor matching, one N1 x N2 popc pass per frame pair.
+//
+// Replaces cv2.BFMatcher(NORM_HAMMING, crossCheck=True).match (reference src/image_pair.py:234,
+// matcher built at src/image_and_keypoints.py:9 / src/visual_slam.py:18) and the brute-force
+// knnMatch(k=2)+ratio of src/feature_detection.py:20-26.
+//
+// Layout: each thread keeps RQ query descriptors (8 x u32 each) in registers; train descriptors
+// stream through shared memory in TT-descriptor tiles staged by 1-D TMA bulk copies
+// (cp.async.bulk + mbarrier, NSTAGE deep).  Every lane reads the same train descriptor
+// (broadcast LDS.128), so one smem read feeds 32*RQ distances.  Row (query) top-2 lives in
+// registers as packed keys (dist<<16 | trainIdx): min() on the key is "smallest distance, lowest
+// index on ties" = OpenCV's order.  Column (train) minima use keys (dist<<16 | queryIdx):
+// per-thread min over RQ -> REDUX warp min -> shared atomicMin -> one global atomicMin per tile
+// column, so forward NN, second NN and backward NN all come out of ONE pass (cv2 does two).
+#include "common.cuh"
+
+namespace vo {
+
+constexpr int HM_THREADS = 128;
+constexpr int HM_TT = 128;     // train descriptors per smem tile (4 KB)
+constexpr int HM_NSTAGE = 4;
+constexpr uint32_t KEY_INF = 0xffffffffu;
+
+template <int RQ>
+__global__ void __launch_bounds__(HM_THREADS)
+hamming_top2_kernel(const uint8_t* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
+                    const int32_t* __restrict__ pairs, const uint8_t* __restrict__ desc2_direct,
+                    int n1_direct, int n2_direct, int n_splits,
+                    uint32_t* __restrict__ rowbest /*[P][S][n_cap][2]*/,
+                    uint32_t* __restrict__ colmin /*[P][n_cap]*/) {
+  __shared__ __align__(128) uint4 tile[HM_NSTAGE][HM_TT * 2];
+  __shared__ uint32_t cmin[HM_NSTAGE][HM_TT];
+  __shared__ __align__(8) uint64_t full[HM_NSTAGE];
+
+  const int pair = blockIdx.y;
+  const int split = blockIdx.z;
+  // pairs == nullptr: single pair given directly as (desc, desc2_direct)
+  const int f1 = pairs ? pairs[2 * pair] : 0, f2 = pairs ? pairs[2 * pair + 1] : 0;
+  const int n1 = pairs ? nkp[f1] : n1_direct, n2 = pairs ? nkp[f2] : n2_direct;
+  const int q0 = blockIdx.x * (HM_THREADS * RQ);
+  if (q0 >= n1) return;
+
+  // train range of this split, in whole tiles
+  const int n_tiles_all = (n2 + HM_TT - 1) / HM_TT;
+  const int tiles_per_split = (n_tiles_all + n_splits - 1) / n_splits;
+  const int tile_lo = split * tiles_per_split;
+  const int tile_hi = min(n_tiles_all, tile_lo + tiles_per_split);
+  const int n_tiles = tile_hi - tile_lo;
+
+  const int tid = threadIdx.x;
+  const uint8_t* d2 = pairs ? desc + (size_t)f2 * n_cap * 32 : desc2_direct;
+
+  if (tid == 0) {
+    for (int s = 0; s < HM_NSTAGE; ++s) mbar_init(&full[s], 1);
+    fence_barrier_init();
+  }
+  for (int k = tid; k < HM_NSTAGE * HM_TT; k += HM_THREADS) (&cmin[0][0])[k] = KEY_INF;
+  __syncthreads();
+
+  auto issue = [&](int k) {  // tile k of this split -> stage k % NSTAGE   (thread 0 only)
+    const int j0 = (tile_lo + k) * HM_TT;
+    const uint32_t bytes = (uint32_t)min(HM_TT, n2 - j0) * 32u;
+    const int s = k % HM_NSTAGE;
+    mbar_expect_tx(&full[s], bytes);
+    bulk_g2s(&tile[s][0], d2 + (size_t)j0 * 32, bytes, &full[s]);
+  };
+  if (tid == 0)
+    for (int k = 0; k < min(HM_NSTAGE, n_tiles); ++k) issue(k);
+
+  // query descriptors -> registers
+  uint32_t qd[RQ][8];
+  uint32_t qkey[RQ];
+  uint32_t m1[RQ], m2[RQ];
+  const uint4* d1 = reinterpret_cast<const uint4*>(desc + (size_t)f1 * n_cap * 32);
+#pragma unroll
+  for (int r = 0; r < RQ; ++r) {
+    const int i = q0 + r * HM_THREADS + tid;
+    const bool ok = i < n1;
+    uint4 a = make_uint4(0, 0, 0, 0), b = a;
+    if (ok) {
+      a = __ldg(d1 + 2 * i);
+      b = __ldg(d1 + 2 * i + 1);
+    }
+    qd[r][0] = a.x; qd[r][1] = a.y; qd[r][2] = a.z; qd[r][3] = a.w;
+    qd[r][4] = b.x; qd[r][5] = b.y; qd[r][6] = b.z; qd[r][7] = b.w;
+    // invalid queries get the largest query index bits + a distance bias that can never win
+    qkey[r] = ok ? (uint32_t)i : 0x7fff0000u;
+    m1[r] = KEY_INF;
+    m2[r] = KEY_INF;
+  }
+
+  for (int k = 0; k < n_tiles; ++k) {
+    const int s = k % HM_NSTAGE;
+    const int j0 = (tile_lo + k) * HM_TT;
+    const int nj = min(HM_TT, n2 - j0);
+    mbar_wait(&full[s], (k / HM_NSTAGE) & 1);
+    const uint4* tp = &tile[s][0];
+#pragma unroll 2
+    for (int jj = 0; jj < nj; ++jj) {
+      const uint4 ta = tp[2 * jj], tb = tp[2 * jj + 1];
+      const uint32_t jkey = (uint32_t)(j0 + jj);
+      uint32_t ck = KEY_INF;
+#pragma unroll
+      for (int r = 0; r < RQ; ++r) {
+        const uint32_t d = __popc(qd[r][0] ^ ta.x) + __popc(qd[r][1] ^ ta.y) +
+                           __popc(qd[r][2] ^ ta.z) + __popc(qd[r][3] ^ ta.w) +
+                           __popc(qd[r][4] ^ tb.x) + __popc(qd[r][5] ^ tb.y) +
+                           __popc(qd[r][6] ^ tb.z) + __popc(qd[r][7] ^ tb.w);
+        const uint32_t rk = (d << 16) | jkey;
+        m2[r] = min(m2[r], max(m1[r], rk));
+        m1[r] = min(m1[r], rk);
+        ck = min(ck, (d << 16) + qkey[r]);
+      }
+      ck = warp_min_u32(ck);
+      if ((tid & 31) == 0) atomicMin(&cmin[s][jj], ck);
+    }
+    __syncthreads();  // all warps done with tile[s] and cmin[s]
+    if (tid < nj) {
+      const uint32_t v = cmin[s][tid];
+      if (v < 0x7fff0000u) atomicMin(colmin + (size_t)pair * n_cap + j0 + tid, v);
+    }
+    if (tid < HM_TT) cmin[s][tid] = KEY_INF;
+    if (tid == 0 && k + HM_NSTAGE < n_tiles) {
+      fence_proxy_async();
+      issue(k + HM_NSTAGE);
+    }
+  }
+
+  uint2* rb = reinterpret_cast<uint2*>(rowbest) + ((size_t)pair * n_splits + split) * n_cap;
+#pragma unroll
+  for (int r = 0; r < RQ; ++r) {
+    const int i = q0 + r * HM_THREADS + tid;
+    if (i < n1) rb[i] = make_uint2(m1[r], m2[r]);
+  }
+}
+
+// K1b: per pair, merge split partials, apply cross-check or ratio test, stable-compact by
+// queryIdx, gather KeyPoint.pt of both sides into float64 (image_pair.py:294-299).
+constexpr int CP_THREADS = 1024;
+__global__ void __launch_bounds__(CP_THREADS)
+match_compact_kernel(const uint32_t* __restrict__ rowbest, const uint32_t* __restrict__ colmin,
+                     const int32_t* __restrict__ nkp, const float* __restrict__ kp, int n_cap,
+                     const int32_t* __restrict__ pairs, int n1_direct, int n2_direct,
+                     int n_splits, int mode, float ratio, int32_t* __restrict__ q, int32_t* __restrict__ t, float* __restrict__ dist,
+                     int32_t* __restrict__ t2, float* __restrict__ dist2,
+                     double* __restrict__ pts, int32_t* __restrict__ n_out) {
+  __shared__ int warp_tot[CP_THREADS / 32];
+  __shared__ int base_s;
+  const int pair = blockIdx.x;
+  const int f1 = pairs ? pairs[2 * pair] : 0, f2 = pairs ? pairs[2 * pair + 1] : 0;
+  const int n1 = pairs ? nkp[f1] : n1_direct, n2 = pairs ? nkp[f2] : n2_direct;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint2* rb = reinterpret_cast<const uint2*>(rowbest) + (size_t)pair * n_splits * n_cap;
+  const uint32_t* cm = colmin + (size_t)pair * n_cap;
+  const size_t ob = (size_t)pair * n_cap;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < n1; i0 += CP_THREADS) {
+    const int i = i0 + tid;
+    uint32_t a = KEY_INF, b = KEY_INF;
+    bool keep = false;
+    if (i < n1 && n2 > 0) {
+      for (int s = 0; s < n_splits; ++s) {
+        const uint2 v = rb[(size_t)s * n_cap + i];
+        // merge two sorted pairs
+        const uint32_t lo = min(a, v.x), hi = max(a, v.x);
+        b = min(hi, min(b, v.y));
+        a = lo;
+      }
+      if (mode == VO_MATCH_MUTUAL) {
+        keep = (cm[a & 0xffffu] & 0xffffu) == (uint32_t)i;
+      } else {
+        // Lowe ratio as written in feature_detection.py:24: m.distance < ratio * n.distance
+        // ratio < 0: plain nearest neighbour for every query (no test)
+        keep = ratio < 0.f ? true
+                           : (b != KEY_INF) && ((float)(a >> 16) < ratio * (float)(b >> 16));
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_tot[wid] = __popc(bal);
+    __syncthreads();
+    int off = base_s;
+    for (int w = 0; w < wid; ++w) off += warp_tot[w];
+    off += __popc(bal & ((1u << lane) - 1u));
+    if (keep) {
+      const int j = a & 0xffffu;
+      q[ob + off] = i;
+      t[ob + off] = j;
+      dist[ob + off] = (float)(a >> 16);
+      if (t2) t2[ob + off] = (b == KEY_INF) ? -1 : (int)(b & 0xffffu);
+      if (dist2) dist2[ob + off] = (b == KEY_INF) ? 0.f : (float)(b >> 16);
+      if (pts && kp) {
+        const float2 p1 = reinterpret_cast<const float2*>(kp)[(size_t)f1 * n_cap + i];
+        const float2 p2 = reinterpret_cast<const float2*>(kp)[(size_t)f2 * n_cap + j];
+        double4 o = make_double4((double)p1.x, (double)p1.y, (double)p2.x, (double)p2.y);
+        reinterpret_cast<double4*>(pts)[ob + off] = o;
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int tot = 0;
+      for (int w = 0; w < CP_THREADS / 32; ++w) tot += warp_tot[w];
+      base_s += tot;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) n_out[pair] = base_s;
+}
+
+}  // namespace vo
+
+using namespace vo;
+
+extern "C" size_t vo_match_workspace_bytes(int n_pairs, int n_cap) {
+  // rowbest for up to 16 splits + colmin
+  return (size_t)n_pairs * n_cap * (16 * 2 + 1) * sizeof(uint32_t);
+}
+
+static int pick_splits(int n_pairs, int qtiles, int n_cap) {
+  const long ctas = (long)n_pairs * qtiles;
+  int s = (int)((148L * 4 + ctas - 1) / ctas);
+  const int max_s = (n_cap + HM_TT - 1) / HM_TT;
+  if (s > 16) s = 16;
+  if (s > max_s) s = max_s;
+  if (s < 1) s = 1;
+  return s;
+}
+
+static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, int n2d,
+                          const int32_t* nkp, const float* kp, int n_cap, const int32_t* pairs,
+                          int n_pairs, int mode, float ratio, int32_t* q, int32_t* t, float* dist,
+                          int32_t* t2, float* dist2, double* pts, int32_t* n_out, void* ws,
+                          cudaStream_t st) {
+  // small batches: 128-query tiles + train splits to fill 148 SMs; big batches: 512-query tiles
+  const bool small = (long)n_pairs * ((n_cap + 511) / 512) < 148L * 4;
+  const int rq = small ? 1 : 4;
+  const int qtiles = (n_cap + HM_THREADS * rq - 1) / (HM_THREADS * rq);
+  const int splits = pick_splits(n_pairs, qtiles, n_cap);
+  uint32_t* colmin = (uint32_t*)ws;
+  uint32_t* rowbest = colmin + (size_t)n_pairs * n_cap;
+  cudaMemsetAsync(colmin, 0xff, (size_t)n_pairs * n_cap * sizeof(uint32_t), st);
+  for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
+    const int np = n_pairs - p0 < 65535 ? n_pairs - p0 : 65535;
+    dim3 grid(qtiles, np, splits);
+    uint32_t* rb = rowbest + (size_t)p0 * splits * n_cap * 2;
+    uint32_t* cm = colmin + (size_t)p0 * n_cap;
+    const int32_t* pp = pairs ? pairs + 2 * p0 : nullptr;
+    if (rq == 1)
+      hamming_top2_kernel<1><<<grid, HM_THREADS, 0, st>>>(desc, nkp, n_cap, pp, desc2, n1d, n2d,
+                                                         splits, rb, cm);
+    else
+      hamming_top2_kernel<4><<<grid, HM_THREADS, 0, st>>>(desc, nkp, n_cap, pp, desc2, n1d, n2d,
+                                                         splits, rb, cm);
+    const size_t ob = (size_t)p0 * n_cap;
+    match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
+        rb, cm, nkp, kp, n_cap, pp, n1d, n2d, splits, mode, ratio, q + ob, t + ob, dist + ob,
+        t2 ? t2 + ob : nullptr, dist2 ? dist2 + ob : nullptr, pts ? pts + ob * 4 : nullptr,
+        n_out + p0);
+  }
+  return check_launch("vo_match_hamming");
+}
+
+extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp,
+                                      int n_cap, const int32_t* pairs, int n_pairs, int mode,
+                                      float ratio, int32_t* q, int32_t* t, float* dist,
+                                      int32_t* t2, float* dist2, double* pts, int32_t* n_out,
+                                      void* ws, size_t ws_bytes, void* stream) {
+  VO_REQUIRE(desc && nkp && pairs && q && t && dist && n_out && ws, VO_ERR_INVALID_ARG,
+             "vo_match_hamming_batch: null pointer");
+  VO_REQUIRE(n_cap > 0 && n_cap <= 65535 && n_pairs >= 0, VO_ERR_INVALID_ARG,
+             "vo_match_hamming_batch: n_cap must be in 1..65535 (got %d)", n_cap);
+  VO_REQUIRE(mode == VO_MATCH_MUTUAL || mode == VO_MATCH_KNN2_RATIO, VO_ERR_INVALID_ARG,
+             "vo_match_hamming_batch: bad mode %d", mode);
+  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(n_pairs, n_cap), VO_ERR_WORKSPACE,
+             "vo_match_hamming_batch: workspace too small");
+  if (n_pairs == 0) return VO_OK;
+  return launch_hamming(desc, nullptr, 0, 0, nkp, kp, n_cap, pairs, n_pairs, mode, ratio, q, t,
+                        dist, t2, dist2, pts, n_out, ws, (cudaStream_t)stream);
+}
+
+extern "C" int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode,
+                                float ratio, int32_t* q, int32_t* t, float* dist, int32_t* t2,
+                                float* dist2, int32_t* n_out, void* ws, size_t ws_bytes,
+                                void* stream) {
+  VO_REQUIRE(q && t && dist && n_out && ws, VO_ERR_INVALID_ARG, "vo_match_hamming: null pointer");
+  VO_REQUIRE(n1 >= 0 && n2 >= 0 && n1 <= 65535 && n2 <= 65535, VO_ERR_INVALID_ARG,
+             "vo_match_hamming: descriptor counts must be in 0..65535");
+  VO_REQUIRE(mode == VO_MATCH_MUTUAL || mode == VO_MATCH_KNN2_RATIO, VO_ERR_INVALID_ARG,
+             "vo_match_hamming: bad mode %d", mode);
+  const int n_cap = n1 > n2 ? n1 : n2;
+  if (n1 == 0 || n2 == 0) {
+    cudaMemsetAsync(n_out, 0, sizeof(int32_t), (cudaStream_t)stream);
+    return check_launch("vo_match_hamming");
+  }
+  VO_REQUIRE(d1 && d2, VO_ERR_INVALID_ARG, "vo_match_hamming: null descriptors");
+  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(1, n_cap), VO_ERR_WORKSPACE,
+             "vo_match_hamming: workspace too small");
+  return launch_hamming(d1, d2, n1, n2, nullptr, nullptr, n_cap, nullptr, 1, mode, ratio, q, t,
+                        dist, t2, dist2, nullptr, n_out, ws, (cudaStream_t)stream);
+}
