@@ -236,8 +236,8 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
   const int rq = small ? 1 : 4;
   const int qtiles = (n_cap + HM_THREADS * rq - 1) / (HM_THREADS * rq);
   const int splits = pick_splits(n_pairs, qtiles, n_cap);
-  uint32_t* colmin = (uint32_t*)ws;
-  uint32_t* rowbest = colmin + (size_t)n_pairs * n_cap;
+  uint32_t* rowbest = (uint32_t*)ws;  // 8-byte aligned (uint2 access); colmin sits behind it
+  uint32_t* colmin = rowbest + (size_t)n_pairs * n_cap * 32;
   cudaMemsetAsync(colmin, 0xff, (size_t)n_pairs * n_cap * sizeof(uint32_t), st);
   for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
     const int np = n_pairs - p0 < 65535 ? n_pairs - p0 : 65535;
