@@ -1,0 +1,420 @@
+// ransac.cu — K2/K3 + control: essential-matrix 5-point RANSAC with OpenCV's exact semantics.
+//
+// Replaces cv2.findEssentialMat(p1, p2, K, FM_RANSAC, 0.99, 1) (reference
+// src/image_pair.py:280-286; run twice per pair, src/visual_slam.py:296,165).
+// OpenCV's loop (ptsetreg.cpp RANSACPointSetRegistrator::run) is sequential:
+//     sample(cv::RNG(2^64-1)) -> <=10 models -> count inliers -> strict-greater best update ->
+//     shrink niters (RANSACUpdateNumIters)
+// but every iteration's sample depends only on the RNG stream and the point count, so the GPU
+// replays the stream, solves and scores a whole CHUNK of iterations in parallel (one warp per
+// 5-point solve, one warp per sample for Sampson scoring with coalesced 32-byte correspondence
+// reads) and then applies the sequential best/adaptive-stop rule as a cheap ordered scan.
+// Iterations at or beyond the current bound are skipped, exactly as OpenCV never runs them.
+#include <float.h>
+
+#include "fivept.cuh"
+
+namespace vo {
+
+// ------------------------------------------------------------------ workspace carving
+struct RansacWs {
+  double* ptsn;       // [P][n_cap][4] normalised correspondences
+  double* models;     // [P][C][10][9]
+  uint64_t* rng;      // [P]
+  int32_t* niters;    // [P]
+  int32_t* maxgood;   // [P]
+  int32_t* done;      // [P]
+  int32_t* samples;   // [P][C][5]
+  int32_t* nmodels;   // [P][C]
+  int32_t* counts;    // [P][C][10]
+  size_t bytes;
+};
+
+static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static RansacWs carve(void* base, int P, int n_cap, int C) {
+  RansacWs w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (char*)base + off : nullptr;
+    off += align_up(bytes);
+    return p;
+  };
+  w.ptsn = (double*)take((size_t)P * n_cap * 4 * sizeof(double));
+  w.models = (double*)take((size_t)P * C * 90 * sizeof(double));
+  w.rng = (uint64_t*)take((size_t)P * sizeof(uint64_t));
+  w.niters = (int32_t*)take((size_t)P * sizeof(int32_t));
+  w.maxgood = (int32_t*)take((size_t)P * sizeof(int32_t));
+  w.done = (int32_t*)take((size_t)P * sizeof(int32_t));
+  w.samples = (int32_t*)take((size_t)P * C * 5 * sizeof(int32_t));
+  w.nmodels = (int32_t*)take((size_t)P * C * sizeof(int32_t));
+  w.counts = (int32_t*)take((size_t)P * C * 10 * sizeof(int32_t));
+  w.bytes = off;
+  return w;
+}
+
+constexpr int RANSAC_CHUNK0 = 32;    // first rounds (adaptive runs usually stop inside them)
+constexpr int RANSAC_CHUNK_MAX = 256;
+
+static inline int chunk_cap(int max_iters) {
+  return max_iters < RANSAC_CHUNK_MAX ? (max_iters < 1 ? 1 : max_iters) : RANSAC_CHUNK_MAX;
+}
+
+__device__ __forceinline__ double4 ldg_d4(const double4* p) {
+  const double2 a = __ldg(reinterpret_cast<const double2*>(p));
+  const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+
+// ------------------------------------------------------------------ cv::RNG replay
+__device__ __forceinline__ uint32_t cvrng_next(uint64_t& s) {
+  s = (uint64_t)(uint32_t)s * 4164903690ull + (uint32_t)(s >> 32);
+  return (uint32_t)s;
+}
+// RANSACPointSetRegistrator::getSubset: 5 distinct indices, redraw on duplicate
+__device__ __forceinline__ void draw_sample(uint64_t& s, int count, int32_t* idx) {
+  for (int i = 0; i < 5;) {
+    const int v = (int)(cvrng_next(s) % (uint32_t)count);
+    bool dup = false;
+    for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
+    idx[i] = v;
+    if (!dup) ++i;
+  }
+}
+
+__global__ void ransac_init_kernel(const double* __restrict__ pts, const int32_t* __restrict__ m,
+                                   int n_cap, const double* __restrict__ K, int max_iters,
+                                   RansacWs w, int32_t* __restrict__ n_inl,
+                                   int32_t* __restrict__ status) {
+  const int p = blockIdx.y;
+  const int mp = m[p];
+  const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < mp; i += gridDim.x * blockDim.x) {
+    const double4 v = reinterpret_cast<const double4*>(pts)[(size_t)p * n_cap + i];
+    double4 o;
+    o.x = (v.x - cx) / fx; o.y = (v.y - cy) / fy;
+    o.z = (v.z - cx) / fx; o.w = (v.w - cy) / fy;
+    reinterpret_cast<double4*>(w.ptsn)[(size_t)p * n_cap + i] = o;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    w.rng[p] = 0xffffffffffffffffull;
+    w.niters[p] = max_iters;
+    w.maxgood[p] = 0;
+    w.done[p] = (mp < 5) ? 1 : 0;
+    n_inl[p] = 0;
+    status[p] = (mp < 5) ? VO_ERR_TOO_FEW_POINTS : VO_OK;
+  }
+}
+
+__global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int n_pairs, int chunk,
+                                     int chunk_stride, RansacWs w) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pairs || w.done[p]) return;
+  uint64_t s = w.rng[p];
+  const int count = m[p];
+  int32_t* out = w.samples + (size_t)p * chunk_stride * 5;
+  for (int it = 0; it < chunk; ++it) {
+    int32_t idx[5];
+    draw_sample(s, count, idx);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
+  }
+  w.rng[p] = s;
+}
+
+// ------------------------------------------------------------------ K3 launch: warp per sample
+constexpr int SOLVE_WARPS = 4;
+__global__ void __launch_bounds__(SOLVE_WARPS * 32)
+ransac_solve_kernel(int n_cap, int it0, int chunk, int chunk_stride, RansacWs w) {
+  __shared__ FiveptSmem sm[SOLVE_WARPS];
+  __shared__ double p5[SOLVE_WARPS][20];
+  const int p = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = blockIdx.x * SOLVE_WARPS + warp;
+  if (s >= chunk) return;
+  int32_t* nm = w.nmodels + (size_t)p * chunk_stride + s;
+  if (w.done[p] || it0 + s >= w.niters[p]) {
+    if (lane == 0) *nm = 0;
+    return;
+  }
+  const int32_t* idx = w.samples + ((size_t)p * chunk_stride + s) * 5;
+  if (lane < 20) {
+    const int i = idx[lane >> 2];
+    p5[warp][lane] = w.ptsn[((size_t)p * n_cap + i) * 4 + (lane & 3)];
+  }
+  __syncwarp();
+  const int n = fivept_solve_warp(p5[warp], sm[warp],
+                                  w.models + ((size_t)p * chunk_stride + s) * 90);
+  if (lane == 0) *nm = n;
+}
+
+// ------------------------------------------------------------------ K2: Sampson scoring
+// EMEstimatorCallback::computeError restated with OpenCV's operation order and no FMA
+// contraction: err = float((x2'Ex1)^2 / (a+b+c+d)); inlier iff err <= float(thr^2).
+__device__ __forceinline__ float sampson_exact(const double* __restrict__ E, double x1, double y1,
+                                               double x2, double y2) {
+  const double ex0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], x1), __dmul_rn(E[1], y1)), E[2]);
+  const double ex1 = __dadd_rn(__dadd_rn(__dmul_rn(E[3], x1), __dmul_rn(E[4], y1)), E[5]);
+  const double ex2 = __dadd_rn(__dadd_rn(__dmul_rn(E[6], x1), __dmul_rn(E[7], y1)), E[8]);
+  const double et0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], x2), __dmul_rn(E[3], y2)), E[6]);
+  const double et1 = __dadd_rn(__dadd_rn(__dmul_rn(E[1], x2), __dmul_rn(E[4], y2)), E[7]);
+  const double xe = __dadd_rn(__dadd_rn(__dmul_rn(x2, ex0), __dmul_rn(y2, ex1)), ex2);
+  const double a = __dmul_rn(ex0, ex0), b = __dmul_rn(ex1, ex1);
+  const double c = __dmul_rn(et0, et0), d = __dmul_rn(et1, et1);
+  const double den = __dadd_rn(__dadd_rn(__dadd_rn(a, b), c), d);
+  return __double2float_rn(__ddiv_rn(__dmul_rn(xe, xe), den));
+}
+
+// Division-free fast decision (FMA allowed): only correspondences within 1e-6 relative of the
+// threshold (where float rounding of err could matter) take the exact path above.
+__device__ __forceinline__ bool sampson_inlier(const double* __restrict__ E, double x1, double y1,
+                                               double x2, double y2, float thr2f, double t_lo,
+                                               double t_hi) {
+  const double ex0 = fma(E[0], x1, fma(E[1], y1, E[2]));
+  const double ex1 = fma(E[3], x1, fma(E[4], y1, E[5]));
+  const double ex2 = fma(E[6], x1, fma(E[7], y1, E[8]));
+  const double et0 = fma(E[0], x2, fma(E[3], y2, E[6]));
+  const double et1 = fma(E[1], x2, fma(E[4], y2, E[7]));
+  const double xe = fma(x2, ex0, fma(y2, ex1, ex2));
+  const double den = fma(ex0, ex0, fma(ex1, ex1, fma(et0, et0, et1 * et1)));
+  const double num = xe * xe;
+  bool inl = num < t_lo * den;
+  if (!inl && !(num > t_hi * den)) inl = sampson_exact(E, x1, y1, x2, y2) <= thr2f;
+  return inl;
+}
+
+constexpr int SCORE_WARPS = 8;
+__global__ void __launch_bounds__(SCORE_WARPS * 32)
+ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int chunk, int chunk_stride,
+                    float thr2f, RansacWs w) {
+  __shared__ double Es[SCORE_WARPS][90];
+  const int p = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = blockIdx.x * SCORE_WARPS + warp;
+  if (s >= chunk) return;
+  const int nm = w.nmodels[(size_t)p * chunk_stride + s];
+  if (nm == 0) return;
+  const double* src = w.models + ((size_t)p * chunk_stride + s) * 90;
+  for (int e = lane; e < nm * 9; e += 32) Es[warp][e] = src[e];
+  __syncwarp();
+  const int mp = m[p];
+  const double t_lo = (double)thr2f * (1.0 - 1e-6), t_hi = (double)thr2f * (1.0 + 1e-6);
+  const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
+  int cnt = 0;
+  for (int i0 = 0; i0 < mp; i0 += 32) {
+    const int i = i0 + lane;
+    const bool act = i < mp;
+    double4 v = make_double4(0, 0, 0, 0);
+    if (act) v = ldg_d4(pts + i);
+    for (int k = 0; k < nm; ++k) {
+      const bool inl = act && sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+      const unsigned b = __ballot_sync(0xffffffffu, inl);
+      if (lane == k) cnt += __popc(b);
+    }
+  }
+  if (lane < nm) w.counts[((size_t)p * chunk_stride + s) * 10 + lane] = cnt;
+}
+
+// standalone scoring of arbitrary hypotheses (C-ABI vo_sampson_score): warp per hypothesis
+__global__ void __launch_bounds__(256)
+sampson_score_kernel(const double* __restrict__ E, int H, const double* __restrict__ ptsn, int m,
+                     float thr2f, int32_t* __restrict__ counts, uint8_t* __restrict__ masks) {
+  const int h = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (h >= H) return;
+  double e[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) e[k] = E[(size_t)h * 9 + k];
+  const double4* pts = reinterpret_cast<const double4*>(ptsn);
+  int cnt = 0;
+  for (int i = lane; i < m; i += 32) {
+    const double4 v = ldg_d4(pts + i);
+    const bool inl = sampson_exact(e, v.x, v.y, v.z, v.w) <= thr2f;
+    cnt += inl;
+    if (masks) masks[(size_t)h * m + i] = inl;
+  }
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if (lane == 0) counts[h] = cnt;
+}
+
+// ------------------------------------------------------------------ ordered scan (the sequential rule)
+__device__ int ransac_update_num_iters(double p, double ep, int model_points, int max_iters) {
+  p = fmax(p, 0.0); p = fmin(p, 1.0);
+  ep = fmax(ep, 0.0); ep = fmin(ep, 1.0);
+  double num = fmax(1.0 - p, DBL_MIN);
+  double denom = 1.0 - pow(1.0 - ep, (double)model_points);
+  if (denom < DBL_MIN) return 0;
+  num = log(num);
+  denom = log(denom);
+  return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
+}
+
+__global__ void ransac_scan_kernel(const int32_t* __restrict__ m, int n_pairs, int it0, int chunk,
+                                   int chunk_stride, double conf, int adaptive, RansacWs w,
+                                   double* __restrict__ E_out) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pairs || w.done[p]) return;
+  int niters = w.niters[p], maxgood = w.maxgood[p];
+  const int count = m[p];
+  int bs = -1, bk = -1;
+  for (int s = 0; s < chunk; ++s) {
+    if (it0 + s >= niters) break;
+    const int nm = w.nmodels[(size_t)p * chunk_stride + s];
+    for (int k = 0; k < nm; ++k) {
+      const int c = w.counts[((size_t)p * chunk_stride + s) * 10 + k];
+      if (c > max(maxgood, 4)) {
+        maxgood = c; bs = s; bk = k;
+        if (adaptive)
+          niters = ransac_update_num_iters(conf, (double)(count - c) / count, 5, niters);
+      }
+    }
+  }
+  if (bs >= 0) {
+    const double* src = w.models + ((size_t)p * chunk_stride + bs) * 90 + 9 * bk;
+    for (int e = 0; e < 9; ++e) E_out[(size_t)p * 9 + e] = src[e];
+  }
+  w.niters[p] = niters;
+  w.maxgood[p] = maxgood;
+  if (it0 + chunk >= niters) w.done[p] = 1;
+}
+
+__global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap, float thr2f,
+                                   RansacWs w, double* __restrict__ E_out,
+                                   uint8_t* __restrict__ mask, int32_t* __restrict__ n_inl,
+                                   int32_t* __restrict__ n_iters, int32_t* __restrict__ status) {
+  const int p = blockIdx.y;
+  const int mp = m[p];
+  const int good = w.maxgood[p];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    n_inl[p] = good;
+    n_iters[p] = w.niters[p];
+    if (good == 0) {
+      if (status[p] == VO_OK) status[p] = VO_ERR_TOO_FEW_POINTS;  // no model found
+      for (int e = 0; e < 9; ++e) E_out[(size_t)p * 9 + e] = 0.0;
+    }
+  }
+  double e[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) e[k] = good ? E_out[(size_t)p * 9 + k] : 0.0;
+  const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_cap; i += gridDim.x * blockDim.x) {
+    uint8_t v = 0;
+    if (i < mp && good) {
+      const double4 q = pts[i];
+      v = sampson_exact(e, q.x, q.y, q.z, q.w) <= thr2f;
+    }
+    mask[(size_t)p * n_cap + i] = v;
+  }
+}
+
+}  // namespace vo
+
+using namespace vo;
+
+extern "C" size_t vo_essential_workspace_bytes(int n_pairs, int n_cap, int max_iters) {
+  if (n_pairs <= 0 || n_cap <= 0) return 0;
+  return carve(nullptr, n_pairs, n_cap, chunk_cap(max_iters)).bytes;
+}
+
+extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, int n_cap,
+                                         int n_pairs, const double* K, double conf, double thr_px,
+                                         int max_iters, int adaptive, double* E, uint8_t* mask,
+                                         int32_t* n_inl, int32_t* n_iters, int32_t* status,
+                                         void* ws, size_t ws_bytes, void* stream) {
+  VO_REQUIRE(pts && m && K && E && mask && n_inl && n_iters && status && ws, VO_ERR_INVALID_ARG,
+             "vo_essential_ransac_batch: null pointer");
+  VO_REQUIRE(n_cap > 0 && n_pairs >= 0 && max_iters > 0, VO_ERR_INVALID_ARG,
+             "vo_essential_ransac_batch: bad sizes");
+  VO_REQUIRE(n_pairs <= 65535, VO_ERR_INVALID_ARG,
+             "vo_essential_ransac_batch: at most 65535 pairs per call");
+  const int C = chunk_cap(max_iters);
+  RansacWs w = carve(ws, n_pairs, n_cap, C);
+  VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_essential_ransac_batch: workspace too small");
+  if (n_pairs == 0) return VO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  // threshold /= (fx+fy)/2 needs K on the host: K is tiny, but reading it would sync. Instead the
+  // caller-visible contract is thr in pixels; fx,fy are read back once per call (pageable copy).
+  double Kh[9];
+  if (cudaMemcpyAsync(Kh, K, sizeof(Kh), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess)
+    return check_launch("vo_essential_ransac_batch(K readback)");
+  const double thr = thr_px / ((Kh[0] + Kh[4]) / 2.0);
+  const float thr2f = (float)(thr * thr);
+
+  const int nb = (n_cap + 255) / 256;
+  ransac_init_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(pts, m, n_cap, K, max_iters, w,
+                                                                    n_inl, status);
+  int it0 = 0;
+  int chunk = RANSAC_CHUNK0 < C ? RANSAC_CHUNK0 : C;
+  int round = 0;
+  while (it0 < max_iters) {
+    if (it0 + chunk > max_iters) chunk = max_iters - it0;
+    ransac_sample_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, chunk, C, w);
+    ransac_solve_kernel<<<dim3((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS, n_pairs),
+                          SOLVE_WARPS * 32, 0, st>>>(n_cap, it0, chunk, C, w);
+    ransac_score_kernel<<<dim3((chunk + SCORE_WARPS - 1) / SCORE_WARPS, n_pairs),
+                          SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, thr2f, w);
+    ransac_scan_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, it0, chunk, C, conf,
+                                                          adaptive, w, E);
+    it0 += chunk;
+    ++round;
+    if (adaptive) {
+      if (round >= 2 && chunk < C) chunk = (chunk * 2 < C) ? chunk * 2 : C;
+    } else {
+      chunk = C;
+    }
+  }
+  ransac_mask_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(m, n_cap, thr2f, w, E, mask,
+                                                                    n_inl, n_iters, status);
+  return check_launch("vo_essential_ransac_batch");
+}
+
+__global__ void __launch_bounds__(SOLVE_WARPS * 32)
+fivept_standalone_kernel(const double* __restrict__ ptsn, const int32_t* __restrict__ samples,
+                         int n_samples, double* __restrict__ E, int32_t* __restrict__ n_models) {
+  __shared__ FiveptSmem sm[SOLVE_WARPS];
+  __shared__ double p5[SOLVE_WARPS][20];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = blockIdx.x * SOLVE_WARPS + warp;
+  if (s >= n_samples) return;
+  if (lane < 20) p5[warp][lane] = ptsn[(size_t)samples[5 * s + (lane >> 2)] * 4 + (lane & 3)];
+  __syncwarp();
+  const int n = fivept_solve_warp(p5[warp], sm[warp], E + (size_t)s * 90);
+  if (lane == 0) n_models[s] = n;
+}
+
+extern "C" int vo_fivept_solve(const double* pts_n, int m, const int32_t* samples, int n_samples,
+                               double* E, int32_t* n_models, void* stream) {
+  VO_REQUIRE(pts_n && samples && E && n_models, VO_ERR_INVALID_ARG, "vo_fivept_solve: null pointer");
+  VO_REQUIRE(m >= 5, VO_ERR_TOO_FEW_POINTS, "vo_fivept_solve: needs >= 5 points (got %d)", m);
+  if (n_samples <= 0) return VO_OK;
+  fivept_standalone_kernel<<<(n_samples + SOLVE_WARPS - 1) / SOLVE_WARPS, SOLVE_WARPS * 32, 0,
+                             (cudaStream_t)stream>>>(pts_n, samples, n_samples, E, n_models);
+  return check_launch("vo_fivept_solve");
+}
+
+extern "C" int vo_sampson_score(const double* E, int H, const double* pts_n, int m, float thr2,
+                                int32_t* counts, uint8_t* masks, void* stream) {
+  VO_REQUIRE(E && pts_n && counts, VO_ERR_INVALID_ARG, "vo_sampson_score: null pointer");
+  if (H <= 0) return VO_OK;
+  sampson_score_kernel<<<(H + 7) / 8, 256, 0, (cudaStream_t)stream>>>(E, H, pts_n, m, thr2, counts,
+                                                                     masks);
+  return check_launch("vo_sampson_score");
+}
+
+__global__ void samples_standalone_kernel(int count, int n_iters, int32_t* out) {
+  if (blockIdx.x || threadIdx.x) return;
+  uint64_t s = 0xffffffffffffffffull;
+  for (int it = 0; it < n_iters; ++it) {
+    int32_t idx[5];
+    draw_sample(s, count, idx);
+    for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
+  }
+}
+
+extern "C" int vo_ransac_samples(int count, int n_iters, int32_t* samples, void* stream) {
+  VO_REQUIRE(samples, VO_ERR_INVALID_ARG, "vo_ransac_samples: null pointer");
+  VO_REQUIRE(count >= 5, VO_ERR_TOO_FEW_POINTS, "vo_ransac_samples: needs >= 5 points");
+  if (n_iters <= 0) return VO_OK;
+  samples_standalone_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(count, n_iters, samples);
+  return check_launch("vo_ransac_samples");
+}

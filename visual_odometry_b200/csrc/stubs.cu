@@ -4,11 +4,6 @@
 #define NOT_YET(name) vo::set_error(name ": not implemented yet"); return VO_ERR_INVALID_ARG;
 extern "C" size_t vo_match_l2_workspace_bytes(int, int, int) { return 0; }
 extern "C" int vo_match_l2_batch(const float*, const int32_t*, const float*, int, int, const int32_t*, int, int, float, int32_t*, int32_t*, float*, int32_t*, float*, double*, int32_t*, void*, size_t, void*) { NOT_YET("vo_match_l2_batch") }
-extern "C" size_t vo_essential_workspace_bytes(int, int, int) { return 0; }
-extern "C" int vo_essential_ransac_batch(const double*, const int32_t*, int, int, const double*, double, double, int, int, double*, uint8_t*, int32_t*, int32_t*, int32_t*, void*, size_t, void*) { NOT_YET("vo_essential_ransac_batch") }
-extern "C" int vo_fivept_solve(const double*, int, const int32_t*, int, double*, int32_t*, void*) { NOT_YET("vo_fivept_solve") }
-extern "C" int vo_sampson_score(const double*, int, const double*, int, float, int32_t*, uint8_t*, void*) { NOT_YET("vo_sampson_score") }
-extern "C" int vo_ransac_samples(int, int, int32_t*, void*) { NOT_YET("vo_ransac_samples") }
 extern "C" size_t vo_pose_workspace_bytes(int, int) { return 0; }
 extern "C" int vo_recover_pose_batch(const double*, const double*, const int32_t*, const uint8_t*, int, int, const double*, double, double*, double*, uint8_t*, int32_t*, void*, size_t, void*) { NOT_YET("vo_recover_pose_batch") }
 extern "C" int vo_triangulate(const double*, const double*, const double*, const double*, int, double*, int, void*) { NOT_YET("vo_triangulate") }
