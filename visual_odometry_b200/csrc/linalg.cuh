@@ -1,0 +1,134 @@
+// linalg.cuh — tiny fp64 dense algebra kept entirely in registers (fully unrolled).
+// One-sided (Hestenes) Jacobi SVD, the same family OpenCV's cv::SVD uses for small matrices
+// (core/src/lapack.cpp JacobiSVDImpl_), so null vectors agree with cv2 to rounding.
+#pragma once
+#include "common.cuh"
+
+namespace vo {
+
+// A (N x N, row-major, modified in place to U*diag(s)); V accumulates the right singular vectors
+// as columns. Column norms of the result are the singular values (unsorted).
+template <int N>
+__device__ __forceinline__ void jacobi_svd(double (&A)[N][N], double (&V)[N][N]) {
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+#pragma unroll
+    for (int j = 0; j < N; ++j) V[i][j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 30; ++sweep) {
+    bool changed = false;
+#pragma unroll
+    for (int p = 0; p < N - 1; ++p) {
+#pragma unroll
+      for (int q = p + 1; q < N; ++q) {
+        double alpha = 0.0, beta = 0.0, gamma = 0.0;
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          alpha += A[k][p] * A[k][p];
+          beta += A[k][q] * A[k][q];
+          gamma += A[k][p] * A[k][q];
+        }
+        if (fabs(gamma) <= 2.2e-15 * sqrt(alpha * beta)) continue;
+        changed = true;
+        const double zeta = (beta - alpha) / (2.0 * gamma);
+        const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double c = rsqrt(1.0 + t * t);
+        const double s = c * t;
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const double ap = A[k][p], aq = A[k][q];
+          A[k][p] = c * ap - s * aq;
+          A[k][q] = s * ap + c * aq;
+          const double vp = V[k][p], vq = V[k][q];
+          V[k][p] = c * vp - s * vq;
+          V[k][q] = s * vp + c * vq;
+        }
+      }
+    }
+    if (!changed) break;
+  }
+}
+
+// Right singular vector of the smallest singular value of the 4x4 DLT matrix (unit norm).
+__device__ __forceinline__ void null_vector4(double (&A)[4][4], double (&x)[4]) {
+  double V[4][4];
+  jacobi_svd<4>(A, V);
+  double best = 1e300;
+  int bj = 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double n2 = A[0][j] * A[0][j] + A[1][j] * A[1][j] + A[2][j] * A[2][j] + A[3][j] * A[3][j];
+    if (n2 < best) { best = n2; bj = j; }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    x[k] = (bj == 0) ? V[k][0] : (bj == 1) ? V[k][1] : (bj == 2) ? V[k][2] : V[k][3];
+}
+
+// cv::triangulatePoints for one point: rows x*P[2]-P[0], y*P[2]-P[1] for both cameras.
+__device__ __forceinline__ void dlt_point(const double* __restrict__ P1,
+                                          const double* __restrict__ P2, double x1, double y1,
+                                          double x2, double y2, double (&X)[4]) {
+  double A[4][4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    A[0][k] = x1 * P1[8 + k] - P1[k];
+    A[1][k] = y1 * P1[8 + k] - P1[4 + k];
+    A[2][k] = x2 * P2[8 + k] - P2[k];
+    A[3][k] = y2 * P2[8 + k] - P2[4 + k];
+  }
+  null_vector4(A, X);
+}
+
+__device__ __forceinline__ double det3(const double* M) {
+  return M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) +
+         M[2] * (M[3] * M[7] - M[4] * M[6]);
+}
+
+// decomposeEssentialMat (five-point.cpp): E = U diag(1,1,0) V^T, det(U),det(V^T) > 0,
+// R1 = U W V^T, R2 = U W^T V^T, t = U[:,2].  Row-major outputs.
+__device__ inline void decompose_essential(const double* __restrict__ E, double* R1, double* R2,
+                                           double* t) {
+  double A[3][3], V[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) A[i][j] = E[3 * i + j];
+  jacobi_svd<3>(A, V);
+  double s2[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) s2[j] = A[0][j] * A[0][j] + A[1][j] * A[1][j] + A[2][j] * A[2][j];
+  // order columns by descending singular value
+  int o0 = 0, o1 = 1, o2 = 2;
+  if (s2[o0] < s2[o1]) { int x = o0; o0 = o1; o1 = x; }
+  if (s2[o1] < s2[o2]) { int x = o1; o1 = o2; o2 = x; }
+  if (s2[o0] < s2[o1]) { int x = o0; o0 = o1; o1 = x; }
+  double U[3][3], W[3][3];  // W here = V with ordered columns
+  const double i0 = rsqrt(s2[o0]), i1 = rsqrt(s2[o1]);
+  for (int k = 0; k < 3; ++k) {
+    U[k][0] = A[k][o0] * i0;
+    U[k][1] = A[k][o1] * i1;
+    W[k][0] = V[k][o0];
+    W[k][1] = V[k][o1];
+    W[k][2] = V[k][o2];
+  }
+  // third left vector completes a right-handed basis (sigma_3 = 0 leaves it free): det(U) = +1
+  U[0][2] = U[1][0] * U[2][1] - U[2][0] * U[1][1];
+  U[1][2] = U[2][0] * U[0][1] - U[0][0] * U[2][1];
+  U[2][2] = U[0][0] * U[1][1] - U[1][0] * U[0][1];
+  double Vt[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) Vt[3 * i + j] = W[j][i];
+  if (det3(Vt) < 0)
+    for (int e = 0; e < 9; ++e) Vt[e] = -Vt[e];
+  // U*W = [-u2, u1, u3] ; U*W^T = [u2, -u1, u3]
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      const double a = -U[i][1] * Vt[j] + U[i][0] * Vt[3 + j];
+      const double b = U[i][2] * Vt[6 + j];
+      R1[3 * i + j] = a + b;
+      R2[3 * i + j] = -a + b;
+    }
+  t[0] = U[0][2]; t[1] = U[1][2]; t[2] = U[2][2];
+}
+
+}  // namespace vo

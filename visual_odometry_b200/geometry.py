@@ -83,3 +83,62 @@ def ransac_samples(count, n_iters, device="cuda"):
     out = torch.empty(n_iters, 5, dtype=I32, device=device)
     _lib.check(lib.vo_ransac_samples(int(count), int(n_iters), _lib.ptr(out), _lib.cur_stream()))
     return out
+
+
+def recover_pose_batch(E, pts, m, mask, K, dist_thresh=50.0, want_mask=False):
+    """Batched cv2.recoverPose(E, p1, p2, K) over the inliers of `mask`
+    (reference src/image_pair.py:304-308).  Returns dict(R [B,3,3], t [B,3], n_good [B],
+    pose_mask [B,n_cap] u8 {0,255} if requested)."""
+    lib = _lib.load()
+    B, n_cap = pts.shape[0], pts.shape[1]
+    dev = pts.device
+    R = torch.empty(B, 3, 3, dtype=F64, device=dev)
+    t = torch.empty(B, 3, dtype=F64, device=dev)
+    n_good = torch.empty(B, dtype=I32, device=dev)
+    pm = torch.empty(B, n_cap, dtype=U8, device=dev) if want_mask else None
+    wsb = lib.vo_pose_workspace_bytes(B, n_cap)
+    ws = _workspace(wsb, dev, "pose")
+    _lib.check(lib.vo_recover_pose_batch(
+        _lib.ptr(E.contiguous()), _lib.ptr(pts), _lib.ptr(m), _lib.ptr(mask), n_cap, B,
+        _lib.ptr(K.contiguous()), float(dist_thresh), _lib.ptr(R), _lib.ptr(t), _lib.ptr(pm),
+        _lib.ptr(n_good), _lib.ptr(ws), ws.numel(), _lib.cur_stream()))
+    return dict(R=R, t=t, n_good=n_good, pose_mask=pm)
+
+
+def triangulate(P1, P2, x1, x2, dehomog=False):
+    """cv2.triangulatePoints(P1, P2, x1, x2) (reference src/image_pair.py:332-336) for points
+    given as [n,2] f64 tensors; returns X [n,4] (divide by w if dehomog, image_pair.py:339)."""
+    lib = _lib.load()
+    n = x1.shape[0]
+    X = torch.empty(n, 4, dtype=F64, device=x1.device)
+    _lib.check(lib.vo_triangulate(_lib.ptr(P1.contiguous()), _lib.ptr(P2.contiguous()),
+                                  _lib.ptr(x1.contiguous()), _lib.ptr(x2.contiguous()), n,
+                                  _lib.ptr(X), int(bool(dehomog)), _lib.cur_stream()))
+    return X
+
+
+def triangulate_pairs(R, t, pts, m, mask, K):
+    """Per pair: ImagePair.reconstruct_3d_points default path (src/image_pair.py:316-339):
+    P_first = K[R^T|-R^T t] with frame-1 points, P_second = K[I|0] with frame-2 points, inliers
+    only, X /= w.  Returns (X [B,n_cap,4] compacted, n_x [B])."""
+    lib = _lib.load()
+    B, n_cap = pts.shape[0], pts.shape[1]
+    X = torch.empty(B, n_cap, 4, dtype=F64, device=pts.device)
+    n_x = torch.empty(B, dtype=I32, device=pts.device)
+    _lib.check(lib.vo_triangulate_pairs(_lib.ptr(R.contiguous()), _lib.ptr(t.contiguous()),
+                                        _lib.ptr(pts), _lib.ptr(m), _lib.ptr(mask), n_cap, B,
+                                        _lib.ptr(K.contiguous()), _lib.ptr(X), _lib.ptr(n_x),
+                                        _lib.cur_stream()))
+    return X, n_x
+
+
+def chain_poses(R, t, P0=None):
+    """Trajectory chaining (north_star): P_0 = I (or P0), P_k = [R_k|t_k] * P_{k-1}.
+    Returns poses [B+1,4,4]."""
+    lib = _lib.load()
+    B = R.shape[0]
+    poses = torch.empty(B + 1, 4, 4, dtype=F64, device=R.device)
+    _lib.check(lib.vo_chain_poses(_lib.ptr(R.contiguous()), _lib.ptr(t.contiguous()), B,
+                                  _lib.ptr(P0.contiguous()) if P0 is not None else None,
+                                  _lib.ptr(poses), _lib.cur_stream()))
+    return poses
