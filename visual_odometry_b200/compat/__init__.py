@@ -1,0 +1,20 @@
+"""Bare-name modules (`initials`, `image_pair`, `frame`, `frame_generator`, `image_and_keypoints`,
+`triangulate_points_from_images`) that shadow the reference's src/ modules of the same name.
+
+Put this directory on sys.path AHEAD of the reference's src/ (see `install()`), and the
+reference's own `main.py`, `main_triangulate.py`, `visual_slam.py`, `map.py`, `tracked_*.py`,
+`observation.py` run unchanged on the B200 hot path (seam 2).
+"""
+import os
+import sys
+
+
+def install(reference_src=None):
+    """Prepend the compat directory (and optionally the reference's src/) to sys.path."""
+    here = os.path.dirname(os.path.abspath(__file__))
+    if reference_src and reference_src not in sys.path:
+        sys.path.insert(0, reference_src)
+    if here in sys.path:
+        sys.path.remove(here)
+    sys.path.insert(0, here)
+    return here

@@ -183,10 +183,16 @@ __device__ __forceinline__ bool sampson_inlier(const double* __restrict__ E, dou
   return inl;
 }
 
+// findEssentialMat: threshold /= (fx+fy)/2 ; findInliers compares with float(thr*thr)
+__device__ __forceinline__ float thr2_from_K(const double* __restrict__ K, double thr_px) {
+  const double thr = thr_px / ((K[0] + K[4]) / 2.0);
+  return (float)(thr * thr);
+}
+
 constexpr int SCORE_WARPS = 8;
 __global__ void __launch_bounds__(SCORE_WARPS * 32)
 ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int chunk, int chunk_stride,
-                    float thr2f, RansacWs w) {
+                    const double* __restrict__ K, double thr_px, RansacWs w) {
   __shared__ double Es[SCORE_WARPS][90];
   const int p = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -198,6 +204,7 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int chunk, int chu
   for (int e = lane; e < nm * 9; e += 32) Es[warp][e] = src[e];
   __syncwarp();
   const int mp = m[p];
+  const float thr2f = thr2_from_K(K, thr_px);
   const double t_lo = (double)thr2f * (1.0 - 1e-6), t_hi = (double)thr2f * (1.0 + 1e-6);
   const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
   int cnt = 0;
@@ -277,12 +284,13 @@ __global__ void ransac_scan_kernel(const int32_t* __restrict__ m, int n_pairs, i
   if (it0 + chunk >= niters) w.done[p] = 1;
 }
 
-__global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap, float thr2f,
-                                   RansacWs w, double* __restrict__ E_out,
+__global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap,
+                                   const double* __restrict__ K, double thr_px, RansacWs w, double* __restrict__ E_out,
                                    uint8_t* __restrict__ mask, int32_t* __restrict__ n_inl,
                                    int32_t* __restrict__ n_iters, int32_t* __restrict__ status) {
   const int p = blockIdx.y;
   const int mp = m[p];
+  const float thr2f = thr2_from_K(K, thr_px);
   const int good = w.maxgood[p];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     n_inl[p] = good;
@@ -331,15 +339,6 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
   VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_essential_ransac_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  // threshold /= (fx+fy)/2 needs K on the host: K is tiny, but reading it would sync. Instead the
-  // caller-visible contract is thr in pixels; fx,fy are read back once per call (pageable copy).
-  double Kh[9];
-  if (cudaMemcpyAsync(Kh, K, sizeof(Kh), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-      cudaStreamSynchronize(st) != cudaSuccess)
-    return check_launch("vo_essential_ransac_batch(K readback)");
-  const double thr = thr_px / ((Kh[0] + Kh[4]) / 2.0);
-  const float thr2f = (float)(thr * thr);
-
   const int nb = (n_cap + 255) / 256;
   ransac_init_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(pts, m, n_cap, K, max_iters, w,
                                                                     n_inl, status);
@@ -352,7 +351,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
     ransac_solve_kernel<<<dim3((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS, n_pairs),
                           SOLVE_WARPS * 32, 0, st>>>(n_cap, it0, chunk, C, w);
     ransac_score_kernel<<<dim3((chunk + SCORE_WARPS - 1) / SCORE_WARPS, n_pairs),
-                          SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, thr2f, w);
+                          SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, K, thr_px, w);
     ransac_scan_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, it0, chunk, C, conf,
                                                           adaptive, w, E);
     it0 += chunk;
@@ -363,7 +362,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
       chunk = C;
     }
   }
-  ransac_mask_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(m, n_cap, thr2f, w, E, mask,
+  ransac_mask_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(m, n_cap, K, thr_px, w, E, mask,
                                                                     n_inl, n_iters, status);
   return check_launch("vo_essential_ransac_batch");
 }

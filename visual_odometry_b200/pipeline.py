@@ -1,0 +1,170 @@
+"""Batched two-view VO over many frame pairs: the form of the hot path that fills a B200.
+
+One `PairPipeline.run_*` call = for every pair (a, b) of a frame set, exactly the reference's
+per-pair chain (src/visual_slam.py:294-298 -> src/image_pair.py:233-354):
+    match_features -> determine_essential_matrix -> estimate_camera_movement ->
+    reconstruct_3d_points,
+followed by the north-star trajectory chaining P_k = [R_k|t_k] P_{k-1} for consecutive pairs.
+All stages are launches of libvo_b200 kernels on one CUDA stream; buffers are allocated once.
+`run_host` is the end-to-end entry (host numpy in, host numpy out, copies inside).
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from . import geometry as G
+
+F64, I32, U8, F32 = torch.float64, torch.int32, torch.uint8, torch.float32
+
+
+class PairPipeline:
+    def __init__(self, n_cap, max_pairs, max_frames=None, descriptor="orb", K=None,
+                 device="cuda", prob=0.99, threshold=1.0, max_iters=1000, adaptive=True,
+                 match_mode=_lib.MATCH_MUTUAL, ratio=0.0, triangulate=True, chain=True):
+        self.lib = _lib.load()
+        self.dev = torch.device(device)
+        self.n_cap, self.P = int(n_cap), int(max_pairs)
+        self.F = int(max_frames if max_frames is not None else max_pairs + 1)
+        self.descriptor = descriptor
+        self.D = 32 if descriptor == "orb" else 128
+        self.ddtype = U8 if descriptor == "orb" else F32
+        self.prob, self.threshold = float(prob), float(threshold)
+        self.max_iters, self.adaptive = int(max_iters), bool(adaptive)
+        self.match_mode, self.ratio = int(match_mode), float(ratio)
+        self.do_tri, self.do_chain = triangulate, chain
+        dev, P, N, F = self.dev, self.P, self.n_cap, self.F
+        e = lambda *s, dt: torch.empty(*s, dtype=dt, device=dev)
+        # inputs resident in HBM
+        self.desc = e(F, N, self.D, dt=self.ddtype)
+        self.kp = e(F, N, 2, dt=F32)
+        self.nkp = e(F, dt=I32)
+        self.pairs = e(P, 2, dt=I32)
+        self.K = e(3, 3, dt=F64)
+        if K is not None:
+            self.K.copy_(torch.as_tensor(np.asarray(K, np.float64)))
+        # per-pair outputs
+        self.q, self.t_idx = e(P, N, dt=I32), e(P, N, dt=I32)
+        self.dist = e(P, N, dt=F32)
+        self.pts = e(P, N, 4, dt=F64)
+        self.n_match = e(P, dt=I32)
+        self.E = e(P, 3, 3, dt=F64)
+        self.mask = e(P, N, dt=U8)
+        self.n_inl, self.n_iters, self.status = e(P, dt=I32), e(P, dt=I32), e(P, dt=I32)
+        self.R, self.t = e(P, 3, 3, dt=F64), e(P, 3, dt=F64)
+        self.n_good = e(P, dt=I32)
+        self.X = e(P, N, 4, dt=F64) if triangulate else None
+        self.n_x = e(P, dt=I32)
+        self.poses = e(P + 1, 4, 4, dt=F64)
+        # workspaces
+        if descriptor == "orb":
+            self.ws_match = e(max(self.lib.vo_match_workspace_bytes(P, N), 256), dt=U8)
+        else:
+            self.ws_match = e(max(self.lib.vo_match_l2_workspace_bytes(P, N, self.D), 256), dt=U8)
+        self.ws_ess = e(max(self.lib.vo_essential_workspace_bytes(P, N, self.max_iters), 256), dt=U8)
+        self.ws_pose = e(max(self.lib.vo_pose_workspace_bytes(P, N), 256), dt=U8)
+        # pinned staging for run_host
+        self._pin = None
+        # kernels launched per run (for bench.py's gpu_launches claim; see launches_per_run)
+        self.launches = 0
+
+    # ------------------------------------------------------------------ device-resident run
+    def run_device(self, n_pairs, stream=None):
+        """Inputs already in self.desc/kp/nkp/pairs. Asynchronous; results in the attributes."""
+        lib, p = self.lib, _lib.ptr
+        st = _lib.cur_stream() if stream is None else stream
+        N, B = self.n_cap, int(n_pairs)
+        if self.descriptor == "orb":
+            _lib.check(lib.vo_match_hamming_batch(
+                p(self.desc), p(self.nkp), p(self.kp), N, p(self.pairs), B, self.match_mode,
+                self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None, p(self.pts),
+                p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
+        else:
+            _lib.check(lib.vo_match_l2_batch(
+                p(self.desc), p(self.nkp), p(self.kp), N, self.D, p(self.pairs), B,
+                self.match_mode, self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None,
+                p(self.pts), p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
+        _lib.check(lib.vo_essential_ransac_batch(
+            p(self.pts), p(self.n_match), N, B, p(self.K), self.prob, self.threshold,
+            self.max_iters, int(self.adaptive), p(self.E), p(self.mask), p(self.n_inl),
+            p(self.n_iters), p(self.status), p(self.ws_ess), self.ws_ess.numel(), st))
+        _lib.check(lib.vo_recover_pose_batch(
+            p(self.E), p(self.pts), p(self.n_match), p(self.mask), N, B, p(self.K), 50.0,
+            p(self.R), p(self.t), None, p(self.n_good), p(self.ws_pose), self.ws_pose.numel(), st))
+        if self.do_tri:
+            _lib.check(lib.vo_triangulate_pairs(
+                p(self.R), p(self.t), p(self.pts), p(self.n_match), p(self.mask), N, B, p(self.K),
+                p(self.X), p(self.n_x), st))
+        if self.do_chain:
+            _lib.check(lib.vo_chain_poses(p(self.R), p(self.t), B, None, p(self.poses), st))
+
+    def launches_per_run(self):
+        """Number of libvo_b200 kernels one run_device issues (memset excluded)."""
+        rounds, it0, chunk, r = 0, 0, min(32, self.max_iters), 0
+        cap = min(256, self.max_iters)
+        while it0 < self.max_iters:
+            chunk = min(chunk, self.max_iters - it0)
+            it0 += chunk
+            rounds += 1
+            r += 1
+            if self.adaptive:
+                if r >= 2 and chunk < cap:
+                    chunk = min(chunk * 2, cap)
+            else:
+                chunk = cap
+        return 2 + (1 + 4 * rounds + 1) + 1 + int(self.do_tri) + int(self.do_chain)
+
+    # ------------------------------------------------------------------ host-buffer run (e2e)
+    def _pinned(self):
+        if self._pin is None:
+            pin = lambda *s, dt: torch.empty(*s, dtype=dt, pin_memory=True)
+            self._pin = dict(
+                desc=pin(self.F, self.n_cap, self.D, dt=self.ddtype),
+                kp=pin(self.F, self.n_cap, 2, dt=F32), nkp=pin(self.F, dt=I32),
+                pairs=pin(self.P, 2, dt=I32),
+                R=pin(self.P, 3, 3, dt=F64), t=pin(self.P, 3, dt=F64),
+                n_inl=pin(self.P, dt=I32), n_match=pin(self.P, dt=I32),
+                status=pin(self.P, dt=I32), poses=pin(self.P + 1, 4, 4, dt=F64))
+        return self._pin
+
+    def stage_host(self, desc, kp, nkp, pairs):
+        """Copy numpy inputs into the pinned staging area (not part of a timed step: it stands
+        for the caller's own pinned frame buffers)."""
+        pin = self._pinned()
+        f, b = desc.shape[0], pairs.shape[0]
+        pin["desc"][:f].copy_(torch.from_numpy(np.ascontiguousarray(desc)))
+        pin["kp"][:f].copy_(torch.from_numpy(np.ascontiguousarray(kp, np.float32)))
+        pin["nkp"][:f].copy_(torch.from_numpy(np.ascontiguousarray(nkp, np.int32)))
+        pin["pairs"][:b].copy_(torch.from_numpy(np.ascontiguousarray(pairs, np.int32)))
+        return f, b
+
+    def run_staged(self, n_frames, n_pairs):
+        """H2D of the staged inputs, the whole chain, D2H of poses/counts; synchronises.
+        Returns (h2d_bytes, d2h_bytes)."""
+        pin, f, b = self._pinned(), int(n_frames), int(n_pairs)
+        self.desc[:f].copy_(pin["desc"][:f], non_blocking=True)
+        self.kp[:f].copy_(pin["kp"][:f], non_blocking=True)
+        self.nkp[:f].copy_(pin["nkp"][:f], non_blocking=True)
+        self.pairs[:b].copy_(pin["pairs"][:b], non_blocking=True)
+        self.run_device(b)
+        pin["R"][:b].copy_(self.R[:b], non_blocking=True)
+        pin["t"][:b].copy_(self.t[:b], non_blocking=True)
+        pin["n_inl"][:b].copy_(self.n_inl[:b], non_blocking=True)
+        pin["n_match"][:b].copy_(self.n_match[:b], non_blocking=True)
+        pin["status"][:b].copy_(self.status[:b], non_blocking=True)
+        pin["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        h2d = sum(pin[k][:f].numel() * pin[k].element_size() for k in ("desc", "kp", "nkp")) + \
+            pin["pairs"][:b].numel() * 4
+        d2h = b * (9 + 3) * 8 + b * 3 * 4 + (b + 1) * 16 * 8
+        return h2d, d2h
+
+    def run_host(self, desc, kp, nkp, pairs):
+        """numpy in -> numpy out (R [B,3,3], t [B,3], n_inl, n_match, status, poses [B+1,4,4])."""
+        f, b = self.stage_host(desc, kp, nkp, pairs)
+        self.run_staged(f, b)
+        pin = self._pin
+        return dict(R=pin["R"][:b].numpy().copy(), t=pin["t"][:b].numpy().copy(),
+                    n_inl=pin["n_inl"][:b].numpy().copy(),
+                    n_match=pin["n_match"][:b].numpy().copy(),
+                    status=pin["status"][:b].numpy().copy(),
+                    poses=pin["poses"][:b + 1].numpy().copy())
