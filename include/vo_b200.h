@@ -126,6 +126,14 @@ int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int 
                   double reproj_px, double conf, double* rvec, double* tvec, int32_t* inliers,
                   int32_t* n_inl, int32_t* ok, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
+ * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
+ * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).
+ * kernel_id: 0 = hamming_top2_kernel (K1), 1 = ransac_score_kernel (K2), 2 = l2 tensor-core GEMM. */
+int vo_profile_enable(int on);
+int vo_profile_read(int kernel_id, double* total_ms, int* launches);
+int vo_measure_popc_peak(double* popc32_per_s, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,6 +15,13 @@ namespace vo {
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 
+// in-stream CUDA-event timing of selected kernels (off unless vo_profile_enable(1))
+struct ProfScope {
+  int id; cudaStream_t st; cudaEvent_t e0 = nullptr, e1 = nullptr;
+  ProfScope(int kernel_id, cudaStream_t stream);
+  ~ProfScope();
+};
+
 #define VO_REQUIRE(cond, code, ...)      \
   do {                                   \
     if (!(cond)) {                       \

@@ -245,12 +245,15 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
     uint32_t* rb = rowbest + (size_t)p0 * splits * n_cap * 2;
     uint32_t* cm = colmin + (size_t)p0 * n_cap;
     const int32_t* pp = pairs ? pairs + 2 * p0 : nullptr;
-    if (rq == 1)
+    {
+      ProfScope prof(0, st);
+      if (rq == 1)
       hamming_top2_kernel<1><<<grid, HM_THREADS, 0, st>>>(desc, nkp, n_cap, pp, desc2, n1d, n2d,
                                                          splits, rb, cm);
     else
       hamming_top2_kernel<4><<<grid, HM_THREADS, 0, st>>>(desc, nkp, n_cap, pp, desc2, n1d, n2d,
                                                          splits, rb, cm);
+    }
     const size_t ob = (size_t)p0 * n_cap;
     match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
         rb, cm, nkp, kp, n_cap, pp, n1d, n2d, splits, mode, ratio, q + ob, t + ob, dist + ob,

@@ -350,8 +350,11 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
     ransac_sample_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, chunk, C, w);
     ransac_solve_kernel<<<dim3((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS, n_pairs),
                           SOLVE_WARPS * 32, 0, st>>>(n_cap, it0, chunk, C, w);
-    ransac_score_kernel<<<dim3((chunk + SCORE_WARPS - 1) / SCORE_WARPS, n_pairs),
-                          SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, K, thr_px, w);
+    {
+      ProfScope prof(1, st);
+      ransac_score_kernel<<<dim3((chunk + SCORE_WARPS - 1) / SCORE_WARPS, n_pairs),
+                            SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, K, thr_px, w);
+    }
     ransac_scan_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, it0, chunk, C, conf,
                                                           adaptive, w, E);
     it0 += chunk;

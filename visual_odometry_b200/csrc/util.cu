@@ -28,3 +28,101 @@ int check_launch(const char* what) {
 
 extern "C" int vo_version(void) { return 100; }
 extern "C" const char* vo_last_error_string(void) { return vo::g_err; }
+
+// ---------------------------------------------------------------- profiling hooks
+#include <mutex>
+#include <vector>
+namespace vo {
+static bool g_prof_on = false;
+static std::mutex g_prof_mu;
+struct ProfRec { int id; cudaEvent_t e0, e1; };
+static std::vector<ProfRec> g_prof;
+
+ProfScope::ProfScope(int kernel_id, cudaStream_t stream) : id(kernel_id), st(stream) {
+  if (!g_prof_on) return;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+}
+ProfScope::~ProfScope() {
+  if (!e0) return;
+  cudaEventRecord(e1, st);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof.push_back({id, e0, e1});
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) popc_body(unsigned* out, unsigned seed, int iters) {
+  unsigned a[8], acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { a[k] = seed * (threadIdx.x + 1 + k * 977u) + blockIdx.x; acc[k] = k; }
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += __popc(a[k] ^ (acc[(k + 1) & 7]));
+  }
+  unsigned s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += acc[k];
+  if (s == 0x12345678u) out[0] = s;
+}
+}  // namespace vo
+
+extern "C" int vo_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(vo::g_prof_mu);
+  for (auto& r : vo::g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  vo::g_prof.clear();
+  vo::g_prof_on = on != 0;
+  return VO_OK;
+}
+
+extern "C" int vo_profile_read(int kernel_id, double* total_ms, int* launches) {
+  std::lock_guard<std::mutex> lk(vo::g_prof_mu);
+  double tot = 0.0;
+  int n = 0;
+  for (auto& r : vo::g_prof) {
+    if (r.id != kernel_id) continue;
+    if (cudaEventSynchronize(r.e1) != cudaSuccess) return vo::check_launch("vo_profile_read");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.e0, r.e1);
+    tot += ms;
+    ++n;
+  }
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = n;
+  return VO_OK;
+}
+
+// XOR + POPC + ADD per 32-bit word, 8 independent chains per thread: the Hamming inner body with
+// nothing else around it.  Best of 5 launches; result in popc32 per second (host pointer).
+extern "C" int vo_measure_popc_peak(double* popc32_per_s, void* stream) {
+  VO_REQUIRE(popc32_per_s, VO_ERR_INVALID_ARG, "vo_measure_popc_peak: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  unsigned* out = nullptr;
+  if (cudaMalloc(&out, 4) != cudaSuccess) return vo::check_launch("vo_measure_popc_peak");
+  const int iters = 20000;
+  dim3 grid(sms * 8), block(256);
+  vo::popc_body<1><<<grid, block, 0, st>>>(out, 3u, 10);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  double best = 1e30;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0, st);
+    vo::popc_body<1><<<grid, block, 0, st>>>(out, 3u, iters);
+    cudaEventRecord(e1, st);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  *popc32_per_s = (double)grid.x * block.x * (double)iters * 32.0 / (best * 1e-3);
+  return vo::check_launch("vo_measure_popc_peak");
+}
