@@ -49,11 +49,11 @@ const char* vo_last_error_string(void);
  */
 size_t vo_match_workspace_bytes(int n_pairs, int n_cap);
 int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
-                           const int32_t* pairs, int n_pairs, int mode, float ratio,
+                           const int32_t* pairs, int n_pairs, int mode, double ratio,
                            int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                            double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 /* single pair convenience: d1 [n1,32], d2 [n2,32]; outputs sized n1 */
-int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode, float ratio,
+int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode, double ratio,
                      int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                      int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
@@ -61,7 +61,7 @@ int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int m
  * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2). */
 size_t vo_match_l2_workspace_bytes(int n_pairs, int n_cap, int dim);
 int vo_match_l2_batch(const float* desc, const int32_t* nkp, const float* kp, int n_cap, int dim,
-                      const int32_t* pairs, int n_pairs, int mode, float ratio,
+                      const int32_t* pairs, int n_pairs, int mode, double ratio,
                       int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                       double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 

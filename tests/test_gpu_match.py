@@ -90,9 +90,9 @@ def test_batched_ragged_frames_and_gathered_points(cuda_dev):
     n_out = torch.empty(B, dtype=torch.int32, device=dev)
     wsb = lib.vo_match_workspace_bytes(B, N)
     ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    nkp_d, pairs_d = torch.from_numpy(nkp).to(dev), torch.from_numpy(pairs).to(dev)
     _lib.check(lib.vo_match_hamming_batch(
-        _lib.ptr(desc), _lib.ptr(torch.from_numpy(nkp).to(dev)), _lib.ptr(kp), N,
-        _lib.ptr(torch.from_numpy(pairs).to(dev)), B, 0, 0.0, _lib.ptr(q), _lib.ptr(t),
+        _lib.ptr(desc), _lib.ptr(nkp_d), _lib.ptr(kp), N, _lib.ptr(pairs_d), B, 0, 0.0, _lib.ptr(q), _lib.ptr(t),
         _lib.ptr(dist), None, None, _lib.ptr(pts), _lib.ptr(n_out), _lib.ptr(ws), wsb,
         _lib.cur_stream()))
     n_out = n_out.cpu().numpy()

@@ -35,11 +35,11 @@ SIGNATURES = {
     "vo_version": (_i, []),
     "vo_last_error_string": (C.c_char_p, []),
     "vo_match_workspace_bytes": (_sz, [_i, _i]),
-    "vo_match_hamming_batch": (_i, [_p, _p, _p, _i, _p, _i, _i, _f, _p, _p, _p, _p, _p, _p, _p,
+    "vo_match_hamming_batch": (_i, [_p, _p, _p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,
                                     _p, _sz, _p]),
-    "vo_match_hamming": (_i, [_p, _i, _p, _i, _i, _f, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vo_match_hamming": (_i, [_p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_match_l2_workspace_bytes": (_sz, [_i, _i, _i]),
-    "vo_match_l2_batch": (_i, [_p, _p, _p, _i, _i, _p, _i, _i, _f, _p, _p, _p, _p, _p, _p, _p,
+    "vo_match_l2_batch": (_i, [_p, _p, _p, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,
                                _p, _sz, _p]),
     "vo_essential_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_essential_ransac_batch": (_i, [_p, _p, _i, _i, _p, _d, _d, _i, _i, _p, _p, _p, _p, _p,

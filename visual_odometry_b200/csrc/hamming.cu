@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(CP_THREADS)
 match_compact_kernel(const uint32_t* __restrict__ rowbest, const uint32_t* __restrict__ colmin,
                      const int32_t* __restrict__ nkp, const float* __restrict__ kp, int n_cap,
                      const int32_t* __restrict__ pairs, int n1_direct, int n2_direct,
-                     int n_splits, int mode, float ratio, int32_t* __restrict__ q, int32_t* __restrict__ t, float* __restrict__ dist,
+                     int n_splits, int mode, double ratio, int32_t* __restrict__ q, int32_t* __restrict__ t, float* __restrict__ dist,
                      int32_t* __restrict__ t2, float* __restrict__ dist2,
                      double* __restrict__ pts, int32_t* __restrict__ n_out) {
   __shared__ int warp_tot[CP_THREADS / 32];
@@ -172,8 +172,9 @@ match_compact_kernel(const uint32_t* __restrict__ rowbest, const uint32_t* __res
       } else {
         // Lowe ratio as written in feature_detection.py:24: m.distance < ratio * n.distance
         // ratio < 0: plain nearest neighbour for every query (no test)
-        keep = ratio < 0.f ? true
-                           : (b != KEY_INF) && ((float)(a >> 16) < ratio * (float)(b >> 16));
+        // (evaluated in double like the Python expression it restates)
+        keep = ratio < 0.0 ? true
+                           : (b != KEY_INF) && ((double)(a >> 16) < ratio * (double)(b >> 16));
       }
     }
     const unsigned bal = __ballot_sync(0xffffffffu, keep);
@@ -228,7 +229,7 @@ static int pick_splits(int n_pairs, int qtiles, int n_cap) {
 
 static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, int n2d,
                           const int32_t* nkp, const float* kp, int n_cap, const int32_t* pairs,
-                          int n_pairs, int mode, float ratio, int32_t* q, int32_t* t, float* dist,
+                          int n_pairs, int mode, double ratio, int32_t* q, int32_t* t, float* dist,
                           int32_t* t2, float* dist2, double* pts, int32_t* n_out, void* ws,
                           cudaStream_t st) {
   // small batches: 128-query tiles + train splits to fill 148 SMs; big batches: 512-query tiles
@@ -265,7 +266,7 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
 
 extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp,
                                       int n_cap, const int32_t* pairs, int n_pairs, int mode,
-                                      float ratio, int32_t* q, int32_t* t, float* dist,
+                                      double ratio, int32_t* q, int32_t* t, float* dist,
                                       int32_t* t2, float* dist2, double* pts, int32_t* n_out,
                                       void* ws, size_t ws_bytes, void* stream) {
   VO_REQUIRE(desc && nkp && pairs && q && t && dist && n_out && ws, VO_ERR_INVALID_ARG,
@@ -282,7 +283,7 @@ extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, c
 }
 
 extern "C" int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode,
-                                float ratio, int32_t* q, int32_t* t, float* dist, int32_t* t2,
+                                double ratio, int32_t* q, int32_t* t, float* dist, int32_t* t2,
                                 float* dist2, int32_t* n_out, void* ws, size_t ws_bytes,
                                 void* stream) {
   VO_REQUIRE(q && t && dist && n_out && ws, VO_ERR_INVALID_ARG, "vo_match_hamming: null pointer");
