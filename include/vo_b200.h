@@ -58,10 +58,12 @@ int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int m
                      int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- K6: SIFT/L2 matching on tensor cores (BFMatcher(NORM_L2), visual_slam.py:19) ----
- * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2). */
-size_t vo_match_l2_workspace_bytes(int n_pairs, int n_cap, int dim);
+ * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2).
+ * Every frame 0..n_frames-1 is converted once (bf16 tiles + norms) and shared by its pairs.
+ * Bit-exact for integer-valued descriptors (cv2 SIFT); other data: fp32 rerank of candidates. */
+size_t vo_match_l2_workspace_bytes(int n_frames, int n_pairs, int n_cap);
 int vo_match_l2_batch(const float* desc, const int32_t* nkp, const float* kp, int n_cap, int dim,
-                      const int32_t* pairs, int n_pairs, int mode, double ratio,
+                      int n_frames, const int32_t* pairs, int n_pairs, int mode, double ratio,
                       int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                       double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 

@@ -39,7 +39,7 @@ SIGNATURES = {
                                     _p, _sz, _p]),
     "vo_match_hamming": (_i, [_p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_match_l2_workspace_bytes": (_sz, [_i, _i, _i]),
-    "vo_match_l2_batch": (_i, [_p, _p, _p, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,
+    "vo_match_l2_batch": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,
                                _p, _sz, _p]),
     "vo_essential_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_essential_ransac_batch": (_i, [_p, _p, _i, _i, _p, _d, _d, _i, _i, _p, _p, _p, _p, _p,

@@ -2,7 +2,5 @@
 // Each returns VO_ERR_INVALID_ARG with a clear message (never a silent CPU path).
 #include "common.cuh"
 #define NOT_YET(name) vo::set_error(name ": not implemented yet"); return VO_ERR_INVALID_ARG;
-extern "C" size_t vo_match_l2_workspace_bytes(int, int, int) { return 0; }
-extern "C" int vo_match_l2_batch(const float*, const int32_t*, const float*, int, int, const int32_t*, int, int, double, int32_t*, int32_t*, float*, int32_t*, float*, double*, int32_t*, void*, size_t, void*) { NOT_YET("vo_match_l2_batch") }
 extern "C" size_t vo_pnp_workspace_bytes(int, int) { return 0; }
 extern "C" int vo_pnp_ransac(const double*, const double*, int, const double*, int, double, double, double*, double*, int32_t*, int32_t*, int32_t*, void*, size_t, void*) { NOT_YET("vo_pnp_ransac") }

@@ -59,7 +59,7 @@ class PairPipeline:
         if descriptor == "orb":
             self.ws_match = e(max(self.lib.vo_match_workspace_bytes(P, N), 256), dt=U8)
         else:
-            self.ws_match = e(max(self.lib.vo_match_l2_workspace_bytes(P, N, self.D), 256), dt=U8)
+            self.ws_match = e(max(self.lib.vo_match_l2_workspace_bytes(F, P, N), 256), dt=U8)
         self.ws_ess = e(max(self.lib.vo_essential_workspace_bytes(P, N, self.max_iters), 256), dt=U8)
         self.ws_pose = e(max(self.lib.vo_pose_workspace_bytes(P, N), 256), dt=U8)
         # pinned staging for run_host
@@ -80,7 +80,7 @@ class PairPipeline:
                 p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
         else:
             _lib.check(lib.vo_match_l2_batch(
-                p(self.desc), p(self.nkp), p(self.kp), N, self.D, p(self.pairs), B,
+                p(self.desc), p(self.nkp), p(self.kp), N, self.D, self.F, p(self.pairs), B,
                 self.match_mode, self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None,
                 p(self.pts), p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
         _lib.check(lib.vo_essential_ransac_batch(
