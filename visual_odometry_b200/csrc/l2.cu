@@ -25,12 +25,18 @@ namespace vo {
 
 constexpr int L2_DIM = 128;
 constexpr int L2_BLK = 128;                       // rows per tile (UMMA M and N)
-constexpr int L2_TILE_ELEMS = L2_BLK * L2_DIM;    // 16384 bf16 = 32 KB
+// a tile = 20 K-groups (kg) of 8 bf16 columns x 128 rows: kg 0..15 the descriptor, kg 16 = [1,1,1,0..]
+// (A-side extras), kg 17 = 0, kg 18 = -|b|^2/2 split into three bf16 (B-side extras), kg 19 = 0.
+// A ninth K=16 MMA step over (kg16,kg17) x (kg18,kg19) adds -|b_j|^2/2 to the accumulator, so the
+// epilogue ranks  a.b - |b|^2/2  directly: no norm loads, no FMA per element.
+constexpr int L2_KG = 20;
+constexpr int L2_TILE_ELEMS = L2_BLK * 8 * L2_KG;  // 20480 bf16 = 40 KB
 constexpr int L2_TILE_BYTES = L2_TILE_ELEMS * 2;
 constexpr uint32_t L2_LBO = 2048;                 // between the two K core matrices of a K=16 slice
 constexpr uint32_t L2_SBO = 128;                  // between 8-row groups
 constexpr int L2_NSTAGE = 3;
-constexpr int L2_THREADS = 192;
+constexpr int L2_EPI_WARPS = 16;  // 4 per TMEM lane quarter, 32 columns each
+constexpr int L2_THREADS = (L2_EPI_WARPS + 2) * 32;  // + MMA warp + TMA warp
 
 struct L2Ws {
   __nv_bfloat16* tiles;   // [F][nblk][16384]
@@ -89,25 +95,57 @@ l2_prep_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, 
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     if (lane == 0)
       w.norms[((size_t)f * nblk + blk) * L2_BLK + rl] = (r < n) ? ss : __int_as_float(0x7f800000);
+    if (lane < 4) {  // the four extra K-groups of this row (16 bytes each)
+      uint4 e = make_uint4(0, 0, 0, 0);
+      if (lane == 0) {
+        e.x = 0x3f803f80u;  // bf16 (1, 1)
+        e.y = 0x00003f80u;  // bf16 (1, 0)
+      } else if (lane == 2) {
+        __nv_bfloat16 h, m, l;
+        if (r < n) {
+          const float x = -0.5f * ss;
+          h = __float2bfloat16_rn(x);
+          const float r1 = x - __bfloat162float(h);
+          m = __float2bfloat16_rn(r1);
+          l = __float2bfloat16_rn(r1 - __bfloat162float(m));
+        } else {
+          h = __float2bfloat16_rn(__int_as_float(0xff800000));  // -inf: padded column never wins
+          m = l = __float2bfloat16_rn(0.f);
+        }
+        e.x = (uint32_t)__bfloat16_as_ushort(h) | ((uint32_t)__bfloat16_as_ushort(m) << 16);
+        e.y = (uint32_t)__bfloat16_as_ushort(l);
+      }
+      *reinterpret_cast<uint4*>(reinterpret_cast<char*>(tile) + (size_t)(16 + lane) * 2048 +
+                                (size_t)(rl >> 3) * 128 + (rl & 7) * 16) = e;
+    }
   }
   if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(w.inexact, 1);
 }
 
 // ------------------------------------------------------------------ tensor-core top-2
+// bit 0: producer loads each stage only once (no per-tile TMA); bit 1: epilogue skips the scan;
+// bit 2: epilogue skips the TMEM load too.  Diagnostics only (results are wrong when set).
+__device__ int g_l2_debug = 0;
+
 struct __align__(1024) L2Smem {
   uint8_t A[L2_TILE_BYTES];
   uint8_t B[L2_NSTAGE][L2_TILE_BYTES];
+  float4 part[3][L2_BLK];  // top-2 of column quarters 1..3 of each row, merged by quarter 0
   uint64_t full_a;
   uint64_t full_b[L2_NSTAGE], empty_b[L2_NSTAGE];
   uint64_t tmem_full[2], tmem_empty[2];
   uint32_t tmem_base;
 };
 
+// running top-2 of the LARGEST scores; ties keep the earlier (lower) column
 __device__ __forceinline__ void top2_insert(float s, int c, float& s1, int& i1, float& s2, int& i2) {
-  if (s < s1) { s2 = s1; i2 = i1; s1 = s; i1 = c; }
+  if (s > s1) { s2 = s1; i2 = i1; s1 = s; i1 = c; }
   else { s2 = s; i2 = c; }
 }
 
+// TOP2 = false: cross-check matching needs only the nearest neighbour of every row (in both
+// directions), which halves the number of threshold hits and shortens the hit path.
+template <bool TOP2>
 __global__ void __launch_bounds__(L2_THREADS, 1)
 l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ pairs, int nblk,
                   int n_splits, L2Ws w) {
@@ -127,30 +165,33 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
   if (threadIdx.x == 0) {
     mbar_init(&S.full_a, 1);
     for (int s = 0; s < L2_NSTAGE; ++s) { mbar_init(&S.full_b[s], 1); mbar_init(&S.empty_b[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&S.tmem_full[s], 1); mbar_init(&S.tmem_empty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&S.tmem_full[s], 1); mbar_init(&S.tmem_empty[s], L2_EPI_WARPS); }
     fence_barrier_init();
   }
-  if (warp == 4) tc::tmem_alloc(&S.tmem_base, 256);
+  if (warp == L2_EPI_WARPS) tc::tmem_alloc(&S.tmem_base, 256);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = S.tmem_base;
+  const float NEG_INF = __int_as_float(0xff800000);
+  const int dbg = g_l2_debug;
 
-  if (warp == 5) {
-    // ===== TMA producer: one 32 KB bulk copy per tile =====
+  if (warp == L2_EPI_WARPS + 1) {
+    // ===== TMA producer: one 40 KB bulk copy per tile =====
     if (lane == 0 && ntile > 0) {
       mbar_expect_tx(&S.full_a, L2_TILE_BYTES);
       bulk_g2s(S.A, w.tiles + ((size_t)fq * nblk + rb) * L2_TILE_ELEMS, L2_TILE_BYTES, &S.full_a);
       for (int t = 0; t < ntile; ++t) {
         const int st = t % L2_NSTAGE;
         mbar_wait(&S.empty_b[st], ((t / L2_NSTAGE) & 1) ^ 1);
+        if ((dbg & 1) && t >= L2_NSTAGE) { tc::mbar_arrive(&S.full_b[st]); continue; }
         mbar_expect_tx(&S.full_b[st], L2_TILE_BYTES);
         bulk_g2s(S.B[st], w.tiles + ((size_t)ft * nblk + t_lo + t) * L2_TILE_ELEMS, L2_TILE_BYTES,
                  &S.full_b[st]);
       }
     }
-  } else if (warp == 4) {
-    // ===== MMA issuer: one thread, 8 x (128x128x16) per tile, accumulator double-buffered =====
+  } else if (warp == L2_EPI_WARPS) {
+    // ===== MMA issuer: one thread, 9 x (128x128x16) per tile, accumulator double-buffered =====
     if (lane == 0 && ntile > 0) {
       const uint32_t idesc = tc::idesc_bf16_f32(L2_BLK, L2_BLK);
       mbar_wait(&S.full_a, 0);
@@ -162,60 +203,101 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
         tc::fence_after_sync();
         const uint32_t b_addr = smem_u32(S.B[st]);
 #pragma unroll
-        for (int k = 0; k < L2_DIM / 16; ++k) {
-          const uint64_t ad = tc::smem_desc(a_addr + k * 2 * L2_LBO, L2_LBO, L2_SBO);
-          const uint64_t bd = tc::smem_desc(b_addr + k * 2 * L2_LBO, L2_LBO, L2_SBO);
-          tc::mma_bf16(tmem + as * L2_BLK, ad, bd, idesc, k > 0);
+        for (int k = 0; k < 9; ++k) {
+          // steps 0..7: descriptor columns; step 8: A extras (kg16,17) x B extras (kg18,19)
+          const uint32_t ao = (k < 8) ? k * 2 * L2_LBO : 16 * L2_LBO;
+          const uint32_t bo = (k < 8) ? k * 2 * L2_LBO : 18 * L2_LBO;
+          tc::mma_bf16(tmem + as * L2_BLK, tc::smem_desc(a_addr + ao, L2_LBO, L2_SBO),
+                       tc::smem_desc(b_addr + bo, L2_LBO, L2_SBO), idesc, k > 0);
         }
         tc::commit(&S.empty_b[st]);     // smem stage reusable once these MMAs retire
         tc::commit(&S.tmem_full[as]);   // accumulator ready for the epilogue
       }
     }
   } else {
-    // ===== epilogue warps 0..3: thread = TMEM lane = query row; running top-2 over columns =====
-    const int row = rb * L2_BLK + warp * 32 + lane;
-    float s1 = __int_as_float(0x7f800000), s2 = s1;
+    // ===== epilogue warps 0..7: thread = TMEM lane = query row, warp/4 = column half ==========
+    // running top-2 of  a.b - |b|^2/2  (largest = nearest), 64 columns per TMEM load
+    const int quarter = warp & 3, cq = warp >> 2;   // TMEM lane quarter, column quarter
+    const int rl = quarter * 32 + lane;
+    const int row = rb * L2_BLK + rl;
+    float s1 = NEG_INF, s2 = NEG_INF;
     int i1 = -1, i2 = -1;
-    const float* nbase = w.norms + (size_t)ft * nblk * L2_BLK;
     for (int t = 0; t < ntile; ++t) {
       const int as = t & 1;
       mbar_wait(&S.tmem_full[as], (t >> 1) & 1);
       tc::fence_after_sync();
-      const int c0 = (t_lo + t) * L2_BLK;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        float v[32];
-        tc::ld_32x32(tmem + ((uint32_t)(warp * 32) << 16) + as * L2_BLK + ch * 32, v);
-        const float4* nb4 = reinterpret_cast<const float4*>(nbase + c0 + ch * 32);
+      const int c0 = (t_lo + t) * L2_BLK + cq * 32;
+      float v[32];
+      if (dbg & 4) {
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const float4 nb = __ldg(nb4 + g);
-          const float e0 = fmaf(v[4 * g + 0], -2.f, nb.x), e1 = fmaf(v[4 * g + 1], -2.f, nb.y);
-          const float e2 = fmaf(v[4 * g + 2], -2.f, nb.z), e3 = fmaf(v[4 * g + 3], -2.f, nb.w);
-          const int c = c0 + ch * 32 + 4 * g;
-          if (e0 < s2) top2_insert(e0, c + 0, s1, i1, s2, i2);
-          if (e1 < s2) top2_insert(e1, c + 1, s1, i1, s2, i2);
-          if (e2 < s2) top2_insert(e2, c + 2, s1, i1, s2, i2);
-          if (e3 < s2) top2_insert(e3, c + 3, s1, i1, s2, i2);
-        }
+        for (int c = 0; c < 32; ++c) v[c] = NEG_INF;
+      } else {
+        tc::ld_32x32(tmem + ((uint32_t)(quarter * 32) << 16) + as * L2_BLK + cq * 32, v);
       }
       tc::fence_before_sync();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);
+      if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);   // values are in registers now
+      if (dbg & 2) continue;
+      // group-of-8 prefilter (7 FMNMX + 1 branch).  With 32 independent rows per warp some lane
+      // almost always hits, so the hit path is kept short: locate the first occurrence of the
+      // group maximum, insert it, knock it out, re-test (a second hit in one group is rare).
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float* x = &v[8 * g];
+        float m = fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])),
+                        fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7])));
+        if (TOP2) {
+          while (m > s2) {
+            int pos = 7;
+#pragma unroll
+            for (int k = 6; k >= 0; --k) pos = (x[k] == m) ? k : pos;
+            top2_insert(m, c0 + 8 * g + pos, s1, i1, s2, i2);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = (k == pos) ? NEG_INF : x[k];
+            m = fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])),
+                      fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7])));
+          }
+        } else if (m > s1) {
+          int pos = 7;
+#pragma unroll
+          for (int k = 6; k >= 0; --k) pos = (x[k] == m) ? k : pos;
+          s1 = m;
+          i1 = c0 + 8 * g + pos;
+        }
+      }
     }
-    if (row < nq) {
-      const float na = w.norms[(size_t)fq * nblk * L2_BLK + row];
-      float4 o;
-      o.x = fmaxf(na + s1, 0.f); o.y = __int_as_float(i1);
-      o.z = fmaxf(na + s2, 0.f); o.w = __int_as_float(i2);
-      if (i1 < 0) o.x = __int_as_float(0x7f800000);
-      if (i2 < 0) o.z = __int_as_float(0x7f800000);
-      w.rowbest[(((size_t)pair * 2 + dir) * n_splits + split) * nblk * L2_BLK + row] = o;
+    if (cq > 0) S.part[cq - 1][rl] = make_float4(s1, __int_as_float(i1), s2, __int_as_float(i2));
+    asm volatile("bar.sync 1, 512;" ::: "memory");   // the 16 epilogue warps only
+    if (cq == 0) {
+      // merge the other column quarters; equal scores keep the lower column index
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        const float4 o = S.part[p][rl];
+        const int a = __float_as_int(o.y), b = __float_as_int(o.w);
+        if (a >= 0 && (o.x > s2 || (o.x == s2 && (i2 < 0 || a < i2)))) {
+          if (o.x > s1 || (o.x == s1 && (i1 < 0 || a < i1))) { s2 = s1; i2 = i1; s1 = o.x; i1 = a; }
+          else { s2 = o.x; i2 = a; }
+        }
+        if (b >= 0 && (o.z > s2 || (o.z == s2 && (i2 < 0 || b < i2)))) {
+          if (o.z > s1 || (o.z == s1 && (i1 < 0 || b < i1))) { s2 = s1; i2 = i1; s1 = o.z; i1 = b; }
+          else { s2 = o.z; i2 = b; }
+        }
+      }
+      if (row < nq) {
+        // d^2 = |a|^2 - 2 (a.b - |b|^2/2); exact for integer descriptors
+        const float na = w.norms[(size_t)fq * nblk * L2_BLK + row];
+        float4 r;
+        r.x = i1 >= 0 ? fmaxf(fmaf(-2.f, s1, na), 0.f) : __int_as_float(0x7f800000);
+        r.y = __int_as_float(i1);
+        r.z = i2 >= 0 ? fmaxf(fmaf(-2.f, s2, na), 0.f) : __int_as_float(0x7f800000);
+        r.w = __int_as_float(i2);
+        w.rowbest[(((size_t)pair * 2 + dir) * n_splits + split) * nblk * L2_BLK + row] = r;
+      }
     }
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 4) tc::tmem_dealloc(tmem, 256);
+  if (warp == L2_EPI_WARPS) tc::tmem_dealloc(tmem, 256);
 }
 
 // ------------------------------------------------------------------ fp32 rerank (non-integer data)
@@ -350,6 +432,10 @@ static int l2_pick_splits(int n_pairs, int nblk) {
   return s < 1 ? 1 : s;
 }
 
+extern "C" int vo_debug_l2(int flags) {
+  return cudaMemcpyToSymbol(g_l2_debug, &flags, sizeof(int)) == cudaSuccess ? VO_OK : VO_ERR_CUDA;
+}
+
 extern "C" size_t vo_match_l2_workspace_bytes(int n_frames, int n_pairs, int n_cap) {
   if (n_frames <= 0 || n_pairs <= 0 || n_cap <= 0) return 0;
   return l2_carve(nullptr, n_frames, n_pairs, n_cap, 8).bytes;
@@ -379,15 +465,20 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   static bool attr_set = false;
   const int smem = (int)sizeof(L2Smem) + 1024;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(l2_top2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
-        cudaSuccess)
+    if (cudaFuncSetAttribute(l2_top2_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             smem) != cudaSuccess ||
+        cudaFuncSetAttribute(l2_top2_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             smem) != cudaSuccess)
       return check_launch("vo_match_l2_batch(smem attribute)");
     attr_set = true;
   }
   {
     ProfScope prof(2, st);
-    l2_top2_tc_kernel<<<dim3(nblk, n_pairs * 2, splits), L2_THREADS, smem, st>>>(nkp, pairs, nblk,
-                                                                               splits, w);
+    const dim3 grid(nblk, n_pairs * 2, splits);
+    if (mode == VO_MATCH_MUTUAL)
+      l2_top2_tc_kernel<false><<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, w);
+    else
+      l2_top2_tc_kernel<true><<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, w);
   }
   l2_rerank_kernel<<<dim3((n_cap + 7) / 8, n_pairs * 2), 256, 0, st>>>(desc, nkp, n_cap, pairs, nblk,
                                                                      splits, w);
