@@ -103,7 +103,7 @@ def test_pipeline_sequence_vs_reference_path_and_ground_truth(cuda_dev):
             n = int(pipe.n_x[b])
             X = pipe.X[b, :n].cpu().numpy().T
             rel = np.abs(X - ref["X"]).max(0) / np.abs(ref["X"]).max(0)
-            assert np.median(rel) < 1e-6 and (rel < X_TOL).mean() > 0.99
+            assert np.median(rel) < X_TOL / 4 and (rel < X_TOL).mean() > 0.99
         Rg, tg = seq.relative_pose(b, b + 1)
         assert rot_angle(out["R"][b], Rg) < 0.02          # and close to ground truth
         Rs.append(ref["R"]); ts.append(ref["tvec"])
