@@ -1,0 +1,680 @@
+// pnp.cu — K7: PnP-RANSAC for map tracking.
+//
+// Replaces cv2.solvePnPRansac(X, x, K, zeros(4)) with default arguments (reference
+// src/visual_slam.py:231-235): points converted to float32, RANSAC over 5-point samples replayed
+// from cv::RNG(2^64-1), EPnP minimal solver (OpenCV epnp.cpp), error = float32 squared
+// reprojection distance vs 8 px, 100 iterations with the adaptive bound, strict-greater best
+// update; then the SOLVEPNP_ITERATIVE refit (Levenberg-Marquardt on the reprojection error from
+// the RANSAC model) on the inliers.  Returned inliers = those of the RANSAC model.
+//
+// GPU shape: all hypotheses of a problem are solved in parallel (one thread per EPnP solve —
+// 12x12 Jacobi eigen-decomposition in local memory), scored in parallel (one warp per
+// hypothesis, coalesced point reads), then OpenCV's sequential rule is applied as an ordered
+// scan; the refit accumulates the 6x6 normal equations with a block reduction per iteration.
+#include <float.h>
+
+#include "linalg.cuh"
+
+namespace vo {
+
+constexpr int PNP_MAX_ITERS = 1024;
+
+struct PnpWs {
+  double* Xf;         // [n][3] float32-rounded object points
+  double* xf;         // [n][2] float32-rounded image points
+  double* models;     // [iters][12]  R (9) + t (3)
+  int32_t* samples;   // [iters][5]
+  int32_t* counts;    // [iters]
+  int32_t* valid;     // [iters]
+  int32_t* best;      // [4] best index, niters, max_good, n_inl
+  uint8_t* mask;      // [n]
+  size_t bytes;
+};
+
+static PnpWs pnp_carve(void* base, int n, int iters) {
+  PnpWs w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (char*)base + off : nullptr;
+    off += (bytes + 255) & ~(size_t)255;
+    return p;
+  };
+  w.Xf = (double*)take((size_t)n * 3 * sizeof(double));
+  w.xf = (double*)take((size_t)n * 2 * sizeof(double));
+  w.models = (double*)take((size_t)iters * 12 * sizeof(double));
+  w.samples = (int32_t*)take((size_t)iters * 5 * sizeof(int32_t));
+  w.counts = (int32_t*)take((size_t)iters * sizeof(int32_t));
+  w.valid = (int32_t*)take((size_t)iters * sizeof(int32_t));
+  w.best = (int32_t*)take(4 * sizeof(int32_t));
+  w.mask = (uint8_t*)take((size_t)n);
+  w.bytes = off;
+  return w;
+}
+
+// ------------------------------------------------------------------ small dense helpers (runtime sizes)
+// cyclic Jacobi eigen-decomposition of a symmetric n x n matrix (row-major, destroyed);
+// V columns = eigenvectors, d = eigenvalues (unsorted)
+__device__ void jacobi_eigen(double* A, double* V, double* d, int n) {
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) V[i * n + j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < n; ++i) {
+      diag += A[i * n + i] * A[i * n + i];
+      for (int j = i + 1; j < n; ++j) off += A[i * n + j] * A[i * n + j];
+    }
+    if (off <= 1e-30 * diag || off == 0.0) break;
+    for (int p = 0; p < n - 1; ++p)
+      for (int q = p + 1; q < n; ++q) {
+        const double apq = A[p * n + q];
+        if (fabs(apq) < 1e-300) continue;
+        const double theta = (A[q * n + q] - A[p * n + p]) / (2.0 * apq);
+        const double t = copysign(1.0, theta) / (fabs(theta) + sqrt(1.0 + theta * theta));
+        const double c = rsqrt(1.0 + t * t), s = c * t;
+        for (int k = 0; k < n; ++k) {  // columns p,q
+          const double akp = A[k * n + p], akq = A[k * n + q];
+          A[k * n + p] = c * akp - s * akq;
+          A[k * n + q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < n; ++k) {  // rows p,q
+          const double apk = A[p * n + k], aqk = A[q * n + k];
+          A[p * n + k] = c * apk - s * aqk;
+          A[q * n + k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < n; ++k) {
+          const double vkp = V[k * n + p], vkq = V[k * n + q];
+          V[k * n + p] = c * vkp - s * vkq;
+          V[k * n + q] = s * vkp + c * vkq;
+        }
+      }
+  }
+  for (int i = 0; i < n; ++i) d[i] = A[i * n + i];
+}
+
+// least squares min |A x - b| for m x n (m >= n, n <= 5) by Householder QR (A, b destroyed)
+__device__ bool ls_solve(double* A, double* b, double* x, int m, int n) {
+  for (int k = 0; k < n; ++k) {
+    double nrm = 0.0;
+    for (int i = k; i < m; ++i) nrm += A[i * n + k] * A[i * n + k];
+    nrm = sqrt(nrm);
+    if (!(nrm > 0.0)) return false;
+    const double alpha = A[k * n + k] >= 0 ? -nrm : nrm;
+    const double v0 = A[k * n + k] - alpha;
+    double vtv = v0 * v0;
+    for (int i = k + 1; i < m; ++i) vtv += A[i * n + k] * A[i * n + k];
+    if (vtv > 0.0) {
+      for (int j = k + 1; j < n; ++j) {
+        double dot = v0 * A[k * n + j];
+        for (int i = k + 1; i < m; ++i) dot += A[i * n + k] * A[i * n + j];
+        const double f = 2.0 * dot / vtv;
+        A[k * n + j] -= f * v0;
+        for (int i = k + 1; i < m; ++i) A[i * n + j] -= f * A[i * n + k];
+      }
+      double dot = v0 * b[k];
+      for (int i = k + 1; i < m; ++i) dot += A[i * n + k] * b[i];
+      const double f = 2.0 * dot / vtv;
+      b[k] -= f * v0;
+      for (int i = k + 1; i < m; ++i) b[i] -= f * A[i * n + k];
+    }
+    A[k * n + k] = alpha;
+  }
+  for (int k = n - 1; k >= 0; --k) {
+    double s = b[k];
+    for (int j = k + 1; j < n; ++j) s -= A[k * n + j] * x[j];
+    x[k] = s / A[k * n + k];
+  }
+  return true;
+}
+
+// ------------------------------------------------------------------ EPnP on a 5-point sample
+struct Epnp5 {
+  double X[5][3], u[5][2];
+  double cws[4][3], alphas[5][4];
+  double MtM[144], V[144], ev[12];
+  double L[6][10], rho[6];
+  int vi[4];   // eigenvector columns of the 4 smallest eigenvalues, ascending
+};
+
+__device__ double epnp_R_and_t(const Epnp5& E, const double* betas, double fu, double fv, double uc,
+                               double vc, double* R, double* t) {
+  double ccs[4][3], pcs[5][3];
+  for (int i = 0; i < 4; ++i)
+    for (int k = 0; k < 3; ++k) {
+      double s = 0.0;
+      for (int j = 0; j < 4; ++j) s += betas[j] * E.V[(3 * i + k) * 12 + E.vi[j]];
+      ccs[i][k] = s;
+    }
+  for (int p = 0; p < 5; ++p)
+    for (int k = 0; k < 3; ++k)
+      pcs[p][k] = E.alphas[p][0] * ccs[0][k] + E.alphas[p][1] * ccs[1][k] +
+                  E.alphas[p][2] * ccs[2][k] + E.alphas[p][3] * ccs[3][k];
+  if (pcs[0][2] < 0.0)
+    for (int p = 0; p < 5; ++p)
+      for (int k = 0; k < 3; ++k) pcs[p][k] = -pcs[p][k];
+  double pc0[3] = {0, 0, 0}, pw0[3] = {0, 0, 0};
+  for (int p = 0; p < 5; ++p)
+    for (int k = 0; k < 3; ++k) { pc0[k] += pcs[p][k]; pw0[k] += E.X[p][k]; }
+  for (int k = 0; k < 3; ++k) { pc0[k] /= 5.0; pw0[k] /= 5.0; }
+  double A[3][3], Vv[3][3];
+  for (int j = 0; j < 3; ++j)
+    for (int k = 0; k < 3; ++k) {
+      double s = 0.0;
+      for (int p = 0; p < 5; ++p) s += (pcs[p][j] - pc0[j]) * (E.X[p][k] - pw0[k]);
+      A[j][k] = s;
+    }
+  // R = U V^T from ABt = U S V^T (one-sided Jacobi: A <- U S, Vv = V)
+  jacobi_svd<3>(A, Vv);
+  double sg[3];
+  int o[3] = {0, 1, 2};
+  for (int j = 0; j < 3; ++j) sg[j] = sqrt(A[0][j] * A[0][j] + A[1][j] * A[1][j] + A[2][j] * A[2][j]);
+  if (sg[o[0]] < sg[o[1]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  if (sg[o[1]] < sg[o[2]]) { int x = o[1]; o[1] = o[2]; o[2] = x; }
+  if (sg[o[0]] < sg[o[1]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  double U[3][3];
+  for (int k = 0; k < 3; ++k) {
+    U[k][0] = A[k][o[0]] / sg[o[0]];
+    U[k][1] = A[k][o[1]] / sg[o[1]];
+  }
+  U[0][2] = U[1][0] * U[2][1] - U[2][0] * U[1][1];
+  U[1][2] = U[2][0] * U[0][1] - U[0][0] * U[2][1];
+  U[2][2] = U[0][0] * U[1][1] - U[1][0] * U[0][1];
+  double W[3][3];
+  for (int k = 0; k < 3; ++k) { W[k][0] = Vv[k][o[0]]; W[k][1] = Vv[k][o[1]]; }
+  W[0][2] = W[1][0] * W[2][1] - W[2][0] * W[1][1];
+  W[1][2] = W[2][0] * W[0][1] - W[0][0] * W[2][1];
+  W[2][2] = W[0][0] * W[1][1] - W[1][0] * W[0][1];
+  // both completed bases are right-handed, so det(U W^T) = +1 (OpenCV flips the last row of R
+  // when det < 0, which yields the same proper rotation)
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) R[3 * i + j] = U[i][0] * W[j][0] + U[i][1] * W[j][1] + U[i][2] * W[j][2];
+  for (int i = 0; i < 3; ++i) t[i] = pc0[i] - (R[3 * i] * pw0[0] + R[3 * i + 1] * pw0[1] + R[3 * i + 2] * pw0[2]);
+  double err = 0.0;
+  for (int p = 0; p < 5; ++p) {
+    const double xc = R[0] * E.X[p][0] + R[1] * E.X[p][1] + R[2] * E.X[p][2] + t[0];
+    const double yc = R[3] * E.X[p][0] + R[4] * E.X[p][1] + R[5] * E.X[p][2] + t[1];
+    const double inv = 1.0 / (R[6] * E.X[p][0] + R[7] * E.X[p][1] + R[8] * E.X[p][2] + t[2]);
+    const double du = E.u[p][0] - (uc + fu * xc * inv), dv = E.u[p][1] - (vc + fv * yc * inv);
+    err += sqrt(du * du + dv * dv);
+  }
+  return err / 5.0;
+}
+
+__device__ void epnp_gauss_newton(const Epnp5& E, double* b) {
+  for (int it = 0; it < 5; ++it) {
+    double A[24], r[6], x[4];
+    for (int i = 0; i < 6; ++i) {
+      const double* Lr = E.L[i];
+      A[4 * i + 0] = 2 * Lr[0] * b[0] + Lr[1] * b[1] + Lr[3] * b[2] + Lr[6] * b[3];
+      A[4 * i + 1] = Lr[1] * b[0] + 2 * Lr[2] * b[1] + Lr[4] * b[2] + Lr[7] * b[3];
+      A[4 * i + 2] = Lr[3] * b[0] + Lr[4] * b[1] + 2 * Lr[5] * b[2] + Lr[8] * b[3];
+      A[4 * i + 3] = Lr[6] * b[0] + Lr[7] * b[1] + Lr[8] * b[2] + 2 * Lr[9] * b[3];
+      r[i] = E.rho[i] - (Lr[0] * b[0] * b[0] + Lr[1] * b[0] * b[1] + Lr[2] * b[1] * b[1] +
+                         Lr[3] * b[0] * b[2] + Lr[4] * b[1] * b[2] + Lr[5] * b[2] * b[2] +
+                         Lr[6] * b[0] * b[3] + Lr[7] * b[1] * b[3] + Lr[8] * b[2] * b[3] +
+                         Lr[9] * b[3] * b[3]);
+    }
+    if (!ls_solve(A, r, x, 6, 4)) return;
+    for (int k = 0; k < 4; ++k) b[k] += x[k];
+  }
+}
+
+// full EPnP (epnp.cpp compute_pose) for 5 points; returns false on numerical failure
+__device__ bool epnp5(Epnp5& E, const double* K, double* R, double* t) {
+  const double fu = K[0], fv = K[4], uc = K[2], vc = K[5];
+  // control points: centroid + principal axes scaled by sqrt(lambda / n)
+  double c0[3] = {0, 0, 0};
+  for (int p = 0; p < 5; ++p)
+    for (int k = 0; k < 3; ++k) c0[k] += E.X[p][k];
+  for (int k = 0; k < 3; ++k) c0[k] /= 5.0;
+  double C[9], CV[9], cd[3];
+  for (int j = 0; j < 3; ++j)
+    for (int k = 0; k < 3; ++k) {
+      double s = 0.0;
+      for (int p = 0; p < 5; ++p) s += (E.X[p][j] - c0[j]) * (E.X[p][k] - c0[k]);
+      C[3 * j + k] = s;
+    }
+  jacobi_eigen(C, CV, cd, 3);
+  int o[3] = {0, 1, 2};
+  if (cd[o[0]] < cd[o[1]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  if (cd[o[1]] < cd[o[2]]) { int x = o[1]; o[1] = o[2]; o[2] = x; }
+  if (cd[o[0]] < cd[o[1]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  for (int k = 0; k < 3; ++k) E.cws[0][k] = c0[k];
+  for (int i = 1; i < 4; ++i) {
+    const double kk = sqrt(fmax(cd[o[i - 1]], 0.0) / 5.0);
+    for (int k = 0; k < 3; ++k) E.cws[i][k] = c0[k] + kk * CV[k * 3 + o[i - 1]];
+  }
+  // barycentric coordinates: CC = [c1-c0 c2-c0 c3-c0] (columns); alphas[1..3] = CC^-1 (p - c0)
+  double CC[9], CI[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) CC[3 * i + j] = E.cws[j + 1][i] - E.cws[0][i];
+  const double det = det3(CC);
+  if (!(fabs(det) > 1e-300) || !isfinite(det)) return false;
+  CI[0] = (CC[4] * CC[8] - CC[5] * CC[7]) / det; CI[1] = (CC[2] * CC[7] - CC[1] * CC[8]) / det;
+  CI[2] = (CC[1] * CC[5] - CC[2] * CC[4]) / det; CI[3] = (CC[5] * CC[6] - CC[3] * CC[8]) / det;
+  CI[4] = (CC[0] * CC[8] - CC[2] * CC[6]) / det; CI[5] = (CC[2] * CC[3] - CC[0] * CC[5]) / det;
+  CI[6] = (CC[3] * CC[7] - CC[4] * CC[6]) / det; CI[7] = (CC[1] * CC[6] - CC[0] * CC[7]) / det;
+  CI[8] = (CC[0] * CC[4] - CC[1] * CC[3]) / det;
+  for (int p = 0; p < 5; ++p) {
+    const double d0 = E.X[p][0] - c0[0], d1 = E.X[p][1] - c0[1], d2 = E.X[p][2] - c0[2];
+    for (int j = 0; j < 3; ++j) E.alphas[p][1 + j] = CI[3 * j] * d0 + CI[3 * j + 1] * d1 + CI[3 * j + 2] * d2;
+    E.alphas[p][0] = 1.0 - E.alphas[p][1] - E.alphas[p][2] - E.alphas[p][3];
+  }
+  // M^T M (12x12) accumulated row by row
+  for (int e = 0; e < 144; ++e) E.MtM[e] = 0.0;
+  for (int p = 0; p < 5; ++p) {
+    double m1[12], m2[12];
+    for (int j = 0; j < 4; ++j) {
+      const double a = E.alphas[p][j];
+      m1[3 * j] = a * fu; m1[3 * j + 1] = 0.0; m1[3 * j + 2] = a * (uc - E.u[p][0]);
+      m2[3 * j] = 0.0; m2[3 * j + 1] = a * fv; m2[3 * j + 2] = a * (vc - E.u[p][1]);
+    }
+    for (int i = 0; i < 12; ++i)
+      for (int j = 0; j < 12; ++j) E.MtM[12 * i + j] += m1[i] * m1[j] + m2[i] * m2[j];
+  }
+  jacobi_eigen(E.MtM, E.V, E.ev, 12);
+  {  // four smallest eigenvalues, ascending (selection)
+    bool used[12];
+    for (int i = 0; i < 12; ++i) used[i] = false;
+    for (int k = 0; k < 4; ++k) {
+      int bi = -1;
+      for (int i = 0; i < 12; ++i)
+        if (!used[i] && (bi < 0 || E.ev[i] < E.ev[bi])) bi = i;
+      used[bi] = true;
+      E.vi[k] = bi;
+    }
+  }
+  // L (6x10) and rho
+  const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
+  for (int i = 0; i < 6; ++i) {
+    double dv[4][3];
+    for (int k = 0; k < 4; ++k)
+      for (int c = 0; c < 3; ++c)
+        dv[k][c] = E.V[(3 * pa[i] + c) * 12 + E.vi[k]] - E.V[(3 * pb[i] + c) * 12 + E.vi[k]];
+    auto dot = [&](int a, int b) { return dv[a][0] * dv[b][0] + dv[a][1] * dv[b][1] + dv[a][2] * dv[b][2]; };
+    double* Lr = E.L[i];
+    Lr[0] = dot(0, 0); Lr[1] = 2 * dot(0, 1); Lr[2] = dot(1, 1); Lr[3] = 2 * dot(0, 2);
+    Lr[4] = 2 * dot(1, 2); Lr[5] = dot(2, 2); Lr[6] = 2 * dot(0, 3); Lr[7] = 2 * dot(1, 3);
+    Lr[8] = 2 * dot(2, 3); Lr[9] = dot(3, 3);
+    double s = 0.0;
+    for (int c = 0; c < 3; ++c) { const double d = E.cws[pa[i]][c] - E.cws[pb[i]][c]; s += d * d; }
+    E.rho[i] = s;
+  }
+  // three linearised starts, Gauss-Newton, keep the smallest reprojection error (N = 1,2,3)
+  double bestR[9], bestT[3], best_err = 0.0;
+  bool have = false;
+  for (int N = 1; N <= 3; ++N) {
+    const int ncol = (N == 1) ? 4 : (N == 2 ? 3 : 5);
+    const int cols1[4] = {0, 1, 3, 6}, cols2[3] = {0, 1, 2}, cols3[5] = {0, 1, 2, 3, 4};
+    const int* cols = (N == 1) ? cols1 : (N == 2 ? cols2 : cols3);
+    double A[30], r[6], x[5], b[4];
+    for (int i = 0; i < 6; ++i) {
+      for (int j = 0; j < ncol; ++j) A[i * ncol + j] = E.L[i][cols[j]];
+      r[i] = E.rho[i];
+    }
+    if (!ls_solve(A, r, x, 6, ncol)) continue;
+    if (N == 1) {
+      if (x[0] < 0) { b[0] = sqrt(-x[0]); b[1] = -x[1] / b[0]; b[2] = -x[2] / b[0]; b[3] = -x[3] / b[0]; }
+      else { b[0] = sqrt(x[0]); b[1] = x[1] / b[0]; b[2] = x[2] / b[0]; b[3] = x[3] / b[0]; }
+    } else {
+      if (x[0] < 0) { b[0] = sqrt(-x[0]); b[1] = (x[2] < 0) ? sqrt(-x[2]) : 0.0; }
+      else { b[0] = sqrt(x[0]); b[1] = (x[2] > 0) ? sqrt(x[2]) : 0.0; }
+      if (x[1] < 0) b[0] = -b[0];
+      b[2] = (N == 3) ? x[3] / b[0] : 0.0;
+      b[3] = 0.0;
+    }
+    epnp_gauss_newton(E, b);
+    double R[9], t[3];
+    const double err = epnp_R_and_t(E, b, fu, fv, uc, vc, R, t);
+    if (!isfinite(err)) continue;
+    if (!have || err < best_err) {
+      have = true; best_err = err;
+      for (int e = 0; e < 9; ++e) bestR[e] = R[e];
+      for (int e = 0; e < 3; ++e) bestT[e] = t[e];
+    }
+  }
+  if (!have) return false;
+  for (int e = 0; e < 9; ++e) R[e] = bestR[e];
+  for (int e = 0; e < 3; ++e) t[e] = bestT[e];
+  return true;
+}
+
+// ------------------------------------------------------------------ kernels
+__global__ void pnp_prepare_kernel(const double* __restrict__ X, const double* __restrict__ x, int n,
+                                   PnpWs w) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // solvePnPRansac converts its inputs to CV_32F before anything else
+  for (int k = 0; k < 3; ++k) w.Xf[3 * i + k] = (double)__double2float_rn(X[3 * i + k]);
+  for (int k = 0; k < 2; ++k) w.xf[2 * i + k] = (double)__double2float_rn(x[2 * i + k]);
+}
+
+__device__ __forceinline__ uint32_t pnp_rng_next(uint64_t& s) {
+  s = (uint64_t)(uint32_t)s * 4164903690ull + (uint32_t)(s >> 32);
+  return (uint32_t)s;
+}
+
+__global__ void pnp_sample_kernel(int n, int iters, PnpWs w) {
+  if (blockIdx.x || threadIdx.x) return;
+  uint64_t s = 0xffffffffffffffffull;
+  for (int it = 0; it < iters; ++it) {
+    int32_t idx[5];
+    for (int i = 0; i < 5;) {
+      const int v = (int)(pnp_rng_next(s) % (uint32_t)n);
+      bool dup = false;
+      for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
+      idx[i] = v;
+      if (!dup) ++i;
+    }
+    for (int k = 0; k < 5; ++k) w.samples[5 * it + k] = idx[k];
+  }
+}
+
+// one thread per RANSAC iteration: EPnP on its 5-point sample
+__global__ void __launch_bounds__(32)
+pnp_solve_kernel(const double* __restrict__ K, int iters, PnpWs w) {
+  const int it = blockIdx.x * blockDim.x + threadIdx.x;
+  if (it >= iters) return;
+  Epnp5 E;
+  for (int p = 0; p < 5; ++p) {
+    const int i = w.samples[5 * it + p];
+    for (int k = 0; k < 3; ++k) E.X[p][k] = w.Xf[3 * i + k];
+    for (int k = 0; k < 2; ++k) E.u[p][k] = w.xf[2 * i + k];
+  }
+  double Kl[9], R[9], t[3];
+  for (int e = 0; e < 9; ++e) Kl[e] = K[e];
+  const bool ok = epnp5(E, Kl, R, t);
+  w.valid[it] = ok ? 1 : 0;
+  if (ok) {
+    for (int e = 0; e < 9; ++e) w.models[12 * it + e] = R[e];
+    for (int e = 0; e < 3; ++e) w.models[12 * it + 9 + e] = t[e];
+  }
+}
+
+// PnPRansacCallback::computeError: projectPoints in double, result stored as float32, error =
+// float32 of the squared pixel distance between float32 points
+__device__ __forceinline__ float pnp_error(const double* __restrict__ Rt, const double* __restrict__ K,
+                                           const double* __restrict__ Xp, const double* __restrict__ up) {
+  const double X = Xp[0], Y = Xp[1], Z = Xp[2];
+  double xc = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Rt[0], X), __dmul_rn(Rt[1], Y)), __dmul_rn(Rt[2], Z)), Rt[9]);
+  double yc = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Rt[3], X), __dmul_rn(Rt[4], Y)), __dmul_rn(Rt[5], Z)), Rt[10]);
+  double zc = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(Rt[6], X), __dmul_rn(Rt[7], Y)), __dmul_rn(Rt[8], Z)), Rt[11]);
+  zc = zc != 0.0 ? __ddiv_rn(1.0, zc) : 1.0;
+  xc = __dmul_rn(xc, zc);
+  yc = __dmul_rn(yc, zc);
+  const float pu = __double2float_rn(__dadd_rn(__dmul_rn(xc, K[0]), K[2]));
+  const float pv = __double2float_rn(__dadd_rn(__dmul_rn(yc, K[4]), K[5]));
+  const float du = __fsub_rn((float)up[0], pu), dv = __fsub_rn((float)up[1], pv);
+  return __double2float_rn(__dadd_rn(__dmul_rn((double)du, (double)du), __dmul_rn((double)dv, (double)dv)));
+}
+
+__global__ void __launch_bounds__(256)
+pnp_score_kernel(const double* __restrict__ K, int n, int iters, float thr2, PnpWs w) {
+  const int it = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (it >= iters) return;
+  if (!w.valid[it]) { if (lane == 0) w.counts[it] = 0; return; }
+  double Rt[12], Kl[9];
+  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * it + e];
+  for (int e = 0; e < 9; ++e) Kl[e] = K[e];
+  int cnt = 0;
+  for (int i = lane; i < n; i += 32) cnt += pnp_error(Rt, Kl, w.Xf + 3 * i, w.xf + 2 * i) <= thr2;
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if (lane == 0) w.counts[it] = cnt;
+}
+
+__device__ int pnp_update_num_iters(double p, double ep, int model_points, int max_iters) {
+  p = fmin(fmax(p, 0.0), 1.0);
+  ep = fmin(fmax(ep, 0.0), 1.0);
+  double num = fmax(1.0 - p, DBL_MIN);
+  double denom = 1.0 - pow(1.0 - ep, (double)model_points);
+  if (denom < DBL_MIN) return 0;
+  num = log(num);
+  denom = log(denom);
+  return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
+}
+
+// ordered scan (OpenCV's sequential rule) + inlier mask of the winner + ascending index list
+__global__ void __launch_bounds__(1024)
+pnp_select_kernel(const double* __restrict__ K, int n, int iters, double conf, float thr2, PnpWs w,
+                  int32_t* __restrict__ inliers, int32_t* __restrict__ n_inl, int32_t* __restrict__ ok) {
+  __shared__ int s_best, s_base, warp_tot[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) {
+    int niters = iters, maxgood = 0, best = -1;
+    for (int it = 0; it < iters && it < niters; ++it) {
+      const int c = w.counts[it];
+      if (w.valid[it] && c > max(maxgood, 4)) {
+        maxgood = c; best = it;
+        niters = pnp_update_num_iters(conf, (double)(n - c) / n, 5, niters);
+      }
+    }
+    s_best = best; s_base = 0;
+    w.best[0] = best; w.best[1] = niters; w.best[2] = maxgood;
+  }
+  __syncthreads();
+  const int best = s_best;
+  if (best < 0) {
+    if (tid == 0) { *n_inl = 0; *ok = 0; w.best[3] = 0; }
+    return;
+  }
+  double Rt[12], Kl[9];
+  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * best + e];
+  for (int e = 0; e < 9; ++e) Kl[e] = K[e];
+  for (int i0 = 0; i0 < n; i0 += 1024) {
+    const int i = i0 + tid;
+    const bool in = i < n && pnp_error(Rt, Kl, w.Xf + 3 * i, w.xf + 2 * i) <= thr2;
+    if (i < n) w.mask[i] = in;
+    const unsigned bal = __ballot_sync(0xffffffffu, in);
+    if (lane == 0) warp_tot[wid] = __popc(bal);
+    __syncthreads();
+    int off = s_base;
+    for (int k = 0; k < wid; ++k) off += warp_tot[k];
+    off += __popc(bal & ((1u << lane) - 1u));
+    if (in) inliers[off] = i;
+    __syncthreads();
+    if (tid == 0) { int tot = 0; for (int k = 0; k < 32; ++k) tot += warp_tot[k]; s_base += tot; }
+    __syncthreads();
+  }
+  if (tid == 0) { *n_inl = s_base; *ok = 1; w.best[3] = s_base; }
+}
+
+// ------------------------------------------------------------------ iterative refit (LM)
+// minimise sum |proj(R X + t) - x|^2 over the inliers, updates R <- exp(w) R, t <- t + d.
+// The optimum does not depend on the parametrisation, so it equals the one cv2's
+// SOLVEPNP_ITERATIVE Levenberg-Marquardt (over rvec,tvec) converges to.
+constexpr int REFINE_THREADS = 256;
+
+__device__ void block_reduce(double* vals, int nvals, double* smem /*[8][nvals]*/) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int k = 0; k < nvals; ++k) {
+    double v = vals[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) smem[wid * nvals + k] = v;
+  }
+  __syncthreads();
+  for (int k = 0; k < nvals; ++k) {
+    double s = 0.0;
+    for (int wv = 0; wv < REFINE_THREADS / 32; ++wv) s += smem[wv * nvals + k];
+    vals[k] = s;
+  }
+  __syncthreads();
+}
+
+__device__ void exp_so3(const double* w, double* R /*3x3*/) {
+  const double th = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+  double a, b;
+  if (th < 1e-8) { a = 1.0 - th * th / 6.0; b = 0.5 - th * th / 24.0; }
+  else { a = sin(th) / th; b = (1.0 - cos(th)) / (th * th); }
+  const double Kx[9] = {0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0};
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      double k2 = 0.0;
+      for (int k = 0; k < 3; ++k) k2 += Kx[3 * i + k] * Kx[3 * k + j];
+      R[3 * i + j] = (i == j ? 1.0 : 0.0) + a * Kx[3 * i + j] + b * k2;
+    }
+}
+
+// cv2.Rodrigues(R) -> rvec (matrix to vector)
+__device__ void log_so3(const double* R, double* r) {
+  double rx = R[7] - R[5], ry = R[2] - R[6], rz = R[3] - R[1];
+  const double s = sqrt((rx * rx + ry * ry + rz * rz) * 0.25);
+  double c = (R[0] + R[4] + R[8] - 1.0) * 0.5;
+  c = c > 1.0 ? 1.0 : (c < -1.0 ? -1.0 : c);
+  const double th = acos(c);
+  if (s < 1e-5) {
+    if (c > 0) { r[0] = r[1] = r[2] = 0.0; return; }
+    double t0 = sqrt(fmax((R[0] + 1) * 0.5, 0.0)), t1 = sqrt(fmax((R[4] + 1) * 0.5, 0.0)) * (R[1] < 0 ? -1.0 : 1.0),
+           t2 = sqrt(fmax((R[8] + 1) * 0.5, 0.0)) * (R[2] < 0 ? -1.0 : 1.0);
+    if (fabs(t0) < fabs(t1) && fabs(t0) < fabs(t2) && ((R[5] > 0) != (t1 * t2 > 0))) t2 = -t2;
+    const double sc = th / sqrt(t0 * t0 + t1 * t1 + t2 * t2);
+    r[0] = t0 * sc; r[1] = t1 * sc; r[2] = t2 * sc;
+    return;
+  }
+  const double vth = 0.5 / s * th;
+  r[0] = rx * vth; r[1] = ry * vth; r[2] = rz * vth;
+}
+
+__device__ bool chol_solve6(const double* H, const double* g, double lambda, double* x) {
+  double L[36];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j <= i; ++j) {
+      double s = H[6 * i + j] + (i == j ? lambda * H[6 * i + i] : 0.0);
+      for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
+      if (i == j) { if (!(s > 0.0)) return false; L[6 * i + i] = sqrt(s); }
+      else L[6 * i + j] = s / L[6 * j + j];
+    }
+  double y[6];
+  for (int i = 0; i < 6; ++i) {
+    double s = -g[i];
+    for (int k = 0; k < i; ++k) s -= L[6 * i + k] * y[k];
+    y[i] = s / L[6 * i + i];
+  }
+  for (int i = 5; i >= 0; --i) {
+    double s = y[i];
+    for (int k = i + 1; k < 6; ++k) s -= L[6 * k + i] * x[k];
+    x[i] = s / L[6 * i + i];
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(REFINE_THREADS)
+pnp_refine_kernel(const double* __restrict__ K, PnpWs w, const int32_t* __restrict__ inliers,
+                  double* __restrict__ rvec, double* __restrict__ tvec) {
+  __shared__ double red[8 * 28];
+  __shared__ double sR[9], st[3], cR[9], ct[3];
+  __shared__ double s_cost, s_lambda;
+  __shared__ int s_state;   // 0 continue, 1 converged/stop
+  const int best = w.best[0], ni = w.best[3];
+  if (best < 0) return;
+  const int tid = threadIdx.x;
+  if (tid < 9) sR[tid] = w.models[12 * best + tid];
+  if (tid < 3) st[tid] = w.models[12 * best + 9 + tid];
+  if (tid == 0) { s_lambda = 1e-3; s_state = 0; s_cost = -1.0; }
+  __syncthreads();
+  const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+  for (int iter = 0; iter < 60; ++iter) {
+    // normal equations at (sR, st)
+    double acc[28];
+    for (int k = 0; k < 28; ++k) acc[k] = 0.0;
+    for (int q = tid; q < ni; q += REFINE_THREADS) {
+      const int i = inliers[q];
+      const double X = w.Xf[3 * i], Y = w.Xf[3 * i + 1], Z = w.Xf[3 * i + 2];
+      const double rx = sR[0] * X + sR[1] * Y + sR[2] * Z, ry = sR[3] * X + sR[4] * Y + sR[5] * Z,
+                   rz = sR[6] * X + sR[7] * Y + sR[8] * Z;
+      const double xc = rx + st[0], yc = ry + st[1], zc = rz + st[2];
+      const double iz = 1.0 / zc;
+      const double eu = fx * xc * iz + cx - w.xf[2 * i], ev = fy * yc * iz + cy - w.xf[2 * i + 1];
+      // d(u,v)/dXc
+      const double a0 = fx * iz, a2 = -fx * xc * iz * iz, b1 = fy * iz, b2 = -fy * yc * iz * iz;
+      // dXc/dw = -[RX]x ; dXc/dt = I
+      double Ju[6], Jv[6];
+      Ju[0] = a2 * ry;            Ju[1] = a0 * rz - a2 * rx;  Ju[2] = -a0 * ry;
+      Jv[0] = -b1 * rz + b2 * ry; Jv[1] = -b2 * rx;           Jv[2] = b1 * rx;
+      Ju[3] = a0; Ju[4] = 0.0; Ju[5] = a2;
+      Jv[3] = 0.0; Jv[4] = b1; Jv[5] = b2;
+      int e = 0;
+      for (int r = 0; r < 6; ++r)
+        for (int c = 0; c <= r; ++c) acc[e++] += Ju[r] * Ju[c] + Jv[r] * Jv[c];
+      for (int r = 0; r < 6; ++r) acc[21 + r] += Ju[r] * eu + Jv[r] * ev;
+      acc[27] += eu * eu + ev * ev;
+    }
+    block_reduce(acc, 28, red);
+    if (tid == 0) {
+      double H[36], g[6], d[6];
+      int e = 0;
+      for (int r = 0; r < 6; ++r)
+        for (int c = 0; c <= r; ++c) { H[6 * r + c] = acc[e]; H[6 * c + r] = acc[e]; ++e; }
+      for (int r = 0; r < 6; ++r) g[r] = acc[21 + r];
+      s_cost = acc[27];
+      if (!chol_solve6(H, g, s_lambda, d)) { s_lambda *= 10.0; for (int k = 0; k < 6; ++k) d[k] = 0.0; }
+      double dR[9];
+      exp_so3(d, dR);
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) cR[3 * i + j] = dR[3 * i] * sR[j] + dR[3 * i + 1] * sR[3 + j] + dR[3 * i + 2] * sR[6 + j];
+      // t' = exp(w) t_rot-part is NOT applied to t: X_c' = exp(w) R X + t + d
+      for (int i = 0; i < 3; ++i) ct[i] = st[i] + d[3 + i];
+      const double dn = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + d[3] * d[3] + d[4] * d[4] + d[5] * d[5]);
+      const double pn = sqrt(st[0] * st[0] + st[1] * st[1] + st[2] * st[2]) + 1.0;
+      if (dn < 1e-13 * pn) s_state = 1;
+    }
+    __syncthreads();
+    if (s_state) break;
+    // cost at the candidate
+    double c1[1] = {0.0};
+    for (int q = tid; q < ni; q += REFINE_THREADS) {
+      const int i = inliers[q];
+      const double X = w.Xf[3 * i], Y = w.Xf[3 * i + 1], Z = w.Xf[3 * i + 2];
+      const double xc = cR[0] * X + cR[1] * Y + cR[2] * Z + ct[0], yc = cR[3] * X + cR[4] * Y + cR[5] * Z + ct[1],
+                   zc = cR[6] * X + cR[7] * Y + cR[8] * Z + ct[2];
+      const double eu = fx * xc / zc + cx - w.xf[2 * i], ev = fy * yc / zc + cy - w.xf[2 * i + 1];
+      c1[0] += eu * eu + ev * ev;
+    }
+    block_reduce(c1, 1, red);
+    if (tid == 0) {
+      if (c1[0] <= s_cost) {
+        for (int k = 0; k < 9; ++k) sR[k] = cR[k];
+        for (int k = 0; k < 3; ++k) st[k] = ct[k];
+        s_lambda = fmax(s_lambda * 0.1, 1e-15);
+      } else {
+        s_lambda *= 10.0;
+        if (s_lambda > 1e15) s_state = 1;
+      }
+    }
+    __syncthreads();
+    if (s_state) break;
+  }
+  if (tid == 0) {
+    log_so3(sR, rvec);
+    for (int k = 0; k < 3; ++k) tvec[k] = st[k];
+  }
+}
+
+}  // namespace vo
+
+using namespace vo;
+
+extern "C" size_t vo_pnp_workspace_bytes(int n, int iters) {
+  if (n <= 0 || iters <= 0) return 0;
+  return pnp_carve(nullptr, n, iters).bytes;
+}
+
+extern "C" int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int iters,
+                             double reproj_px, double conf, double* rvec, double* tvec,
+                             int32_t* inliers, int32_t* n_inl, int32_t* ok, void* ws, size_t ws_bytes,
+                             void* stream) {
+  VO_REQUIRE(X && x && K && rvec && tvec && inliers && n_inl && ok && ws, VO_ERR_INVALID_ARG,
+             "vo_pnp_ransac: null pointer");
+  VO_REQUIRE(n >= 5, VO_ERR_TOO_FEW_POINTS,
+             "vo_pnp_ransac: needs >= 5 points (got %d); the 4-point P3P path is not implemented", n);
+  VO_REQUIRE(iters > 0 && iters <= PNP_MAX_ITERS, VO_ERR_INVALID_ARG, "vo_pnp_ransac: iters must be in 1..1024");
+  PnpWs w = pnp_carve(ws, n, iters);
+  VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_pnp_ransac: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const float thr2 = (float)(reproj_px * reproj_px);
+  pnp_prepare_kernel<<<(n + 255) / 256, 256, 0, st>>>(X, x, n, w);
+  pnp_sample_kernel<<<1, 32, 0, st>>>(n, iters, w);
+  pnp_solve_kernel<<<(iters + 31) / 32, 32, 0, st>>>(K, iters, w);
+  pnp_score_kernel<<<(iters + 7) / 8, 256, 0, st>>>(K, n, iters, thr2, w);
+  pnp_select_kernel<<<1, 1024, 0, st>>>(K, n, iters, conf, thr2, w, inliers, n_inl, ok);
+  pnp_refine_kernel<<<1, REFINE_THREADS, 0, st>>>(K, w, inliers, rvec, tvec);
+  return check_launch("vo_pnp_ransac");
+}
