@@ -1,0 +1,61 @@
+"""CPU, build container only (skipped where /root/reference is absent): the reference's OWN
+driver modules import and construct on top of the compat modules (seam 2) —
+visual_slam.py / map.py / tracked_*.py / main*.py are used unmodified from /root/reference/src."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+
+REF = "/root/reference/src"
+pytestmark = pytest.mark.skipif(not os.path.isdir(REF), reason="reference sources not on this box")
+
+_NAMES = ["initials", "image_pair", "frame", "frame_generator", "image_and_keypoints",
+          "triangulate_points_from_images", "visual_slam", "map", "tracked_camera", "tracked_point",
+          "observation", "main", "main_triangulate"]
+
+
+@pytest.fixture()
+def compat_path():
+    from visual_odometry_b200 import compat
+    saved_path, saved_mods = list(sys.path), {k: sys.modules.get(k) for k in _NAMES}
+    for k in _NAMES:
+        sys.modules.pop(k, None)
+    sys.dont_write_bytecode = True
+    compat.install(reference_src=REF)
+    yield
+    sys.path[:] = saved_path
+    for k in _NAMES:
+        sys.modules.pop(k, None)
+        if saved_mods[k] is not None:
+            sys.modules[k] = saved_mods[k]
+
+
+def test_reference_visual_slam_runs_on_compat_modules(compat_path):
+    vs = importlib.import_module("visual_slam")            # the reference's file, unmodified
+    assert vs.__file__.startswith(REF)
+    import image_pair, frame_generator, initials            # ours, shadowing the reference's
+    assert "visual_odometry_b200" in image_pair.ImagePair.__module__
+    assert vs.ImagePair is image_pair.ImagePair and vs.FrameGenerator is frame_generator.FrameGenerator
+    slam = vs.VisualSlam("/nonexistent")
+    slam.set_camera_matrix()
+    # the committed test.g2o pins f, cx, cy of the live intrinsics
+    assert np.allclose([slam.camera_matrix[0, 0], slam.camera_matrix[0, 2], slam.camera_matrix[1, 2]],
+                       [802.832, 565.427, 240.124], atol=1e-3)
+    assert vs.cv2 is initials.cv2 and hasattr(vs.cv2, "solvePnPRansac")
+    # namedtuples keep the reference's field order
+    assert initials.Match._fields == ('featureid1', 'featureid2', 'keypoint1', 'keypoint2',
+                                      'descriptor1', 'descriptor2', 'distance', 'color')
+    assert initials.Match3D._fields[-1] == 'point'
+    assert initials.MatchWithMap._fields[2:4] == ('imagecoord', 'mapcoord')
+
+
+def test_reference_entry_points_import(compat_path):
+    mt = importlib.import_module("main_triangulate")        # reference file, unmodified
+    import triangulate_points_from_images as tp
+    assert mt.TriangulatePointsFromTwoImages is tp.TriangulatePointsFromTwoImages
+    assert "visual_odometry_b200" in tp.TriangulatePointsFromTwoImages.__module__
+    from image_pair import ImagePair
+    legacy = ImagePair("ORB")                                # the shape main_triangulate.py needs
+    assert hasattr(legacy, "standard_pipeline") and hasattr(legacy, "set_images")
