@@ -21,6 +21,35 @@ constexpr int HM_TT = 128;     // train descriptors per smem tile (4 KB)
 constexpr int HM_NSTAGE = 4;
 constexpr uint32_t KEY_INF = 0xffffffffu;
 
+
+// 256-bit Hamming distance with a carry-save adder tree (Harley-Seal): the popc unit (XU pipe,
+// 16 lanes/clk/SM) is the scarce resource, LOP3 (ALU pipe, 64 lanes/clk/SM) is not.  Three
+// full adders compress seven of the eight XOR words into ones / twos words, so the distance is
+//   popc(ones) + popc(x7) + 2*(popc(c1) + popc(c2) + popc(c3))        = 5 popc + 6 LOP3
+// instead of 8 popc.  (A fourth adder over c1..c3 would give 4 popc + 8 LOP3, which moves the
+// bottleneck to the ALU pipe.)  Exact: a full adder preserves  a + b + c = sum + 2*carry  per bit.
+// (inline PTX so that ptxas keeps exactly one LOP3 per sum and per carry: left to itself the
+// compiler re-associates the XORs into the adders and ends up with 18 LOP3 instead of 14.)
+__device__ __forceinline__ uint32_t csa_sum(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));  // a ^ b ^ c
+  return r;
+}
+__device__ __forceinline__ uint32_t csa_carry(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));  // majority
+  return r;
+}
+__device__ __forceinline__ uint32_t hamming256(const uint32_t (&q)[8], const uint4& ta,
+                                               const uint4& tb) {
+  const uint32_t x0 = q[0] ^ ta.x, x1 = q[1] ^ ta.y, x2 = q[2] ^ ta.z, x3 = q[3] ^ ta.w;
+  const uint32_t x4 = q[4] ^ tb.x, x5 = q[5] ^ tb.y, x6 = q[6] ^ tb.z, x7 = q[7] ^ tb.w;
+  const uint32_t s1 = csa_sum(x0, x1, x2), c1 = csa_carry(x0, x1, x2);
+  const uint32_t s2 = csa_sum(x3, x4, x5), c2 = csa_carry(x3, x4, x5);
+  const uint32_t ones = csa_sum(s1, s2, x6), c3 = csa_carry(s1, s2, x6);
+  return (__popc(ones) + __popc(x7)) + 2u * (__popc(c1) + __popc(c2) + __popc(c3));
+}
+
 template <int RQ>
 __global__ void __launch_bounds__(HM_THREADS)
 hamming_top2_kernel(const uint8_t* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
@@ -102,10 +131,7 @@ hamming_top2_kernel(const uint8_t* __restrict__ desc, const int32_t* __restrict_
       uint32_t ck = KEY_INF;
 #pragma unroll
       for (int r = 0; r < RQ; ++r) {
-        const uint32_t d = __popc(qd[r][0] ^ ta.x) + __popc(qd[r][1] ^ ta.y) +
-                           __popc(qd[r][2] ^ ta.z) + __popc(qd[r][3] ^ ta.w) +
-                           __popc(qd[r][4] ^ tb.x) + __popc(qd[r][5] ^ tb.y) +
-                           __popc(qd[r][6] ^ tb.z) + __popc(qd[r][7] ^ tb.w);
+        const uint32_t d = hamming256(qd[r], ta, tb);
         const uint32_t rk = (d << 16) | jkey;
         m2[r] = min(m2[r], max(m1[r], rk));
         m1[r] = min(m1[r], rk);

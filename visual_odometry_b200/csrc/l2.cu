@@ -7,16 +7,28 @@
 // descriptors are integers in [0,255]: exact in bf16, dot products < 2^24 exact in fp32, so the
 // GEMM is EXACT for real SIFT data; other float descriptors get an fp32 rerank of the candidates.
 //
+// The GEMM has only K = 128, so one 128x128 accumulator tile is 576 tensor-pipe cycles of MMA
+// against 16384 values to rank: the epilogue, not the MMA, is the scarce resource.  Design:
+//   * the accumulator already holds an ORDERED INTEGER: a ninth K-step adds
+//       -s^2|b_j|^2/2 + MAGIC   (MAGIC = 1.5*2^22, s = a power-of-two scale)
+//     so the fp32 bit pattern of every element is  const + 2*s^2*(a.b - |b|^2/2): ranking is
+//     integer max on the raw bits, the column index rides in 7 low bits of a packed key
+//     (one IMAD on the FMA pipe + half a 3-input VIMNMX3 per element, no branches, no
+//     divergence; ties resolve to the lowest column exactly like OpenCV).
+//   * persistent CTAs (one per SM) walk a list of work items (pair, direction, 256-row block,
+//     column split) so TMEM allocation, barrier set-up and pipeline fill are paid once per SM.
+//   * every 40 KB B tile streamed from L2 feeds TWO 128-row A blocks (18 MMAs), halving the
+//     L2 -> SM traffic that capped the one-block version at ~60 % of the tensor rate.
+//
 // Pipeline per launch:
-//   l2_prep_kernel   fp32 [F,n,128] -> bf16 tiles already in the UMMA canonical K-major
-//                    no-swizzle layout (one 128x128 tile = one contiguous 32 KB block, so a tile
-//                    is ONE 1-D TMA bulk copy, no tensor map) + exact fp32 squared norms.
-//   l2_top2_tc_kernel  warp-specialised: warp 5 = TMA producer, warp 4 = single-thread MMA
-//                    issuer, warps 0-3 = epilogue (thread = TMEM lane = query row) keeping a
-//                    running top-2 of (d^2, index) straight out of TMEM.  Runs in both directions
-//                    (query->train, train->query) so the cross-check needs no column reduction.
-//   l2_compact_kernel  merges split partials, cross-check / ratio test, sqrtf, stable compaction,
-//                    keypoint gather.
+//   l2_norm_kernel   exact fp32 squared norms + the largest norm (fixes the scale s).
+//   l2_tile_kernel   fp32 [F,n,128] -> bf16 tiles already in the UMMA canonical K-major
+//                    no-swizzle layout (one 128x160 tile = one contiguous 40 KB block = ONE 1-D
+//                    TMA bulk copy, no tensor map).
+//   l2_top2_tc_kernel  warp-specialised: warp 17 = TMA producer, warp 16 = single-thread MMA
+//                    issuer, warps 0-15 = epilogue (thread = TMEM lane = query row).
+//   l2_rerank_kernel / l2_compact_kernel  fp32 rerank when the data is not exactly
+//                    representable; cross-check / ratio test, sqrtf, stable compaction, gather.
 #include <cuda_bf16.h>
 
 #include "tc.cuh"
@@ -26,22 +38,27 @@ namespace vo {
 constexpr int L2_DIM = 128;
 constexpr int L2_BLK = 128;                       // rows per tile (UMMA M and N)
 // a tile = 20 K-groups (kg) of 8 bf16 columns x 128 rows: kg 0..15 the descriptor, kg 16 = [1,1,1,0..]
-// (A-side extras), kg 17 = 0, kg 18 = -|b|^2/2 split into three bf16 (B-side extras), kg 19 = 0.
-// A ninth K=16 MMA step over (kg16,kg17) x (kg18,kg19) adds -|b_j|^2/2 to the accumulator, so the
-// epilogue ranks  a.b - |b|^2/2  directly: no norm loads, no FMA per element.
+// (A-side extras), kg 17 = 0, kg 18 = (-s^2|b|^2/2 + MAGIC) split into three bf16 (B-side
+// extras), kg 19 = 0.  A ninth K=16 MMA step over (kg16,kg17) x (kg18,kg19) adds that term.
 constexpr int L2_KG = 20;
 constexpr int L2_TILE_ELEMS = L2_BLK * 8 * L2_KG;  // 20480 bf16 = 40 KB
 constexpr int L2_TILE_BYTES = L2_TILE_ELEMS * 2;
 constexpr uint32_t L2_LBO = 2048;                 // between the two K core matrices of a K=16 slice
 constexpr uint32_t L2_SBO = 128;                  // between 8-row groups
 constexpr int L2_NSTAGE = 3;
+constexpr int L2_RBK = 2;                         // 128-row A blocks per work item
 constexpr int L2_EPI_WARPS = 16;  // 4 per TMEM lane quarter, 32 columns each
 constexpr int L2_THREADS = (L2_EPI_WARPS + 2) * 32;  // + MMA warp + TMA warp
+// fp32(MAGIC + x) has bit pattern bits(MAGIC) + 2x for every multiple x of 0.5 with |x| < 2^21
+#define L2_MAGIC 6291456.0f
+constexpr uint32_t L2_MAGIC_BITS = 0x4AC00000u;
+constexpr uint32_t L2_QBIAS = L2_MAGIC_BITS & 0x1ffffffu;   // what (key >> 7) reads for x = 0
+constexpr float L2_PAD_SCORE = 4194304.0f;        // MAGIC - 2^21: below every real score
 
 struct L2Ws {
-  __nv_bfloat16* tiles;   // [F][nblk][16384]
+  __nv_bfloat16* tiles;   // [F][nblk][20480]
   float* norms;           // [F][nblk*128]   (+inf on padded rows)
-  int32_t* inexact;       // [1] set when some value is not exactly representable in bf16
+  int32_t* flags;         // [0] inexact data, [1] bits of the largest squared norm
   float4* rowbest;        // [P][2][S][nblk*128]  (d2_1, idx_1, d2_2, idx_2) idx as int bits
   size_t bytes;
 };
@@ -59,30 +76,74 @@ static L2Ws l2_carve(void* base, int n_frames, int n_pairs, int n_cap, int split
   };
   w.tiles = (__nv_bfloat16*)take((size_t)n_frames * nblk * L2_TILE_BYTES);
   w.norms = (float*)take((size_t)n_frames * nblk * L2_BLK * sizeof(float));
-  w.inexact = (int32_t*)take(256);
+  w.flags = (int32_t*)take(256);
   w.rowbest = (float4*)take((size_t)n_pairs * 2 * splits * nblk * L2_BLK * sizeof(float4));
   w.bytes = off;
   return w;
 }
 
-// ------------------------------------------------------------------ prep: fp32 -> bf16 tiles
-// tile layout (bytes): kg*2048 + rg*128 + rr*16 + kk*2  with r = 8*rg+rr, k = 8*kg+kk
+// bit 0: producer loads each stage only once (no per-tile TMA); bit 1: epilogue skips the scan;
+// bit 2: epilogue skips the TMEM load too (diagnostics only: results are wrong when set);
+// bit 3: MAGIC is added by the epilogue (FADD) instead of inside the ninth MMA step.
+__device__ int g_l2_debug = 0;
+
+// scale s = 2^k with s^2 * max|d|^2 <= 2^20: every score  s^2 (a.b - |b|^2/2)  then lies inside
+// the +-2^21 window around MAGIC, and is a multiple of 0.5 (= exact) for integer descriptors.
+__device__ __forceinline__ float l2_scale(const int32_t* flags) {
+  const float maxn2 = __int_as_float(flags[1]);
+  if (!(maxn2 > 0.f) || !(maxn2 < 3.0e38f)) return 1.f;
+  int e;
+  frexpf(maxn2, &e);             // maxn2 = m * 2^e, m in [0.5, 1)  =>  maxn2 <= 2^e
+  const int k2 = 20 - e;         // s^2 <= 2^k2
+  const int k = (k2 >= 0) ? (k2 >> 1) : -((1 - k2) >> 1);
+  return ldexpf(1.f, k);
+}
+
+// ------------------------------------------------------------------ prep 1: norms + largest norm
 __global__ void __launch_bounds__(256)
-l2_prep_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
+l2_norm_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
                int nblk, L2Ws w) {
   const int f = blockIdx.y, blk = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = nkp[f];
+  float mx = 0.f;
+  for (int rl = warp; rl < L2_BLK; rl += 8) {
+    const int r = blk * L2_BLK + rl;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < n) v = __ldg(reinterpret_cast<const float4*>(desc + ((size_t)f * n_cap + r) * L2_DIM) + lane);
+    float ss = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (lane == 0)
+      w.norms[((size_t)f * nblk + blk) * L2_BLK + rl] = (r < n) ? ss : __int_as_float(0x7f800000);
+    if (r < n) mx = fmaxf(mx, ss);
+  }
+  // non-negative floats order like their bit patterns
+  if (lane == 0 && mx > 0.f) atomicMax(&w.flags[1], __float_as_int(mx));
+}
+
+// ------------------------------------------------------------------ prep 2: fp32 -> bf16 tiles
+// tile layout (bytes): kg*2048 + rg*128 + rr*16 + kk*2  with r = 8*rg+rr, k = 8*kg+kk
+__global__ void __launch_bounds__(256)
+l2_tile_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
+               int nblk, L2Ws w) {
+  const int f = blockIdx.y, blk = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = nkp[f];
+  const float sc = l2_scale(w.flags);
+  const bool fold_magic = (g_l2_debug & 8) == 0;
   __nv_bfloat16* tile = w.tiles + ((size_t)f * nblk + blk) * L2_TILE_ELEMS;
   bool bad = false;
   for (int rl = warp; rl < L2_BLK; rl += 8) {
     const int r = blk * L2_BLK + rl;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (r < n) v = __ldg(reinterpret_cast<const float4*>(desc + ((size_t)f * n_cap + r) * L2_DIM) + lane);
+    v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;      // power of two: exact
     const __nv_bfloat16 b0 = __float2bfloat16_rn(v.x), b1 = __float2bfloat16_rn(v.y),
                         b2 = __float2bfloat16_rn(v.z), b3 = __float2bfloat16_rn(v.w);
+    // exact path needs: representable in bf16 AND integer after scaling (scores multiples of 1)
     bad |= (__bfloat162float(b0) != v.x) | (__bfloat162float(b1) != v.y) |
-           (__bfloat162float(b2) != v.z) | (__bfloat162float(b3) != v.w);
+           (__bfloat162float(b2) != v.z) | (__bfloat162float(b3) != v.w) |
+           (truncf(v.x) != v.x) | (truncf(v.y) != v.y) | (truncf(v.z) != v.z) | (truncf(v.w) != v.w);
     const int k = 4 * lane;
     const size_t byte_off = (size_t)(k >> 3) * 2048 + (size_t)(rl >> 3) * 128 + (rl & 7) * 16 + (k & 7) * 2;
     __nv_bfloat162 lo, hi;
@@ -91,27 +152,22 @@ l2_prep_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, 
     pk.x = *reinterpret_cast<uint32_t*>(&lo);
     pk.y = *reinterpret_cast<uint32_t*>(&hi);
     *reinterpret_cast<uint2*>(reinterpret_cast<char*>(tile) + byte_off) = pk;
-    float ss = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    if (lane == 0)
-      w.norms[((size_t)f * nblk + blk) * L2_BLK + rl] = (r < n) ? ss : __int_as_float(0x7f800000);
     if (lane < 4) {  // the four extra K-groups of this row (16 bytes each)
       uint4 e = make_uint4(0, 0, 0, 0);
       if (lane == 0) {
         e.x = 0x3f803f80u;  // bf16 (1, 1)
         e.y = 0x00003f80u;  // bf16 (1, 0)
       } else if (lane == 2) {
-        __nv_bfloat16 h, m, l;
+        const float base = fold_magic ? L2_MAGIC : 0.f;
+        float x = fold_magic ? L2_PAD_SCORE : -2097152.0f;   // padded column never wins
         if (r < n) {
-          const float x = -0.5f * ss;
-          h = __float2bfloat16_rn(x);
-          const float r1 = x - __bfloat162float(h);
-          m = __float2bfloat16_rn(r1);
-          l = __float2bfloat16_rn(r1 - __bfloat162float(m));
-        } else {
-          h = __float2bfloat16_rn(__int_as_float(0xff800000));  // -inf: padded column never wins
-          m = l = __float2bfloat16_rn(0.f);
+          const float ss = w.norms[((size_t)f * nblk + blk) * L2_BLK + rl];
+          x = fmaf(-0.5f * sc * sc, ss, base);
         }
+        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+        const float r1 = x - __bfloat162float(h);
+        const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+        const __nv_bfloat16 l = __float2bfloat16_rn(r1 - __bfloat162float(m));
         e.x = (uint32_t)__bfloat16_as_ushort(h) | ((uint32_t)__bfloat16_as_ushort(m) << 16);
         e.y = (uint32_t)__bfloat16_as_ushort(l);
       }
@@ -119,185 +175,320 @@ l2_prep_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, 
                                 (size_t)(rl >> 3) * 128 + (rl & 7) * 16) = e;
     }
   }
-  if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(w.inexact, 1);
+  if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(&w.flags[0], 1);
 }
 
-// ------------------------------------------------------------------ tensor-core top-2
-// bit 0: producer loads each stage only once (no per-tile TMA); bit 1: epilogue skips the scan;
-// bit 2: epilogue skips the TMEM load too.  Diagnostics only (results are wrong when set).
-__device__ int g_l2_debug = 0;
-
+// ------------------------------------------------------------------ tensor-core top-1 / top-2
 struct __align__(1024) L2Smem {
-  uint8_t A[L2_TILE_BYTES];
+  uint8_t A[L2_RBK][L2_TILE_BYTES];
   uint8_t B[L2_NSTAGE][L2_TILE_BYTES];
-  float4 part[3][L2_BLK];  // top-2 of column quarters 1..3 of each row, merged by quarter 0
-  uint64_t full_a;
+  uint4 part[3][L2_RBK][L2_BLK];  // (key1, tile1, key2, tile2) of column quarters 1..3
+  uint64_t full_a, empty_a;
   uint64_t full_b[L2_NSTAGE], empty_b[L2_NSTAGE];
   uint64_t tmem_full[2], tmem_empty[2];
   uint32_t tmem_base;
 };
 
-// running top-2 of the LARGEST scores; ties keep the earlier (lower) column
-__device__ __forceinline__ void top2_insert(float s, int c, float& s1, int& i1, float& s2, int& i2) {
-  if (s > s1) { s2 = s1; i2 = i1; s1 = s; i1 = c; }
-  else { s2 = s; i2 = c; }
+struct L2Item {
+  int pair, dir, split, rbp;   // rbp = index of the 256-row block
+  int fq, ft, nq, nt;
+  int t_lo, ntile, nrb;        // column tiles [t_lo, t_lo+ntile), valid 128-row blocks (0..2)
+};
+
+__device__ __forceinline__ L2Item l2_item(int item, const int32_t* __restrict__ nkp,
+                                          const int32_t* __restrict__ pairs, int nblk, int nrbp,
+                                          int n_splits, int ndir) {
+  L2Item it;
+  it.rbp = item % nrbp;
+  int x = item / nrbp;
+  it.split = x % n_splits;
+  x /= n_splits;
+  it.dir = x % ndir;
+  it.pair = x / ndir;
+  it.fq = pairs[2 * it.pair + it.dir];
+  it.ft = pairs[2 * it.pair + 1 - it.dir];
+  it.nq = nkp[it.fq];
+  it.nt = nkp[it.ft];
+  const int ntile_all = (it.nt + L2_BLK - 1) / L2_BLK;
+  const int per = (ntile_all + n_splits - 1) / n_splits;
+  it.t_lo = it.split * per;
+  it.ntile = max(min(ntile_all, it.t_lo + per) - it.t_lo, 0);
+  const int r0 = it.rbp * L2_RBK * L2_BLK;
+  it.nrb = r0 >= it.nq ? 0 : (r0 + L2_BLK < it.nq ? 2 : 1);
+  if (it.nrb == 0) it.ntile = 0;
+  return it;
+}
+
+// a packed key = (score bits << 7) | (31 - column inside the 32-column chunk): unsigned max =
+// largest score, lowest column on ties.  t1/t2 hold the chunk number (tile * 4 + quarter).  Keys
+// of different chunks compare by score only (key >> 7) and an earlier chunk keeps its place on
+// ties, so the global order is "lowest column index wins".
+struct L2Top {
+  uint32_t k1, k2;
+  int t1, t2;
+};
+
+__device__ __forceinline__ uint32_t umax3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u32(a, b, c); }
+
+// fold one tile's (h1 >= h2, both of tile t) into the running top-2
+template <bool TOP2>
+__device__ __forceinline__ void l2_fold_tile(L2Top& s, uint32_t h1, uint32_t h2, int t) {
+  if (!TOP2) {
+    const bool p = (h1 >> 7) > (s.k1 >> 7);
+    s.k1 = p ? h1 : s.k1;
+    s.t1 = p ? t : s.t1;
+  } else {
+    const bool a = (h1 >> 7) > (s.k1 >> 7);
+    // a: new best = h1; second = h2 if it beats the old best (strictly), else the old best
+    // !a: best stays; second = h1 if it beats the old second (strictly)
+    const bool b = a ? ((h2 >> 7) > (s.k1 >> 7)) : ((h1 >> 7) > (s.k2 >> 7));
+    const uint32_t n2 = a ? (b ? h2 : s.k1) : (b ? h1 : s.k2);
+    const int nt2 = a ? (b ? t : s.t1) : (b ? t : s.t2);
+    s.k2 = n2;
+    s.t2 = nt2;
+    s.k1 = a ? h1 : s.k1;
+    s.t1 = a ? t : s.t1;
+  }
+}
+
+template <bool ADDM, int C>
+struct L2Pack {
+  static __device__ __forceinline__ void run(uint32_t (&k)[32], const uint32_t (&v)[32], uint32_t mul) {
+    uint32_t bits = v[C];
+    if (ADDM) bits = __float_as_uint(__fadd_rn(__uint_as_float(bits), L2_MAGIC));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(k[C]) : "r"(bits), "r"(mul), "n"(31 - C));
+    L2Pack<ADDM, C + 1>::run(k, v, mul);
+  }
+};
+template <bool ADDM>
+struct L2Pack<ADDM, 32> {
+  static __device__ __forceinline__ void run(uint32_t (&)[32], const uint32_t (&)[32], uint32_t) {}
+};
+
+// rank 32 accumulator values (one TMEM chunk of this thread's row) into the running state.
+// key = bits * 128 + (31 - c): `mul` holds 128 in a register the compiler cannot see through, so
+// the index stays an immediate addend and the whole packing is ONE IMAD on the FMA pipe.
+template <bool TOP2, bool ADDM>
+__device__ __forceinline__ void l2_rank_chunk(L2Top& s, const uint32_t (&v)[32], uint32_t mul,
+                                              int t) {
+  uint32_t k[32];
+  L2Pack<ADDM, 0>::run(k, v, mul);
+  if (!TOP2) {
+    // 3-input max tree: 32 -> 11 -> 4 -> 2 -> 1  (16 VIMNMX3/VIMNMX, depth 4)
+    uint32_t a[11];
+#pragma unroll
+    for (int c = 0; c < 10; ++c) a[c] = umax3(k[3 * c], k[3 * c + 1], k[3 * c + 2]);
+    a[10] = max(k[30], k[31]);
+    const uint32_t b0 = umax3(a[0], a[1], a[2]), b1 = umax3(a[3], a[4], a[5]),
+                   b2 = umax3(a[6], a[7], a[8]), b3 = max(a[9], a[10]);
+    const uint32_t m = max(umax3(b0, b1, b2), b3);
+    l2_fold_tile<false>(s, m, 0u, t);
+  } else {
+    // tournament of sorted pairs: merge (a1>=a2),(b1>=b2) -> (max(a1,b1), max3(min(a1,b1),a2,b2))
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      hi[c] = max(k[2 * c], k[2 * c + 1]);
+      lo[c] = min(k[2 * c], k[2 * c + 1]);
+    }
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1) {
+#pragma unroll
+      for (int c = 0; c < w; ++c) {
+        const uint32_t a1 = hi[c], b1 = hi[c + w];
+        lo[c] = umax3(min(a1, b1), lo[c], lo[c + w]);
+        hi[c] = max(a1, b1);
+      }
+    }
+    l2_fold_tile<true>(s, hi[0], lo[0], t);
+  }
+}
+
+// merge another warp's partial (other column quarter): order = score desc, global column asc
+__device__ __forceinline__ bool l2_before(uint32_t ka, int ta, uint32_t kb, int tb) {
+  const uint32_t sa = ka >> 7, sb = kb >> 7;
+  if (sa != sb) return sa > sb;
+  const int ca = ta * 32 + 31 - (int)(ka & 127u), cb = tb * 32 + 31 - (int)(kb & 127u);
+  return ca < cb;
+}
+__device__ __forceinline__ void l2_insert(L2Top& s, uint32_t k, int t) {
+  if (t < 0) return;
+  if (s.t1 < 0 || l2_before(k, t, s.k1, s.t1)) {
+    s.k2 = s.k1; s.t2 = s.t1; s.k1 = k; s.t1 = t;
+  } else if (s.t2 < 0 || l2_before(k, t, s.k2, s.t2)) {
+    s.k2 = k; s.t2 = t;
+  }
 }
 
 // TOP2 = false: cross-check matching needs only the nearest neighbour of every row (in both
-// directions), which halves the number of threshold hits and shortens the hit path.
-template <bool TOP2>
+// directions).  Persistent: CTA c handles work items c, c + gridDim.x, ...
+template <bool TOP2, bool ADDM>
 __global__ void __launch_bounds__(L2_THREADS, 1)
 l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ pairs, int nblk,
-                  int n_splits, L2Ws w) {
+                  int n_splits, int ndir, int n_items, L2Ws w) {
   extern __shared__ uint8_t smem_raw[];
   L2Smem& S = *reinterpret_cast<L2Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int pair = blockIdx.y >> 1, dir = blockIdx.y & 1, split = blockIdx.z;
-  const int fq = pairs[2 * pair + dir], ft = pairs[2 * pair + 1 - dir];
-  const int nq = nkp[fq], nt = nkp[ft];
-  const int rb = blockIdx.x;
-  if (rb * L2_BLK >= nq) return;
-  const int ntile_all = (nt + L2_BLK - 1) / L2_BLK;
-  const int per = (ntile_all + n_splits - 1) / n_splits;
-  const int t_lo = split * per, t_hi = min(ntile_all, t_lo + per);
-  const int ntile = max(t_hi - t_lo, 0);
+  const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
 
   if (threadIdx.x == 0) {
     mbar_init(&S.full_a, 1);
+    mbar_init(&S.empty_a, 1);
     for (int s = 0; s < L2_NSTAGE; ++s) { mbar_init(&S.full_b[s], 1); mbar_init(&S.empty_b[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&S.tmem_full[s], 1); mbar_init(&S.tmem_empty[s], L2_EPI_WARPS); }
     fence_barrier_init();
   }
-  if (warp == L2_EPI_WARPS) tc::tmem_alloc(&S.tmem_base, 256);
+  if (warp == L2_EPI_WARPS) tc::tmem_alloc(&S.tmem_base, 512);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = S.tmem_base;
-  const float NEG_INF = __int_as_float(0xff800000);
   const int dbg = g_l2_debug;
 
   if (warp == L2_EPI_WARPS + 1) {
-    // ===== TMA producer: one 40 KB bulk copy per tile =====
-    if (lane == 0 && ntile > 0) {
-      mbar_expect_tx(&S.full_a, L2_TILE_BYTES);
-      bulk_g2s(S.A, w.tiles + ((size_t)fq * nblk + rb) * L2_TILE_ELEMS, L2_TILE_BYTES, &S.full_a);
-      for (int t = 0; t < ntile; ++t) {
-        const int st = t % L2_NSTAGE;
-        mbar_wait(&S.empty_b[st], ((t / L2_NSTAGE) & 1) ^ 1);
-        if ((dbg & 1) && t >= L2_NSTAGE) { tc::mbar_arrive(&S.full_b[st]); continue; }
-        mbar_expect_tx(&S.full_b[st], L2_TILE_BYTES);
-        bulk_g2s(S.B[st], w.tiles + ((size_t)ft * nblk + t_lo + t) * L2_TILE_ELEMS, L2_TILE_BYTES,
-                 &S.full_b[st]);
+    // ===== TMA producer: A blocks once per item, one 40 KB bulk copy per B tile =====
+    if (lane == 0) {
+      uint32_t g = 0, n_it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const L2Item it = l2_item(item, nkp, pairs, nblk, nrbp, n_splits, ndir);
+        if (it.ntile == 0) continue;
+        mbar_wait(&S.empty_a, (n_it & 1) ^ 1);     // MMAs of the previous item are done with A
+        mbar_expect_tx(&S.full_a, (uint32_t)it.nrb * L2_TILE_BYTES);
+        for (int k = 0; k < it.nrb; ++k)
+          bulk_g2s(S.A[k], w.tiles + ((size_t)it.fq * nblk + it.rbp * L2_RBK + k) * L2_TILE_ELEMS,
+                   L2_TILE_BYTES, &S.full_a);
+        for (int t = 0; t < it.ntile; ++t, ++g) {
+          const int st = g % L2_NSTAGE;
+          mbar_wait(&S.empty_b[st], ((g / L2_NSTAGE) & 1) ^ 1);
+          if ((dbg & 1) && g >= L2_NSTAGE) { tc::mbar_arrive(&S.full_b[st]); continue; }
+          mbar_expect_tx(&S.full_b[st], L2_TILE_BYTES);
+          bulk_g2s(S.B[st], w.tiles + ((size_t)it.ft * nblk + it.t_lo + t) * L2_TILE_ELEMS,
+                   L2_TILE_BYTES, &S.full_b[st]);
+        }
+        ++n_it;
       }
     }
   } else if (warp == L2_EPI_WARPS) {
-    // ===== MMA issuer: one thread, 9 x (128x128x16) per tile, accumulator double-buffered =====
-    if (lane == 0 && ntile > 0) {
+    // ===== MMA issuer: one thread, nrb x 9 x (128x128x16) per B tile, accumulators double-buffered
+    if (lane == 0) {
       const uint32_t idesc = tc::idesc_bf16_f32(L2_BLK, L2_BLK);
-      mbar_wait(&S.full_a, 0);
-      const uint32_t a_addr = smem_u32(S.A);
-      for (int t = 0; t < ntile; ++t) {
-        const int st = t % L2_NSTAGE, as = t & 1;
-        mbar_wait(&S.full_b[st], (t / L2_NSTAGE) & 1);
-        mbar_wait(&S.tmem_empty[as], ((t >> 1) & 1) ^ 1);
-        tc::fence_after_sync();
-        const uint32_t b_addr = smem_u32(S.B[st]);
+      uint32_t g = 0, n_it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const L2Item it = l2_item(item, nkp, pairs, nblk, nrbp, n_splits, ndir);
+        if (it.ntile == 0) continue;
+        mbar_wait(&S.full_a, n_it & 1);
+        for (int t = 0; t < it.ntile; ++t, ++g) {
+          const int st = g % L2_NSTAGE, as = g & 1;
+          mbar_wait(&S.full_b[st], (g / L2_NSTAGE) & 1);
+          mbar_wait(&S.tmem_empty[as], ((g >> 1) & 1) ^ 1);
+          tc::fence_after_sync();
+          const uint32_t b_addr = smem_u32(S.B[st]);
+          for (int rb = 0; rb < it.nrb; ++rb) {
+            const uint32_t a_addr = smem_u32(S.A[rb]);
+            const uint32_t d_addr = tmem + as * (L2_RBK * L2_BLK) + rb * L2_BLK;
 #pragma unroll
-        for (int k = 0; k < 9; ++k) {
-          // steps 0..7: descriptor columns; step 8: A extras (kg16,17) x B extras (kg18,19)
-          const uint32_t ao = (k < 8) ? k * 2 * L2_LBO : 16 * L2_LBO;
-          const uint32_t bo = (k < 8) ? k * 2 * L2_LBO : 18 * L2_LBO;
-          tc::mma_bf16(tmem + as * L2_BLK, tc::smem_desc(a_addr + ao, L2_LBO, L2_SBO),
-                       tc::smem_desc(b_addr + bo, L2_LBO, L2_SBO), idesc, k > 0);
+            for (int k = 0; k < 9; ++k) {
+              // steps 0..7: descriptor columns; step 8: A extras (kg16,17) x B extras (kg18,19)
+              const uint32_t ao = (k < 8) ? k * 2 * L2_LBO : 16 * L2_LBO;
+              const uint32_t bo = (k < 8) ? k * 2 * L2_LBO : 18 * L2_LBO;
+              tc::mma_bf16(d_addr, tc::smem_desc(a_addr + ao, L2_LBO, L2_SBO),
+                           tc::smem_desc(b_addr + bo, L2_LBO, L2_SBO), idesc, k > 0);
+            }
+          }
+          tc::commit(&S.empty_b[st]);     // smem stage reusable once these MMAs retire
+          tc::commit(&S.tmem_full[as]);   // accumulators ready for the epilogue
         }
-        tc::commit(&S.empty_b[st]);     // smem stage reusable once these MMAs retire
-        tc::commit(&S.tmem_full[as]);   // accumulator ready for the epilogue
+        tc::commit(&S.empty_a);           // A blocks reusable
+        ++n_it;
       }
     }
   } else {
-    // ===== epilogue warps 0..7: thread = TMEM lane = query row, warp/4 = column half ==========
-    // running top-2 of  a.b - |b|^2/2  (largest = nearest), 64 columns per TMEM load
-    const int quarter = warp & 3, cq = warp >> 2;   // TMEM lane quarter, column quarter
+    // ===== epilogue warps 0..15: thread = TMEM lane = query row, warp/4 = 32-column quarter ====
+    const int quarter = warp & 3, cq = warp >> 2;
     const int rl = quarter * 32 + lane;
-    const int row = rb * L2_BLK + rl;
-    float s1 = NEG_INF, s2 = NEG_INF;
-    int i1 = -1, i2 = -1;
-    for (int t = 0; t < ntile; ++t) {
-      const int as = t & 1;
-      mbar_wait(&S.tmem_full[as], (t >> 1) & 1);
-      tc::fence_after_sync();
-      const int c0 = (t_lo + t) * L2_BLK + cq * 32;
-      float v[32];
-      if (dbg & 4) {
+    const uint32_t mul = 128u + (uint32_t)(n_items < 0);   // = 128, opaque to the compiler
+    const float inv_s2 = 1.f / (l2_scale(w.flags) * l2_scale(w.flags));
+    uint32_t g = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const L2Item it = l2_item(item, nkp, pairs, nblk, nrbp, n_splits, ndir);
+      if (it.nrb == 0) continue;
+      L2Top st[L2_RBK];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) v[c] = NEG_INF;
-      } else {
-        tc::ld_32x32(tmem + ((uint32_t)(quarter * 32) << 16) + as * L2_BLK + cq * 32, v);
+      for (int rb = 0; rb < L2_RBK; ++rb) { st[rb].k1 = st[rb].k2 = 0u; st[rb].t1 = st[rb].t2 = -1; }
+      for (int t = 0; t < it.ntile; ++t, ++g) {
+        const int as = g & 1;
+        mbar_wait(&S.tmem_full[as], (g >> 1) & 1);
+        tc::fence_after_sync();
+        const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + as * (L2_RBK * L2_BLK) + cq * 32;
+        uint32_t v0[32], v1[32];
+        const int tcol = (it.t_lo + t) * 4 + cq;   // chunk number
+        if (dbg & 4) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) v0[c] = v1[c] = L2_MAGIC_BITS;
+          tc::fence_before_sync();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);
+          if (dbg & 2) continue;
+          l2_rank_chunk<TOP2, ADDM>(st[0], v0, mul, tcol);
+          l2_rank_chunk<TOP2, ADDM>(st[1], v1, mul, tcol);
+          continue;
+        }
+        // block 0 is ranked while the load of block 1 is in flight (block 1's TMEM columns always
+        // exist; their content is ignored when the item has a single row block)
+        tc::ld_32x32_issue(taddr, v0);
+        tc::ld_wait(v0);
+        tc::ld_32x32_issue(taddr + L2_BLK, v1);
+        if (!(dbg & 2)) l2_rank_chunk<TOP2, ADDM>(st[0], v0, mul, tcol);
+        tc::ld_wait(v1);
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);   // both accumulators are in registers
+        if (!(dbg & 2) && it.nrb == 2) l2_rank_chunk<TOP2, ADDM>(st[1], v1, mul, tcol);
       }
-      tc::fence_before_sync();
-      __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);   // values are in registers now
-      if (dbg & 2) continue;
-      // group-of-8 prefilter (7 FMNMX + 1 branch).  With 32 independent rows per warp some lane
-      // almost always hits, so the hit path is kept short: locate the first occurrence of the
-      // group maximum, insert it, knock it out, re-test (a second hit in one group is rare).
+      // ---- merge the four column quarters of every row, convert, write ----
+      if (cq > 0) {
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float* x = &v[8 * g];
-        float m = fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])),
-                        fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7])));
-        if (TOP2) {
-          while (m > s2) {
-            int pos = 7;
+        for (int rb = 0; rb < L2_RBK; ++rb)
+          S.part[cq - 1][rb][rl] = make_uint4(st[rb].k1, (uint32_t)st[rb].t1, st[rb].k2, (uint32_t)st[rb].t2);
+      }
+      asm volatile("bar.sync 1, 512;" ::: "memory");   // the 16 epilogue warps only
+      if (cq == 0) {
 #pragma unroll
-            for (int k = 6; k >= 0; --k) pos = (x[k] == m) ? k : pos;
-            top2_insert(m, c0 + 8 * g + pos, s1, i1, s2, i2);
+        for (int rb = 0; rb < L2_RBK; ++rb) {
+          if (rb >= it.nrb) break;
+          L2Top m = st[rb];
+          if (m.t2 >= 0 && m.t1 < 0) { m.k1 = m.k2; m.t1 = m.t2; m.t2 = -1; }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) x[k] = (k == pos) ? NEG_INF : x[k];
-            m = fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])),
-                      fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7])));
+          for (int p = 0; p < 3; ++p) {
+            const uint4 o = S.part[p][rb][rl];
+            l2_insert(m, o.x, (int)o.y);
+            if (TOP2) l2_insert(m, o.z, (int)o.w);
           }
-        } else if (m > s1) {
-          int pos = 7;
-#pragma unroll
-          for (int k = 6; k >= 0; --k) pos = (x[k] == m) ? k : pos;
-          s1 = m;
-          i1 = c0 + 8 * g + pos;
+          const int row = (it.rbp * L2_RBK + rb) * L2_BLK + rl;
+          if (row < it.nq) {
+            // d^2 = |a|^2 - 2 (a.b - |b|^2/2); exact for integer descriptors
+            const float na = w.norms[(size_t)it.fq * nblk * L2_BLK + row];
+            int c1 = m.t1 >= 0 ? m.t1 * 32 + 31 - (int)(m.k1 & 127u) : -1;
+            int c2 = (TOP2 && m.t2 >= 0) ? m.t2 * 32 + 31 - (int)(m.k2 & 127u) : -1;
+            if (c1 >= it.nt) c1 = -1;     // padded column (only when fewer real columns exist)
+            if (c2 >= it.nt) c2 = -1;
+            const float x1 = (float)((int)(m.k1 >> 7) - (int)L2_QBIAS);   // 2 s^2 (a.b - |b|^2/2)
+            const float x2 = (float)((int)(m.k2 >> 7) - (int)L2_QBIAS);
+            float4 r;
+            r.x = c1 >= 0 ? fmaxf(fmaf(-x1, inv_s2, na), 0.f) : __int_as_float(0x7f800000);
+            r.y = __int_as_float(c1);
+            r.z = c2 >= 0 ? fmaxf(fmaf(-x2, inv_s2, na), 0.f) : __int_as_float(0x7f800000);
+            r.w = __int_as_float(c2);
+            w.rowbest[(((size_t)it.pair * 2 + it.dir) * n_splits + it.split) * nblk * L2_BLK + row] = r;
+          }
         }
       }
-    }
-    if (cq > 0) S.part[cq - 1][rl] = make_float4(s1, __int_as_float(i1), s2, __int_as_float(i2));
-    asm volatile("bar.sync 1, 512;" ::: "memory");   // the 16 epilogue warps only
-    if (cq == 0) {
-      // merge the other column quarters; equal scores keep the lower column index
-#pragma unroll
-      for (int p = 0; p < 3; ++p) {
-        const float4 o = S.part[p][rl];
-        const int a = __float_as_int(o.y), b = __float_as_int(o.w);
-        if (a >= 0 && (o.x > s2 || (o.x == s2 && (i2 < 0 || a < i2)))) {
-          if (o.x > s1 || (o.x == s1 && (i1 < 0 || a < i1))) { s2 = s1; i2 = i1; s1 = o.x; i1 = a; }
-          else { s2 = o.x; i2 = a; }
-        }
-        if (b >= 0 && (o.z > s2 || (o.z == s2 && (i2 < 0 || b < i2)))) {
-          if (o.z > s1 || (o.z == s1 && (i1 < 0 || b < i1))) { s2 = s1; i2 = i1; s1 = o.z; i1 = b; }
-          else { s2 = o.z; i2 = b; }
-        }
-      }
-      if (row < nq) {
-        // d^2 = |a|^2 - 2 (a.b - |b|^2/2); exact for integer descriptors
-        const float na = w.norms[(size_t)fq * nblk * L2_BLK + row];
-        float4 r;
-        r.x = i1 >= 0 ? fmaxf(fmaf(-2.f, s1, na), 0.f) : __int_as_float(0x7f800000);
-        r.y = __int_as_float(i1);
-        r.z = i2 >= 0 ? fmaxf(fmaf(-2.f, s2, na), 0.f) : __int_as_float(0x7f800000);
-        r.w = __int_as_float(i2);
-        w.rowbest[(((size_t)pair * 2 + dir) * n_splits + split) * nblk * L2_BLK + row] = r;
-      }
+      asm volatile("bar.sync 1, 512;" ::: "memory");   // part[] may be overwritten by the next item
     }
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == L2_EPI_WARPS) tc::tmem_dealloc(tmem, 256);
+  if (warp == L2_EPI_WARPS) tc::tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------ fp32 rerank (non-integer data)
@@ -306,9 +497,9 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
 // sum of squared differences) and re-order them.  One warp per row.
 __global__ void __launch_bounds__(256)
 l2_rerank_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
-                 const int32_t* __restrict__ pairs, int nblk, int n_splits, L2Ws w) {
-  if (*w.inexact == 0) return;
-  const int pair = blockIdx.y >> 1, dir = blockIdx.y & 1;
+                 const int32_t* __restrict__ pairs, int nblk, int n_splits, int ndir, L2Ws w) {
+  if (w.flags[0] == 0) return;
+  const int pair = blockIdx.y / ndir, dir = blockIdx.y % ndir;
   const int fq = pairs[2 * pair + dir], ft = pairs[2 * pair + 1 - dir];
   const int nq = nkp[fq];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -424,15 +615,30 @@ l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp,
 
 using namespace vo;
 
-static int l2_pick_splits(int n_pairs, int nblk) {
-  const long ctas = (long)n_pairs * 2 * nblk;
-  int s = (int)((148L * 2 + ctas - 1) / ctas);
+static int l2_num_sms() {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
+  return sms;
+}
+
+// column splits only when there are too few (pair, direction, 256-row block) items to give every
+// SM at least one
+static int l2_pick_splits(int n_pairs, int ndir, int nblk) {
+  const long items = (long)n_pairs * ndir * ((nblk + L2_RBK - 1) / L2_RBK);
+  int s = (int)((l2_num_sms() + items - 1) / items);
   if (s > nblk) s = nblk;
   if (s > 8) s = 8;
   return s < 1 ? 1 : s;
 }
 
+static int g_l2_debug_host = 0;
 extern "C" int vo_debug_l2(int flags) {
+  g_l2_debug_host = flags;
   return cudaMemcpyToSymbol(g_l2_debug, &flags, sizeof(int)) == cudaSuccess ? VO_OK : VO_ERR_CUDA;
 }
 
@@ -458,30 +664,34 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   if (n_pairs == 0) return VO_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int nblk = (n_cap + L2_BLK - 1) / L2_BLK;
-  const int splits = l2_pick_splits(n_pairs, nblk);
+  const int ndir = (mode == VO_MATCH_MUTUAL) ? 2 : 1;   // knn + ratio needs query -> train only
+  const int splits = l2_pick_splits(n_pairs, ndir, nblk);
   L2Ws w = l2_carve(ws, n_frames, n_pairs, n_cap, splits);
-  cudaMemsetAsync(w.inexact, 0, sizeof(int32_t), st);
-  l2_prep_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
+  cudaMemsetAsync(w.flags, 0, 2 * sizeof(int32_t), st);
+  l2_norm_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
+  l2_tile_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
+  typedef void (*L2Kernel)(const int32_t*, const int32_t*, int, int, int, int, L2Ws);
+  static const L2Kernel kernels[4] = {l2_top2_tc_kernel<false, false>, l2_top2_tc_kernel<true, false>,
+                                      l2_top2_tc_kernel<false, true>, l2_top2_tc_kernel<true, true>};
   static bool attr_set = false;
   const int smem = (int)sizeof(L2Smem) + 1024;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(l2_top2_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             smem) != cudaSuccess ||
-        cudaFuncSetAttribute(l2_top2_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             smem) != cudaSuccess)
-      return check_launch("vo_match_l2_batch(smem attribute)");
+    for (int k = 0; k < 4; ++k)
+      if (cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
+          cudaSuccess)
+        return check_launch("vo_match_l2_batch(smem attribute)");
     attr_set = true;
   }
   {
     ProfScope prof(2, st);
-    const dim3 grid(nblk, n_pairs * 2, splits);
-    if (mode == VO_MATCH_MUTUAL)
-      l2_top2_tc_kernel<false><<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, w);
-    else
-      l2_top2_tc_kernel<true><<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, w);
+    const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
+    const long n_items = (long)n_pairs * ndir * splits * nrbp;
+    const int grid = (int)(n_items < l2_num_sms() ? n_items : l2_num_sms());
+    const int which = (mode == VO_MATCH_MUTUAL ? 0 : 1) + ((g_l2_debug_host & 8) ? 2 : 0);
+    kernels[which]<<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, ndir, (int)n_items, w);
   }
-  l2_rerank_kernel<<<dim3((n_cap + 7) / 8, n_pairs * 2), 256, 0, st>>>(desc, nkp, n_cap, pairs, nblk,
-                                                                     splits, w);
+  l2_rerank_kernel<<<dim3((n_cap + 7) / 8, n_pairs * ndir), 256, 0, st>>>(desc, nkp, n_cap, pairs,
+                                                                        nblk, splits, ndir, w);
   l2_compact_kernel<<<n_pairs, L2C_THREADS, 0, st>>>(nkp, kp, n_cap, pairs, nblk, splits, mode, ratio,
                                                     w, q, t, dist, t2, dist2, pts, n_out);
   return check_launch("vo_match_l2_batch");
