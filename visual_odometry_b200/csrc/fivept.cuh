@@ -26,6 +26,7 @@ struct FiveptSmem {
   double A[10][21];    // constraint matrix, 20 monomials (+1 pad)
   double B[9][5];      // B(z) entries, ascending powers of z
   double poly[11];     // det B(z), ascending
+  double2 zs[10];      // current root estimates (Aberth), broadcast to all lanes
 };
 
 // index of the degree-2 monomial v_a*v_b among the 10 of (x,y,z,w); compile-time when unrolled
@@ -42,6 +43,14 @@ __constant__ int c_COL3[10][4] = {{0, 2, 4, 5},     {2, 3, 8, 9},     {4, 8, 10,
                                   {9, 7, 14, 15},   {10, 13, 16, 17}, {11, 14, 17, 18},
                                   {12, 15, 18, 19}};
 
+__host__ __device__ constexpr int col3(int m, int c) {
+  constexpr int T[10][4] = {{0, 2, 4, 5},     {2, 3, 8, 9},     {4, 8, 10, 11},
+                            {5, 9, 11, 12},   {3, 1, 6, 7},     {8, 6, 13, 14},
+                            {9, 7, 14, 15},   {10, 13, 16, 17}, {11, 14, 17, 18},
+                            {12, 15, 18, 19}};
+  return T[m][c];
+}
+
 struct cplx {
   double re, im;
 };
@@ -51,6 +60,23 @@ __device__ __forceinline__ cplx cmul(cplx a, cplx b) {
 __device__ __forceinline__ cplx cdiv(cplx a, cplx b) {
   const double d = b.re * b.re + b.im * b.im;
   return {(a.re * b.re + a.im * b.im) / d, (a.im * b.re - a.re * b.im) / d};
+}
+
+// fast fp64 reciprocal (MUFU.RCP64H, ~2^-23 relative) and the same refined by one Newton step
+// (~2^-46).  Only used inside the Aberth iteration, whose fixed points (p(z) = 0) do not depend on
+// how accurately the correction is evaluated; every root is re-polished in full fp64 afterwards.
+__device__ __forceinline__ double rcp_fast(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  return r;
+}
+__device__ __forceinline__ double rcp_mid(double x) {
+  const double r = rcp_fast(x);
+  return r * (2.0 - x * r);
+}
+__device__ __forceinline__ cplx cdiv_mid(cplx a, cplx b) {
+  const double inv = rcp_mid(b.re * b.re + b.im * b.im);
+  return {(a.re * b.re + a.im * b.im) * inv, (a.im * b.re - a.re * b.im) * inv};
 }
 
 // degree-1 polynomial of E[r][c] in (x,y,z,w): coefficient v is basis[v][3r+c]
@@ -155,23 +181,30 @@ __device__ int fivept_solve_warp(const double* __restrict__ p5, FiveptSmem& S,
     }
     S.P2[p][m] = v;
   }
-  for (int e = lane; e < 210; e += 32) (&S.A[0][0])[e] = 0.0;
   __syncwarp();
 
-  // ---- 3b. ten cubic rows: rows 0..8 = (Lambda E)[i][j], row 9 = det E
+  // ---- 3b. ten cubic rows: rows 0..8 = (Lambda E)[i][j], row 9 = det E.  The row lives in
+  // registers (column indices are compile-time after unrolling) and is stored once.
   if (lane < 10) {
     const int i = lane / 3, j = lane % 3;
+    double row[20];
+#pragma unroll
+    for (int c = 0; c < 20; ++c) row[c] = 0.0;
+#pragma unroll
     for (int k = 0; k < 3; ++k) {
       const double* d2 = (lane < 9) ? S.P2[3 * i + k] : S.P2[9 + k];
       double d1[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) d1[c] = (lane < 9) ? E1(S, c, k, j) : E1(S, c, 0, k);
+#pragma unroll
       for (int m = 0; m < 10; ++m) {
         const double a = d2[m];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) S.A[lane][c_COL3[m][c]] += a * d1[c];
+        for (int c = 0; c < 4; ++c) row[col3(m, c)] += a * d1[c];
       }
     }
+#pragma unroll
+    for (int c = 0; c < 20; ++c) S.A[lane][c] = row[c];
   }
   __syncwarp();
 
@@ -285,21 +318,24 @@ __device__ int fivept_solve_warp(const double* __restrict__ p5, FiveptSmem& S,
       p = cmul(p, z);
       p.re += mc[k];
     }
-    const cplx nt = cdiv(p, dp);
+    const cplx nt = cdiv_mid(p, dp);
+    __syncwarp();
+    if (lane < 10) S.zs[lane] = make_double2(z.re, z.im);
+    __syncwarp();
     cplx s = {0.0, 0.0};
 #pragma unroll
     for (int j = 0; j < 10; ++j) {
-      const double ore = __shfl_sync(FULL, z.re, j), oim = __shfl_sync(FULL, z.im, j);
-      if (j != slot) {
-        const cplx d = {z.re - ore, z.im - oim};
-        const double dd = d.re * d.re + d.im * d.im;
-        s.re += d.re / dd;
-        s.im -= d.im / dd;
-      }
+      const double2 o = S.zs[j];
+      const double dre = z.re - o.x, dim = z.im - o.y;
+      // own slot: d = 0 -> contributes nothing (inv is forced to 0)
+      const double dd = dre * dre + dim * dim;
+      const double inv = (j != slot) ? rcp_fast(dd) : 0.0;
+      s.re += dre * inv;
+      s.im -= dim * inv;
     }
     cplx den = cmul(nt, s);
     den.re = 1.0 - den.re; den.im = -den.im;
-    const cplx w = cdiv(nt, den);
+    const cplx w = cdiv_mid(nt, den);
     const bool fin = isfinite(w.re) && isfinite(w.im);
     if (fin) { z.re -= w.re; z.im -= w.im; }
     const bool ok = !fin || (w.re * w.re + w.im * w.im <= 1e-24 * (z.re * z.re + z.im * z.im));

@@ -243,14 +243,42 @@ extern "C" size_t vo_match_workspace_bytes(int n_pairs, int n_cap) {
   return (size_t)n_pairs * n_cap * (16 * 2 + 1) * sizeof(uint32_t);
 }
 
-static int pick_splits(int n_pairs, int qtiles, int n_cap) {
+// Train-range splits serve two purposes: filling the SMs when there are few (pair, query tile)
+// CTAs, and avoiding a mostly empty last wave when there are many: the split count with the best
+// wave efficiency  waves / ceil(waves)  wins (each extra split costs ~1.5 % in partial merges).
+static int pick_splits(int n_pairs, int qtiles, int n_cap, int resident_ctas) {
   const long ctas = (long)n_pairs * qtiles;
-  int s = (int)((148L * 4 + ctas - 1) / ctas);
   const int max_s = (n_cap + HM_TT - 1) / HM_TT;
-  if (s > 16) s = 16;
-  if (s > max_s) s = max_s;
-  if (s < 1) s = 1;
-  return s;
+  if (ctas * 4 <= resident_ctas) {           // tiny batch: spread over the SMs
+    int s = (int)((resident_ctas + ctas - 1) / ctas);
+    if (s > 16) s = 16;
+    if (s > max_s) s = max_s;
+    return s < 1 ? 1 : s;
+  }
+  int best = 1;
+  double best_eff = -1.0;
+  for (int s = 1; s <= 4 && s <= max_s; ++s) {
+    const double waves = (double)(ctas * s) / resident_ctas;
+    const double full = (double)((ctas * s + resident_ctas - 1) / resident_ctas);
+    const double eff = waves / full - 0.015 * (s - 1);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+  }
+  return best;
+}
+
+template <int RQ>
+static int hamming_resident_ctas() {
+  static int cached = 0;
+  if (!cached) {
+    int dev = 0, sms = 148, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hamming_top2_kernel<RQ>, HM_THREADS,
+                                                      0) != cudaSuccess || per_sm <= 0)
+      per_sm = 4;
+    cached = sms * per_sm;
+  }
+  return cached;
 }
 
 static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, int n2d,
@@ -262,7 +290,8 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
   const bool small = (long)n_pairs * ((n_cap + 511) / 512) < 148L * 4;
   const int rq = small ? 1 : 4;
   const int qtiles = (n_cap + HM_THREADS * rq - 1) / (HM_THREADS * rq);
-  const int splits = pick_splits(n_pairs, qtiles, n_cap);
+  const int splits = pick_splits(n_pairs, qtiles, n_cap, rq == 1 ? hamming_resident_ctas<1>()
+                                                                 : hamming_resident_ctas<4>());
   uint32_t* rowbest = (uint32_t*)ws;  // 8-byte aligned (uint2 access); colmin sits behind it
   uint32_t* colmin = rowbest + (size_t)n_pairs * n_cap * 32;
   cudaMemsetAsync(colmin, 0xff, (size_t)n_pairs * n_cap * sizeof(uint32_t), st);

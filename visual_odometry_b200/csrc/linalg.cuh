@@ -6,6 +6,18 @@
 
 namespace vo {
 
+__device__ __forceinline__ double rcp_nr(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  return r * (2.0 - x * r);
+}
+__device__ __forceinline__ double sqrt_nr(double x) {   // x >= 1 here
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  y = y * (1.5 - 0.5 * x * y * y);
+  return x * y;
+}
+
 // A (N x N, row-major, modified in place to U*diag(s)); V accumulates the right singular vectors
 // as columns. Column norms of the result are the singular values (unsorted).
 template <int N>
@@ -27,11 +39,16 @@ __device__ __forceinline__ void jacobi_svd(double (&A)[N][N], double (&V)[N][N])
           beta += A[k][q] * A[k][q];
           gamma += A[k][p] * A[k][q];
         }
-        if (fabs(gamma) <= 2.2e-15 * sqrt(alpha * beta)) continue;
+        // |gamma| <= eps * sqrt(alpha * beta), without the square root
+        if (gamma * gamma <= (2.2e-15 * 2.2e-15) * (alpha * beta)) continue;
         changed = true;
-        const double zeta = (beta - alpha) / (2.0 * gamma);
-        const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double c = rsqrt(1.0 + t * t);
+        // The rotation ANGLE only steers convergence, so zeta and t use fast reciprocals /
+        // square roots (MUFU seed + one Newton step, ~2^-45); c = 1/sqrt(1+t^2) is computed to
+        // full precision so that (c, s) stays an exact rotation and V stays orthonormal.
+        const double zeta = (beta - alpha) * 0.5 * rcp_nr(gamma);
+        const double az = fabs(zeta);
+        const double t = copysign(rcp_nr(az + sqrt_nr(fma(zeta, zeta, 1.0))), zeta);
+        const double c = rsqrt(fma(t, t, 1.0));
         const double s = c * t;
 #pragma unroll
         for (int k = 0; k < N; ++k) {

@@ -40,34 +40,51 @@ recover_pose_kernel(const double* __restrict__ E, const double* __restrict__ pts
   const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
   const double P0[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
   uint8_t* fl = flags + (size_t)p * n_cap;
-  int local[4] = {0, 0, 0, 0};
-  // work item = (point, candidate): 4 consecutive threads share a point
-  for (int it = tid; it < 4 * mp; it += POSE_THREADS) {
-    const int i = it >> 2, c = it & 3;
-    bool good = false;
-    if (!mask || mask[(size_t)p * n_cap + i]) {
+  int lp = 0, lm = 0;   // this thread's rotation index is fixed: c = tid & 1
+  // work item = (point, rotation c in {0,1}): candidates c and c+2 differ only in the sign of t,
+  // and [R|-t] has the DLT matrix of [R|t] with its fourth column negated, so its null vector is
+  // (Q0,Q1,Q2,-Q3): ONE 4x4 SVD serves both.  2 consecutive threads share a point.
+  const int n_items = 2 * mp;
+  for (int it0 = 0; it0 < n_items; it0 += POSE_THREADS) {
+    const int it = it0 + tid;
+    const int i = it >> 1, c = it & 1;
+    bool good_p = false, good_m = false;
+    if (it < n_items && (!mask || mask[(size_t)p * n_cap + i])) {
       const double4 v = reinterpret_cast<const double4*>(pts)[(size_t)p * n_cap + i];
       const double x1 = (v.x - cx) / fx, y1 = (v.y - cy) / fy;
       const double x2 = (v.z - cx) / fx, y2 = (v.w - cy) / fy;
       double Q[4];
       dlt_point(P0, sP[c], x1, y1, x2, y2, Q);
-      good = (Q[2] * Q[3]) > 0;
-      const double qx = Q[0] / Q[3], qy = Q[1] / Q[3], qz = Q[2] / Q[3];
-      good = good && (qz < dist);
-      // Q = P1 * Q with Q[3] = w/w = 1
       const double* P = sP[c];
-      const double z2 = ((P[8] * qx + P[9] * qy) + P[10] * qz) + P[11] * (Q[3] / Q[3]);
-      good = good && (z2 > 0) && (z2 < dist);
+      {  // candidate c: [R | +t]
+        good_p = (Q[2] * Q[3]) > 0;
+        const double qx = Q[0] / Q[3], qy = Q[1] / Q[3], qz = Q[2] / Q[3];
+        good_p = good_p && (qz < dist);
+        // Q = P1 * Q with Q[3] = w/w = 1
+        const double z2 = ((P[8] * qx + P[9] * qy) + P[10] * qz) + P[11] * (Q[3] / Q[3]);
+        good_p = good_p && (z2 > 0) && (z2 < dist);
+      }
+      {  // candidate c+2: [R | -t], null vector (Q0,Q1,Q2,-Q3)
+        const double w = -Q[3];
+        good_m = (Q[2] * w) > 0;
+        const double qx = Q[0] / w, qy = Q[1] / w, qz = Q[2] / w;
+        good_m = good_m && (qz < dist);
+        const double z2 = ((P[8] * qx + P[9] * qy) + P[10] * qz) + (-P[11]) * (w / w);
+        good_m = good_m && (z2 > 0) && (z2 < dist);
+      }
     }
-    // gather the 4 candidate bits of this point into its first lane and store them
+    // gather the 4 candidate bits of this point into its even lane and store them
     const unsigned lane = tid & 31;
-    const unsigned bal = __ballot_sync(__activemask(), good);
-    if (c == 0) fl[i] = (uint8_t)((bal >> lane) & 0xfu);
-    local[c] += good;
+    const unsigned bal_p = __ballot_sync(0xffffffffu, good_p);
+    const unsigned bal_m = __ballot_sync(0xffffffffu, good_m);
+    if (c == 0 && it < n_items)
+      fl[i] = (uint8_t)(((bal_p >> lane) & 3u) | (((bal_m >> lane) & 3u) << 2));
+    lp += good_p;
+    lm += good_m;
   }
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
-    int v = local[c];
+    int v = ((tid & 1) == (c & 1)) ? (c < 2 ? lp : lm) : 0;
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if ((tid & 31) == 0 && v) atomicAdd(&cnt[c], v);
   }
@@ -173,24 +190,78 @@ triangulate_pairs_kernel(const double* __restrict__ R, const double* __restrict_
   if (tid == 0) n_x[p] = base_s;
 }
 
-// P_0 given (or I); P_k = rel_k * P_{k-1}, rel_k = [R_{k-1} t_{k-1}; 0 1]
-__global__ void chain_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
-                             const double* __restrict__ P0, double* __restrict__ poses) {
-  if (blockIdx.x || threadIdx.x) return;
-  double P[12];
-  for (int e = 0; e < 12; ++e) P[e] = P0 ? P0[e] : ((e % 5 == 0) ? 1.0 : 0.0);
-  for (int e = 0; e < 12; ++e) poses[e] = P[e];
-  poses[12] = poses[13] = poses[14] = 0.0; poses[15] = 1.0;
-  for (int k = 0; k < n; ++k) {
-    const double* Rk = R + (size_t)k * 9;
-    const double* tk = t + (size_t)k * 3;
-    double Q[12];
-    for (int i = 0; i < 3; ++i)
-      for (int j = 0; j < 4; ++j)
-        Q[4 * i + j] = Rk[3 * i] * P[j] + Rk[3 * i + 1] * P[4 + j] + Rk[3 * i + 2] * P[8 + j] +
-                       (j == 3 ? tk[i] : 0.0);
+// P_0 given (or I); P_k = rel_k * P_{k-1}, rel_k = [R_{k-1} t_{k-1}; 0 1].
+// SE(3) composition is associative, so the chain is a prefix product: every thread multiplies a
+// contiguous run of CHAIN_RUN relative poses, the run totals are scanned across the block
+// (Hillis-Steele in shared memory), and each thread replays its run from its carried-in prefix.
+// The multiplication order inside every product is the sequential one (rel_k on the left of the
+// accumulated pose), so results differ from a serial loop only by fp64 re-association (~1e-16).
+constexpr int CHAIN_THREADS = 128;
+struct Rt { double m[12]; };   // [R|t] row-major 3x4
+
+// out = a * b  (a applied after b): R = Ra Rb, t = Ra tb + ta
+__device__ __forceinline__ Rt rt_mul(const Rt& a, const Rt& b) {
+  Rt o;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      o.m[4 * i + j] = a.m[4 * i] * b.m[j] + a.m[4 * i + 1] * b.m[4 + j] + a.m[4 * i + 2] * b.m[8 + j] +
+                       (j == 3 ? a.m[4 * i + 3] : 0.0);
+  return o;
+}
+__device__ __forceinline__ Rt rt_load(const double* __restrict__ R, const double* __restrict__ t, int k) {
+  Rt o;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) o.m[4 * i + j] = R[(size_t)k * 9 + 3 * i + j];
+    o.m[4 * i + 3] = t[(size_t)k * 3 + i];
+  }
+  return o;
+}
+
+__global__ void __launch_bounds__(CHAIN_THREADS)
+chain_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
+             const double* __restrict__ P0, double* __restrict__ poses) {
+  __shared__ Rt sc[2][CHAIN_THREADS];
+  const int tid = threadIdx.x;
+  const int run = (n + CHAIN_THREADS - 1) / CHAIN_THREADS;
+  const int k0 = tid * run, k1 = min(n, k0 + run);
+  Rt ident;
+#pragma unroll
+  for (int e = 0; e < 12; ++e) ident.m[e] = (e % 5 == 0) ? 1.0 : 0.0;
+  // 1) product of this thread's run: rel_{k1-1} ... rel_{k0}
+  Rt acc = ident;
+  for (int k = k0; k < k1; ++k) acc = rt_mul(rt_load(R, t, k), acc);
+  sc[0][tid] = acc;
+  __syncthreads();
+  // 2) inclusive scan of run totals (later runs multiply on the left)
+  int cur = 0;
+  for (int off = 1; off < CHAIN_THREADS; off <<= 1) {
+    Rt v = sc[cur][tid];
+    if (tid >= off) v = rt_mul(v, sc[cur][tid - off]);
+    sc[cur ^ 1][tid] = v;
+    cur ^= 1;
+    __syncthreads();
+  }
+  // 3) carried-in prefix = P0 composed with everything before this run
+  Rt pre = ident;
+  if (P0) {
+#pragma unroll
+    for (int e = 0; e < 12; ++e) pre.m[e] = P0[e];
+  }
+  if (tid > 0) pre = rt_mul(sc[cur][tid - 1], pre);
+  if (tid == 0) {
+#pragma unroll
+    for (int e = 0; e < 12; ++e) poses[e] = pre.m[e];
+    poses[12] = poses[13] = poses[14] = 0.0; poses[15] = 1.0;
+  }
+  for (int k = k0; k < k1; ++k) {
+    pre = rt_mul(rt_load(R, t, k), pre);
     double* o = poses + (size_t)(k + 1) * 16;
-    for (int e = 0; e < 12; ++e) { P[e] = Q[e]; o[e] = Q[e]; }
+#pragma unroll
+    for (int e = 0; e < 12; ++e) o[e] = pre.m[e];
     o[12] = o[13] = o[14] = 0.0; o[15] = 1.0;
   }
 }
@@ -241,6 +312,6 @@ extern "C" int vo_triangulate_pairs(const double* R, const double* t, const doub
 extern "C" int vo_chain_poses(const double* R, const double* t, int n_pairs, const double* P0,
                               double* poses, void* stream) {
   VO_REQUIRE(R && t && poses && n_pairs >= 0, VO_ERR_INVALID_ARG, "vo_chain_poses: bad arguments");
-  chain_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(R, t, n_pairs, P0, poses);
+  chain_kernel<<<1, CHAIN_THREADS, 0, (cudaStream_t)stream>>>(R, t, n_pairs, P0, poses);
   return check_launch("vo_chain_poses");
 }

@@ -27,13 +27,17 @@ struct RansacWs {
   int32_t* samples;   // [P][C][5]
   int32_t* nmodels;   // [P][C]
   int32_t* counts;    // [P][C][10]
+  int32_t* active;    // [2][P] pairs still iterating (ping-pong between rounds)
+  int32_t* n_active;  // [max_rounds + 1]
+  int max_rounds;
   size_t bytes;
 };
 
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-static RansacWs carve(void* base, int P, int n_cap, int C) {
+static RansacWs carve(void* base, int P, int n_cap, int C, int max_iters) {
   RansacWs w;
+  w.max_rounds = max_iters / C + 8;   // chunks of C, plus the short warm-up rounds
   size_t off = 0;
   auto take = [&](size_t bytes) {
     void* p = base ? (char*)base + off : nullptr;
@@ -49,11 +53,13 @@ static RansacWs carve(void* base, int P, int n_cap, int C) {
   w.samples = (int32_t*)take((size_t)P * C * 5 * sizeof(int32_t));
   w.nmodels = (int32_t*)take((size_t)P * C * sizeof(int32_t));
   w.counts = (int32_t*)take((size_t)P * C * 10 * sizeof(int32_t));
+  w.active = (int32_t*)take((size_t)2 * P * sizeof(int32_t));
+  w.n_active = (int32_t*)take((size_t)(w.max_rounds + 1) * sizeof(int32_t));
   w.bytes = off;
   return w;
 }
 
-constexpr int RANSAC_CHUNK0 = 32;    // first rounds (adaptive runs usually stop inside them)
+constexpr int RANSAC_CHUNK0 = 16;    // first rounds (adaptive runs usually stop inside them)
 constexpr int RANSAC_CHUNK_MAX = 256;
 
 static inline int chunk_cap(int max_iters) {
@@ -101,51 +107,70 @@ __global__ void ransac_init_kernel(const double* __restrict__ pts, const int32_t
     w.niters[p] = max_iters;
     w.maxgood[p] = 0;
     w.done[p] = (mp < 5) ? 1 : 0;
+    if (mp >= 5) w.active[atomicAdd(&w.n_active[0], 1)] = p;
     n_inl[p] = 0;
     status[p] = (mp < 5) ? VO_ERR_TOO_FEW_POINTS : VO_OK;
   }
 }
 
-__global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int n_pairs, int chunk,
-                                     int chunk_stride, RansacWs w) {
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= n_pairs || w.done[p]) return;
-  uint64_t s = w.rng[p];
-  const int count = m[p];
-  int32_t* out = w.samples + (size_t)p * chunk_stride * 5;
-  for (int it = 0; it < chunk; ++it) {
-    int32_t idx[5];
-    draw_sample(s, count, idx);
+// Every kernel of a round walks the list of pairs that are still iterating (built by the init
+// kernel, rebuilt by every scan), with a fixed small grid: a round in which all pairs have
+// already stopped costs a few microseconds instead of tens of thousands of empty blocks.
+__global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int round, int n_pairs,
+                                     int chunk, int chunk_stride, RansacWs w) {
+  const int n_act = w.n_active[round];
+  const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
+  for (int a = blockIdx.x * blockDim.x + threadIdx.x; a < n_act; a += gridDim.x * blockDim.x) {
+    const int p = list[a];
+    uint64_t s = w.rng[p];
+    const int count = m[p];
+    int32_t* out = w.samples + (size_t)p * chunk_stride * 5;
+    for (int it = 0; it < chunk; ++it) {
+      int32_t idx[5];
+      draw_sample(s, count, idx);
 #pragma unroll
-    for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
+      for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
+    }
+    w.rng[p] = s;
   }
-  w.rng[p] = s;
 }
 
 // ------------------------------------------------------------------ K3 launch: warp per sample
 constexpr int SOLVE_WARPS = 4;
-__global__ void __launch_bounds__(SOLVE_WARPS * 32)
-ransac_solve_kernel(int n_cap, int it0, int chunk, int chunk_stride, RansacWs w) {
+// MINB = resident blocks per SM the register budget is sized for: the solver is a chain of
+// dependent fp64 operations, so throughput comes from warps in flight, not from ILP.
+static int g_solve_minb = 4;
+template <int MINB>
+__global__ void __launch_bounds__(SOLVE_WARPS * 32, MINB)
+ransac_solve_kernel(int n_cap, int round, int n_pairs, int it0, int chunk, int chunk_stride,
+                    RansacWs w) {
   __shared__ FiveptSmem sm[SOLVE_WARPS];
   __shared__ double p5[SOLVE_WARPS][20];
-  const int p = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int s = blockIdx.x * SOLVE_WARPS + warp;
-  if (s >= chunk) return;
-  int32_t* nm = w.nmodels + (size_t)p * chunk_stride + s;
-  if (w.done[p] || it0 + s >= w.niters[p]) {
-    if (lane == 0) *nm = 0;
-    return;
+  const int n_act = w.n_active[round];
+  const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
+  const int per_pair = (chunk + SOLVE_WARPS - 1) / SOLVE_WARPS;
+  const long n_items = (long)n_act * per_pair;
+  for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int p = list[item / per_pair];
+    const int s = (int)(item % per_pair) * SOLVE_WARPS + warp;
+    if (s >= chunk) continue;
+    int32_t* nm = w.nmodels + (size_t)p * chunk_stride + s;
+    if (it0 + s >= w.niters[p]) {
+      if (lane == 0) *nm = 0;
+      continue;
+    }
+    const int32_t* idx = w.samples + ((size_t)p * chunk_stride + s) * 5;
+    __syncwarp();
+    if (lane < 20) {
+      const int i = idx[lane >> 2];
+      p5[warp][lane] = w.ptsn[((size_t)p * n_cap + i) * 4 + (lane & 3)];
+    }
+    __syncwarp();
+    const int n = fivept_solve_warp(p5[warp], sm[warp],
+                                    w.models + ((size_t)p * chunk_stride + s) * 90);
+    if (lane == 0) *nm = n;
   }
-  const int32_t* idx = w.samples + ((size_t)p * chunk_stride + s) * 5;
-  if (lane < 20) {
-    const int i = idx[lane >> 2];
-    p5[warp][lane] = w.ptsn[((size_t)p * n_cap + i) * 4 + (lane & 3)];
-  }
-  __syncwarp();
-  const int n = fivept_solve_warp(p5[warp], sm[warp],
-                                  w.models + ((size_t)p * chunk_stride + s) * 90);
-  if (lane == 0) *nm = n;
 }
 
 // ------------------------------------------------------------------ K2: Sampson scoring
@@ -191,35 +216,42 @@ __device__ __forceinline__ float thr2_from_K(const double* __restrict__ K, doubl
 
 constexpr int SCORE_WARPS = 8;
 __global__ void __launch_bounds__(SCORE_WARPS * 32)
-ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int chunk, int chunk_stride,
-                    const double* __restrict__ K, double thr_px, RansacWs w) {
+ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_pairs, int chunk,
+                    int chunk_stride, const double* __restrict__ K, double thr_px, RansacWs w) {
   __shared__ double Es[SCORE_WARPS][90];
-  const int p = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int s = blockIdx.x * SCORE_WARPS + warp;
-  if (s >= chunk) return;
-  const int nm = w.nmodels[(size_t)p * chunk_stride + s];
-  if (nm == 0) return;
-  const double* src = w.models + ((size_t)p * chunk_stride + s) * 90;
-  for (int e = lane; e < nm * 9; e += 32) Es[warp][e] = src[e];
-  __syncwarp();
-  const int mp = m[p];
+  const int n_act = w.n_active[round];
+  const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
+  const int per_pair = (chunk + SCORE_WARPS - 1) / SCORE_WARPS;
+  const long n_items = (long)n_act * per_pair;
   const float thr2f = thr2_from_K(K, thr_px);
   const double t_lo = (double)thr2f * (1.0 - 1e-6), t_hi = (double)thr2f * (1.0 + 1e-6);
-  const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
-  int cnt = 0;
-  for (int i0 = 0; i0 < mp; i0 += 32) {
-    const int i = i0 + lane;
-    const bool act = i < mp;
-    double4 v = make_double4(0, 0, 0, 0);
-    if (act) v = ldg_d4(pts + i);
-    for (int k = 0; k < nm; ++k) {
-      const bool inl = act && sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
-      const unsigned b = __ballot_sync(0xffffffffu, inl);
-      if (lane == k) cnt += __popc(b);
+  for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int p = list[item / per_pair];
+    const int s = (int)(item % per_pair) * SCORE_WARPS + warp;
+    if (s >= chunk) continue;
+    const int nm = w.nmodels[(size_t)p * chunk_stride + s];
+    if (nm == 0) continue;
+    const double* src = w.models + ((size_t)p * chunk_stride + s) * 90;
+    __syncwarp();
+    for (int e = lane; e < nm * 9; e += 32) Es[warp][e] = src[e];
+    __syncwarp();
+    const int mp = m[p];
+    const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
+    int cnt = 0;
+    for (int i0 = 0; i0 < mp; i0 += 32) {
+      const int i = i0 + lane;
+      const bool act = i < mp;
+      double4 v = make_double4(0, 0, 0, 0);
+      if (act) v = ldg_d4(pts + i);
+      for (int k = 0; k < nm; ++k) {
+        const bool inl = act && sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+        const unsigned b = __ballot_sync(0xffffffffu, inl);
+        if (lane == k) cnt += __popc(b);
+      }
     }
+    if (lane < nm) w.counts[((size_t)p * chunk_stride + s) * 10 + lane] = cnt;
   }
-  if (lane < nm) w.counts[((size_t)p * chunk_stride + s) * 10 + lane] = cnt;
 }
 
 // standalone scoring of arbitrary hypotheses (C-ABI vo_sampson_score): warp per hypothesis
@@ -255,33 +287,38 @@ __device__ int ransac_update_num_iters(double p, double ep, int model_points, in
   return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
 }
 
-__global__ void ransac_scan_kernel(const int32_t* __restrict__ m, int n_pairs, int it0, int chunk,
-                                   int chunk_stride, double conf, int adaptive, RansacWs w,
-                                   double* __restrict__ E_out) {
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= n_pairs || w.done[p]) return;
-  int niters = w.niters[p], maxgood = w.maxgood[p];
-  const int count = m[p];
-  int bs = -1, bk = -1;
-  for (int s = 0; s < chunk; ++s) {
-    if (it0 + s >= niters) break;
-    const int nm = w.nmodels[(size_t)p * chunk_stride + s];
-    for (int k = 0; k < nm; ++k) {
-      const int c = w.counts[((size_t)p * chunk_stride + s) * 10 + k];
-      if (c > max(maxgood, 4)) {
-        maxgood = c; bs = s; bk = k;
-        if (adaptive)
-          niters = ransac_update_num_iters(conf, (double)(count - c) / count, 5, niters);
+__global__ void ransac_scan_kernel(const int32_t* __restrict__ m, int round, int n_pairs, int it0,
+                                   int chunk, int chunk_stride, double conf, int adaptive,
+                                   RansacWs w, double* __restrict__ E_out) {
+  const int n_act = w.n_active[round];
+  const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
+  int32_t* next = w.active + (size_t)((round + 1) & 1) * n_pairs;
+  for (int a = blockIdx.x * blockDim.x + threadIdx.x; a < n_act; a += gridDim.x * blockDim.x) {
+    const int p = list[a];
+    int niters = w.niters[p], maxgood = w.maxgood[p];
+    const int count = m[p];
+    int bs = -1, bk = -1;
+    for (int s = 0; s < chunk; ++s) {
+      if (it0 + s >= niters) break;
+      const int nm = w.nmodels[(size_t)p * chunk_stride + s];
+      for (int k = 0; k < nm; ++k) {
+        const int c = w.counts[((size_t)p * chunk_stride + s) * 10 + k];
+        if (c > max(maxgood, 4)) {
+          maxgood = c; bs = s; bk = k;
+          if (adaptive)
+            niters = ransac_update_num_iters(conf, (double)(count - c) / count, 5, niters);
+        }
       }
     }
+    if (bs >= 0) {
+      const double* src = w.models + ((size_t)p * chunk_stride + bs) * 90 + 9 * bk;
+      for (int e = 0; e < 9; ++e) E_out[(size_t)p * 9 + e] = src[e];
+    }
+    w.niters[p] = niters;
+    w.maxgood[p] = maxgood;
+    if (it0 + chunk >= niters) w.done[p] = 1;
+    else next[atomicAdd(&w.n_active[round + 1], 1)] = p;
   }
-  if (bs >= 0) {
-    const double* src = w.models + ((size_t)p * chunk_stride + bs) * 90 + 9 * bk;
-    for (int e = 0; e < 9; ++e) E_out[(size_t)p * 9 + e] = src[e];
-  }
-  w.niters[p] = niters;
-  w.maxgood[p] = maxgood;
-  if (it0 + chunk >= niters) w.done[p] = 1;
 }
 
 __global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap,
@@ -318,9 +355,14 @@ __global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap,
 
 using namespace vo;
 
+extern "C" int vo_debug_ransac(int solve_minb) {
+  g_solve_minb = solve_minb;
+  return VO_OK;
+}
+
 extern "C" size_t vo_essential_workspace_bytes(int n_pairs, int n_cap, int max_iters) {
   if (n_pairs <= 0 || n_cap <= 0) return 0;
-  return carve(nullptr, n_pairs, n_cap, chunk_cap(max_iters)).bytes;
+  return carve(nullptr, n_pairs, n_cap, chunk_cap(max_iters), max_iters).bytes;
 }
 
 extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, int n_cap,
@@ -335,28 +377,53 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
   VO_REQUIRE(n_pairs <= 65535, VO_ERR_INVALID_ARG,
              "vo_essential_ransac_batch: at most 65535 pairs per call");
   const int C = chunk_cap(max_iters);
-  RansacWs w = carve(ws, n_pairs, n_cap, C);
+  RansacWs w = carve(ws, n_pairs, n_cap, C, max_iters);
   VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_essential_ransac_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = (n_cap + 255) / 256;
+  cudaMemsetAsync(w.n_active, 0, (size_t)(w.max_rounds + 1) * sizeof(int32_t), st);
   ransac_init_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(pts, m, n_cap, K, max_iters, w,
                                                                     n_inl, status);
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
   int it0 = 0;
   int chunk = RANSAC_CHUNK0 < C ? RANSAC_CHUNK0 : C;
   int round = 0;
+  const int list_blocks = (n_pairs + 63) / 64 < sms ? (n_pairs + 63) / 64 : sms;
   while (it0 < max_iters) {
     if (it0 + chunk > max_iters) chunk = max_iters - it0;
-    ransac_sample_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, chunk, C, w);
-    ransac_solve_kernel<<<dim3((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS, n_pairs),
-                          SOLVE_WARPS * 32, 0, st>>>(n_cap, it0, chunk, C, w);
+    if (round >= w.max_rounds - 1) chunk = max_iters - it0 < C ? max_iters - it0 : C;  // never hit
+    ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, chunk, C, w);
     {
-      ProfScope prof(1, st);
-      ransac_score_kernel<<<dim3((chunk + SCORE_WARPS - 1) / SCORE_WARPS, n_pairs),
-                            SCORE_WARPS * 32, 0, st>>>(m, n_cap, chunk, C, K, thr_px, w);
+      // grid sized for the first (full) round; later rounds loop over what is left
+      const long want = (long)n_pairs * ((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS);
+      const long cap = (long)sms * g_solve_minb * 4;
+      const int sg = (int)(want < cap ? want : cap);
+      ProfScope prof(3, st);
+      switch (g_solve_minb) {
+        case 2: ransac_solve_kernel<2><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+        case 3: ransac_solve_kernel<3><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+        case 6: ransac_solve_kernel<6><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+        case 8: ransac_solve_kernel<8><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+        default: ransac_solve_kernel<4><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+      }
     }
-    ransac_scan_kernel<<<(n_pairs + 63) / 64, 64, 0, st>>>(m, n_pairs, it0, chunk, C, conf,
-                                                          adaptive, w, E);
+    {
+      const long want = (long)n_pairs * ((chunk + SCORE_WARPS - 1) / SCORE_WARPS);
+      const long cap = (long)sms * 8 * 4;
+      const int sg = (int)(want < cap ? want : cap);
+      ProfScope prof(1, st);
+      ransac_score_kernel<<<sg, SCORE_WARPS * 32, 0, st>>>(m, n_cap, round, n_pairs, chunk, C, K,
+                                                          thr_px, w);
+    }
+    ransac_scan_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, it0, chunk, C, conf, adaptive,
+                                                  w, E);
     it0 += chunk;
     ++round;
     if (adaptive) {
@@ -370,7 +437,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
   return check_launch("vo_essential_ransac_batch");
 }
 
-__global__ void __launch_bounds__(SOLVE_WARPS * 32)
+__global__ void __launch_bounds__(SOLVE_WARPS * 32, 4)
 fivept_standalone_kernel(const double* __restrict__ ptsn, const int32_t* __restrict__ samples,
                          int n_samples, double* __restrict__ E, int32_t* __restrict__ n_models) {
   __shared__ FiveptSmem sm[SOLVE_WARPS];

@@ -64,42 +64,48 @@ class PairPipeline:
         self.ws_pose = e(max(self.lib.vo_pose_workspace_bytes(P, N), 256), dt=U8)
         # pinned staging for run_host
         self._pin = None
+        self._copy_stream = None
         # kernels launched per run (for bench.py's gpu_launches claim; see launches_per_run)
         self.launches = 0
 
     # ------------------------------------------------------------------ device-resident run
-    def run_device(self, n_pairs, stream=None):
-        """Inputs already in self.desc/kp/nkp/pairs. Asynchronous; results in the attributes."""
-        lib, p = self.lib, _lib.ptr
+    def run_device(self, n_pairs, stream=None, p0=0, chain=None):
+        """Inputs already in self.desc/kp/nkp/pairs. Asynchronous; results in the attributes.
+        Processes pairs [p0, p0 + n_pairs) (outputs land in the same rows)."""
+        lib = self.lib
         st = _lib.cur_stream() if stream is None else stream
-        N, B = self.n_cap, int(n_pairs)
+        N, B, a = self.n_cap, int(n_pairs), int(p0)
+        p = lambda t: _lib.ptr(t[a:]) if a else _lib.ptr(t)      # per-pair arrays: row offset
+        g = _lib.ptr                                             # frame-indexed / global arrays
+        if B <= 0:
+            return
         if self.descriptor == "orb":
             _lib.check(lib.vo_match_hamming_batch(
-                p(self.desc), p(self.nkp), p(self.kp), N, p(self.pairs), B, self.match_mode,
+                g(self.desc), g(self.nkp), g(self.kp), N, p(self.pairs), B, self.match_mode,
                 self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None, p(self.pts),
-                p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
+                p(self.n_match), g(self.ws_match), self.ws_match.numel(), st))
         else:
             _lib.check(lib.vo_match_l2_batch(
-                p(self.desc), p(self.nkp), p(self.kp), N, self.D, self.F, p(self.pairs), B,
+                g(self.desc), g(self.nkp), g(self.kp), N, self.D, self.F, p(self.pairs), B,
                 self.match_mode, self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None,
-                p(self.pts), p(self.n_match), p(self.ws_match), self.ws_match.numel(), st))
+                p(self.pts), p(self.n_match), g(self.ws_match), self.ws_match.numel(), st))
         _lib.check(lib.vo_essential_ransac_batch(
-            p(self.pts), p(self.n_match), N, B, p(self.K), self.prob, self.threshold,
+            p(self.pts), p(self.n_match), N, B, g(self.K), self.prob, self.threshold,
             self.max_iters, int(self.adaptive), p(self.E), p(self.mask), p(self.n_inl),
-            p(self.n_iters), p(self.status), p(self.ws_ess), self.ws_ess.numel(), st))
+            p(self.n_iters), p(self.status), g(self.ws_ess), self.ws_ess.numel(), st))
         _lib.check(lib.vo_recover_pose_batch(
-            p(self.E), p(self.pts), p(self.n_match), p(self.mask), N, B, p(self.K), 50.0,
-            p(self.R), p(self.t), None, p(self.n_good), p(self.ws_pose), self.ws_pose.numel(), st))
+            p(self.E), p(self.pts), p(self.n_match), p(self.mask), N, B, g(self.K), 50.0,
+            p(self.R), p(self.t), None, p(self.n_good), g(self.ws_pose), self.ws_pose.numel(), st))
         if self.do_tri:
             _lib.check(lib.vo_triangulate_pairs(
-                p(self.R), p(self.t), p(self.pts), p(self.n_match), p(self.mask), N, B, p(self.K),
+                p(self.R), p(self.t), p(self.pts), p(self.n_match), p(self.mask), N, B, g(self.K),
                 p(self.X), p(self.n_x), st))
-        if self.do_chain:
-            _lib.check(lib.vo_chain_poses(p(self.R), p(self.t), B, None, p(self.poses), st))
+        if self.do_chain if chain is None else chain:
+            _lib.check(lib.vo_chain_poses(g(self.R), g(self.t), a + B, None, g(self.poses), st))
 
     def launches_per_run(self):
         """Number of libvo_b200 kernels one run_device issues (memset excluded)."""
-        rounds, it0, chunk, r = 0, 0, min(32, self.max_iters), 0
+        rounds, it0, chunk, r = 0, 0, min(16, self.max_iters), 0
         cap = min(256, self.max_iters)
         while it0 < self.max_iters:
             chunk = min(chunk, self.max_iters - it0)
@@ -137,22 +143,56 @@ class PairPipeline:
         pin["pairs"][:b].copy_(torch.from_numpy(np.ascontiguousarray(pairs, np.int32)))
         return f, b
 
-    def run_staged(self, n_frames, n_pairs):
+    def run_staged(self, n_frames, n_pairs, chunks=2, first=0.15):
         """H2D of the staged inputs, the whole chain, D2H of poses/counts; synchronises.
-        Returns (h2d_bytes, d2h_bytes)."""
+        The frame set is uploaded in `chunks` pieces (the first one `first` of the frames) on a
+        copy stream while the compute stream
+        already works on the pairs whose frames have arrived (per-chunk CUDA events), so only the
+        first piece of the upload is exposed.  Returns (h2d_bytes, d2h_bytes)."""
         pin, f, b = self._pinned(), int(n_frames), int(n_pairs)
-        self.desc[:f].copy_(pin["desc"][:f], non_blocking=True)
-        self.kp[:f].copy_(pin["kp"][:f], non_blocking=True)
-        self.nkp[:f].copy_(pin["nkp"][:f], non_blocking=True)
-        self.pairs[:b].copy_(pin["pairs"][:b], non_blocking=True)
-        self.run_device(b)
+        main = torch.cuda.current_stream()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+        cs = self._copy_stream
+        if self.descriptor != "orb":
+            chunks = 1     # the L2 path converts the whole frame set to bf16 tiles per call
+        chunks = max(1, min(int(chunks), f, max(b, 1)))
+        # a small first piece (compute starts early), the rest in equal pieces
+        f0 = max(1, round(first * f)) if chunks > 1 else f
+        fb = [0] + [f0 + round(k * (f - f0) / (chunks - 1)) for k in range(chunks)] if chunks > 1 \
+            else [0, f]
+        cs.wait_stream(main)                       # earlier work may still read the buffers
+        events = []
+        with torch.cuda.stream(cs):
+            self.nkp[:f].copy_(pin["nkp"][:f], non_blocking=True)
+            self.pairs[:b].copy_(pin["pairs"][:b], non_blocking=True)
+            for k in range(chunks):
+                lo, hi = fb[k], fb[k + 1]
+                self.desc[lo:hi].copy_(pin["desc"][lo:hi], non_blocking=True)
+                self.kp[lo:hi].copy_(pin["kp"][lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                events.append(ev)
+        # pair ranges: cut where the highest frame a pair needs crosses an upload boundary
+        need = pin["pairs"][:b].numpy().max(axis=1) if b else np.zeros(0, np.int64)
+        run_max = np.maximum.accumulate(need) if b else need
+        p_lo = 0
+        for k in range(chunks):
+            p_hi = int(np.searchsorted(run_max, fb[k + 1], side="left")) if k + 1 < chunks else b
+            main.wait_event(events[k])
+            if p_hi > p_lo:
+                self.run_device(p_hi - p_lo, p0=p_lo, chain=False)
+                p_lo = p_hi
+        if self.do_chain and b:
+            _lib.check(self.lib.vo_chain_poses(_lib.ptr(self.R), _lib.ptr(self.t), b, None,
+                                               _lib.ptr(self.poses), _lib.cur_stream()))
         pin["R"][:b].copy_(self.R[:b], non_blocking=True)
         pin["t"][:b].copy_(self.t[:b], non_blocking=True)
         pin["n_inl"][:b].copy_(self.n_inl[:b], non_blocking=True)
         pin["n_match"][:b].copy_(self.n_match[:b], non_blocking=True)
         pin["status"][:b].copy_(self.status[:b], non_blocking=True)
         pin["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        main.synchronize()
         h2d = sum(pin[k][:f].numel() * pin[k].element_size() for k in ("desc", "kp", "nkp")) + \
             pin["pairs"][:b].numel() * 4
         d2h = b * (9 + 3) * 8 + b * 3 * 4 + (b + 1) * 16 * 8
