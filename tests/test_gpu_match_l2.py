@@ -1,0 +1,172 @@
+"""GPU: K6 SIFT / NORM_L2 matching on tcgen05 through the C-ABI vs cv2.BFMatcher(NORM_L2).
+
+Bar (north_star): bit-exact indices AND distances for integer-valued SIFT descriptors (the GEMM is
+exact for them); for non-integer float descriptors: same indices, distances within 1e-5 relative
+(bf16 GEMM selects the candidates, an fp32 rerank recomputes their distances)."""
+import numpy as np
+import pytest
+import torch
+
+import cv2
+from visual_odometry_b200 import _lib
+from visual_odometry_b200.matcher import B200Matcher, NORM_L2
+from visual_odometry_b200.synth import make_sequence
+
+pytestmark = pytest.mark.gpu
+
+
+def _triples(ms):
+    return [(m.queryIdx, m.trainIdx, m.distance) for m in ms]
+
+
+def _sift(n, seed):
+    return make_sequence(2, max(n, 8), seed, descriptor="sift")
+
+
+# sizes walk through the kernel's tiling cases: one 128-row block, two blocks of one work item,
+# an odd number of blocks (second item has a single block), column splits (few items), C3 size
+@pytest.mark.parametrize("n1,n2", [(1, 1), (5, 3), (128, 128), (129, 513), (300, 257),
+                                   (1000, 1000), (2000, 1777), (5000, 4289)])
+def test_all_modes_equal_cv2(cuda_dev, n1, n2):
+    seq = _sift(max(n1, n2), n1 * 31 + n2)
+    d1, d2 = seq.desc[0][:n1].copy(), seq.desc[1][:n2].copy()
+    if n1 > 10 and n2 > 10:   # exact duplicates: ties in both directions
+        d1[5] = d1[3]
+        d2[7] = d2[2]
+        d1[9] = d2[2]
+    for cc in (True, False):
+        ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=cc).match(d1, d2)
+        got = B200Matcher(NORM_L2, crossCheck=cc).match(d1, d2)
+        assert _triples(ref) == _triples(got)
+    if n2 >= 2:
+        refk = cv2.BFMatcher(cv2.NORM_L2).knnMatch(d1, d2, k=2)
+        gotk = B200Matcher(NORM_L2).knnMatch(d1, d2, k=2)
+        assert [_triples(r) for r in refk] == [_triples(r) for r in gotk]
+        for ratio in (0.6, 0.75):
+            good = [m for m, n in refk if m.distance < ratio * n.distance]
+            mine = B200Matcher(NORM_L2).ratio_match(d1, d2, ratio)
+            assert _triples(good) == _triples(mine)
+
+
+def test_empty_and_single_column(cuda_dev):
+    e = np.zeros((0, 128), np.float32)
+    d = _sift(10, 3).desc[0][:10]
+    m = B200Matcher(NORM_L2, crossCheck=True)
+    assert m.match(e, d) == [] and m.match(d, e) == [] and m.match(e, e) == []
+    # a single train descriptor: knn(k=2) rows hold one match, like cv2
+    refk = cv2.BFMatcher(cv2.NORM_L2).knnMatch(d, d[:1], k=2)
+    gotk = B200Matcher(NORM_L2).knnMatch(d, d[:1], k=2)
+    assert [_triples(r) for r in refk] == [_triples(r) for r in gotk]
+
+
+def test_all_identical_descriptors_tie_break(cuda_dev):
+    d = np.tile(np.arange(128, dtype=np.float32), (300, 1))
+    ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=True).match(d, d)
+    got = B200Matcher(NORM_L2, crossCheck=True).match(d, d)
+    assert _triples(ref) == _triples(got) == [(0, 0, 0.0)]
+    refk = cv2.BFMatcher(cv2.NORM_L2).knnMatch(d, d, k=2)
+    gotk = B200Matcher(NORM_L2).knnMatch(d, d, k=2)
+    assert [_triples(r) for r in refk] == [_triples(r) for r in gotk]
+
+
+def test_rootsift_floats_same_indices(cuda_dev):
+    """non-integer descriptors (RootSIFT, unit norm): candidates from the bf16 GEMM, distances
+    recomputed in fp32 -> indices equal cv2's, distances within 1e-5 relative."""
+    seq = _sift(800, 9)
+    r1 = np.sqrt(seq.desc[0] / seq.desc[0].sum(1, keepdims=True)).astype(np.float32)
+    r2 = np.sqrt(seq.desc[1] / seq.desc[1].sum(1, keepdims=True)).astype(np.float32)
+    ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=True).match(r1, r2)
+    got = B200Matcher(NORM_L2, crossCheck=True).match(r1, r2)
+    assert [(m.queryIdx, m.trainIdx) for m in ref] == [(m.queryIdx, m.trainIdx) for m in got]
+    rel = max(abs(a.distance - b.distance) / max(a.distance, 1e-9) for a, b in zip(ref, got))
+    assert rel < 1e-5
+
+
+def test_large_norm_descriptors_take_the_rerank_path(cuda_dev):
+    """|d|^2 > 2^20 (not SIFT-like): scores no longer fit the exact integer window, the kernel
+    scales them and flags the data inexact; true matches are still found and their distances are
+    the exact fp32 ones."""
+    rng = np.random.default_rng(5)
+    d2 = rng.integers(0, 256, (700, 128)).astype(np.float32)
+    d1 = d2[rng.permutation(700)[:500]] + rng.integers(-3, 4, (500, 128)).astype(np.float32)
+    d1 = np.clip(d1, 0, 255)
+    ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=True).match(d1, d2)
+    got = B200Matcher(NORM_L2, crossCheck=True).match(d1, d2)
+    assert _triples(ref) == _triples(got)
+
+
+def test_batched_ragged_frames_pair_list_and_points(cuda_dev):
+    """batched entry: ragged keypoint counts, arbitrary pair list (both modes), fused gather."""
+    lib = _lib.load()
+    N = 700
+    seq = make_sequence(5, N, 42, descriptor="sift")
+    nkp = np.array([700, 512, 1, 333, 700], np.int32)
+    pairs = np.array([[0, 1], [1, 2], [2, 3], [3, 4], [4, 0], [0, 0], [1, 3]], np.int32)
+    B, F = len(pairs), 5
+    dev = cuda_dev
+    desc = torch.from_numpy(seq.desc).to(dev)
+    kp = torch.from_numpy(seq.kp).to(dev)
+    nkp_d, pairs_d = torch.from_numpy(nkp).to(dev), torch.from_numpy(pairs).to(dev)
+    wsb = lib.vo_match_l2_workspace_bytes(F, B, N)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+    for mode, ratio in [(_lib.MATCH_MUTUAL, 0.0), (_lib.MATCH_KNN2_RATIO, 0.75)]:
+        q = torch.empty(B, N, dtype=torch.int32, device=dev)
+        t, t2 = torch.empty_like(q), torch.empty_like(q)
+        dist = torch.empty(B, N, dtype=torch.float32, device=dev)
+        dist2 = torch.empty_like(dist)
+        pts = torch.empty(B, N, 4, dtype=torch.float64, device=dev)
+        n_out = torch.empty(B, dtype=torch.int32, device=dev)
+        _lib.check(lib.vo_match_l2_batch(
+            _lib.ptr(desc), _lib.ptr(nkp_d), _lib.ptr(kp), N, 128, F, _lib.ptr(pairs_d), B, mode,
+            ratio, _lib.ptr(q), _lib.ptr(t), _lib.ptr(dist), _lib.ptr(t2), _lib.ptr(dist2),
+            _lib.ptr(pts), _lib.ptr(n_out), _lib.ptr(ws), wsb, _lib.cur_stream()))
+        n = n_out.cpu().numpy()
+        for b, (fa, fb) in enumerate(pairs):
+            da, db = seq.desc[fa, :nkp[fa]], seq.desc[fb, :nkp[fb]]
+            if mode == _lib.MATCH_MUTUAL:
+                ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=True).match(da, db)
+            elif nkp[fb] >= 2:
+                ref = [m for m, k in cv2.BFMatcher(cv2.NORM_L2).knnMatch(da, db, k=2)
+                       if m.distance < ratio * k.distance]
+            else:
+                ref = []
+            assert n[b] == len(ref)
+            rq = np.array([m.queryIdx for m in ref], np.int64)
+            rt = np.array([m.trainIdx for m in ref], np.int64)
+            assert np.array_equal(q[b, :n[b]].cpu().numpy(), rq)
+            assert np.array_equal(t[b, :n[b]].cpu().numpy(), rt)
+            assert np.array_equal(dist[b, :n[b]].cpu().numpy(),
+                                  np.array([m.distance for m in ref], np.float32))
+            want = np.concatenate([seq.kp[fa][rq], seq.kp[fb][rt]], 1).astype(np.float64) \
+                if len(ref) else np.zeros((0, 4))
+            assert np.array_equal(pts[b, :n[b]].cpu().numpy(), want)
+
+
+def test_c3_full_size_pipeline(cuda_dev):
+    """config C3: SIFT 5000 kp, L2 kNN ratio-test matching on tensor cores + E-RANSAC with exactly
+    4096 hypotheses (adaptive stop off).  Matches equal cv2's; the mask is the Sampson inlier set
+    of the returned E; the pose is close to ground truth."""
+    from oracle import cv_geometry as CG
+    from visual_odometry_b200.pipeline import PairPipeline
+    N = 5000
+    seq = make_sequence(2, N, 20261104 + 2, descriptor="sift")
+    pipe = PairPipeline(N, 1, 2, descriptor="sift", K=seq.K, max_iters=4096, adaptive=False,
+                        match_mode=_lib.MATCH_KNN2_RATIO, ratio=0.75)
+    out = pipe.run_host(seq.desc, seq.kp, seq.nkp, seq.consecutive_pairs())
+    n = int(out["n_match"][0])
+    refk = cv2.BFMatcher(cv2.NORM_L2).knnMatch(seq.desc[0], seq.desc[1], k=2)
+    good = [m for m, k in refk if m.distance < 0.75 * k.distance]
+    assert n == len(good)
+    assert np.array_equal(pipe.q[0, :n].cpu().numpy(), [m.queryIdx for m in good])
+    assert np.array_equal(pipe.t_idx[0, :n].cpu().numpy(), [m.trainIdx for m in good])
+    assert int(pipe.n_iters[0]) == 4096 and int(out["status"][0]) == 0
+    E = pipe.E[0].cpu().numpy()
+    pts = pipe.pts[0, :n].cpu().numpy()
+    # findEssentialMat: points normalised by K, threshold divided by the mean focal length
+    thr = 1.0 / ((seq.K[0, 0] + seq.K[1, 1]) / 2.0)
+    want = CG.sampson_mask(E, CG.normalize_points(pts[:, :2], seq.K),
+                           CG.normalize_points(pts[:, 2:], seq.K), thr)
+    assert np.array_equal(pipe.mask[0, :n].cpu().numpy(), want.ravel().astype(np.uint8))
+    Rgt, tgt = seq.relative_pose(0, 1)
+    ang = np.arccos(np.clip((np.trace(out["R"][0].T @ Rgt) - 1) / 2, -1, 1))
+    assert ang < 5e-3

@@ -133,3 +133,28 @@ def test_full_size_c2_property(cuda_dev):
     assert np.median(errs) < 5e-3
     P = out["poses"]
     assert np.abs(P[:, :3, :3] @ P[:, :3, :3].transpose(0, 2, 1) - np.eye(3)).max() < 1e-9
+
+
+def test_full_size_c4_batch_vs_reference_path(cuda_dev):
+    """config C4 size (ORB 4000 kp; 24 pairs of the 4096 here): the batched pipeline equals the
+    reference's cv2 chain pair by pair (matches and masks exact, pose within 1e-4) on the pairs
+    checked, and every pair of the batch solves."""
+    F, N = 25, 4000
+    seq = make_sequence(F, N, 20261104 + 3)
+    pipe = PairPipeline(N, F - 1, K=seq.K)
+    out = pipe.run_host(seq.desc, seq.kp, seq.nkp, seq.consecutive_pairs())
+    assert np.all(out["status"] == 0) and np.all(out["n_match"] > 0.6 * N)
+    exact = 0
+    for b in (0, 11, 23):
+        ref = RP.pair_cv2(seq.desc[b], seq.kp[b], seq.desc[b + 1], seq.kp[b + 1], seq.K,
+                          cv2.NORM_HAMMING)
+        n = int(out["n_match"][b])
+        assert n == len(ref["q"])
+        assert np.array_equal(pipe.q[b, :n].cpu().numpy(), ref["q"])
+        assert np.array_equal(pipe.t_idx[b, :n].cpu().numpy(), ref["t"])
+        assert np.array_equal(pipe.dist[b, :n].cpu().numpy(), ref["dist"])
+        if np.array_equal(pipe.mask[b, :n].cpu().numpy(), ref["mask"].ravel()):
+            exact += 1
+            assert rot_angle(out["R"][b], ref["R"]) < 1e-4
+            assert np.abs(out["t"][b] - ref["tvec"].ravel()).max() < 1e-4
+    assert exact >= 2
