@@ -54,12 +54,20 @@ constexpr int L2_THREADS = (L2_EPI_WARPS + 2) * 32;  // + MMA warp + TMA warp
 constexpr uint32_t L2_MAGIC_BITS = 0x4AC00000u;
 constexpr uint32_t L2_QBIAS = L2_MAGIC_BITS & 0x1ffffffu;   // what (key >> 7) reads for x = 0
 constexpr float L2_PAD_SCORE = 4194304.0f;        // MAGIC - 2^21: below every real score
+// column keys (single-pass mutual mode): ((bits - s^2|a_i|^2 - MAGIC_BITS + 2^23) << 8) | (255 - r)
+// = (2^23 - s^2 d^2(i,j)) << 8 | (255 - row inside the 256-row block): unsigned max over a column
+// = nearest query row, lowest row on ties.  Padded rows carry |a|^2 := 2^22 + 2^21 and always lose.
+constexpr uint32_t L2_COL_OFFSET = L2_MAGIC_BITS - (1u << 23);
+constexpr uint32_t L2_PAD_NORM = (1u << 22) + (1u << 21);
+enum { L2_MODE_TOP1 = 0, L2_MODE_TOP2 = 1, L2_MODE_TOP1_COLMAX = 2 };
 
 struct L2Ws {
   __nv_bfloat16* tiles;   // [F][nblk][20480]
   float* norms;           // [F][nblk*128]   (+inf on padded rows)
   int32_t* flags;         // [0] inexact data, [1] bits of the largest squared norm
   float4* rowbest;        // [P][2][S][nblk*128]  (d2_1, idx_1, d2_2, idx_2) idx as int bits
+  uint32_t* colpart;      // [P][nrbp*4][nblk*128] best query row of every train column among the 64
+                          // rows one epilogue warp owns (256-row block x TMEM lane quarter)
   size_t bytes;
 };
 
@@ -78,6 +86,7 @@ static L2Ws l2_carve(void* base, int n_frames, int n_pairs, int n_cap, int split
   w.norms = (float*)take((size_t)n_frames * nblk * L2_BLK * sizeof(float));
   w.flags = (int32_t*)take(256);
   w.rowbest = (float4*)take((size_t)n_pairs * 2 * splits * nblk * L2_BLK * sizeof(float4));
+  w.colpart = (uint32_t*)take((size_t)n_pairs * ((nblk + 1) / 2) * 4 * nblk * L2_BLK * sizeof(uint32_t));
   w.bytes = off;
   return w;
 }
@@ -304,6 +313,63 @@ __device__ __forceinline__ void l2_rank_chunk(L2Top& s, const uint32_t (&v)[32],
   }
 }
 
+// single-pass mutual mode: column maxima of one 32-column chunk over BOTH row blocks.  The two
+// rows a thread owns are folded first (VIMNMX); the 32 rows of the warp are then folded by a
+// transposing butterfly: at offset OFF a lane keeps the half of its columns selected by its lane
+// bit and receives the partner's values for that half (31 SHFL + 31 max + 62 selects per chunk;
+// one warp REDUX per column measured ~4x slower).  Lane c ends up with the best of column c.
+template <int OFF>
+__device__ __forceinline__ void l2_butterfly(uint32_t (&k)[32], int lane) {
+  const bool hi = (lane & OFF) != 0;
+#pragma unroll
+  for (int j = 0; j < OFF; ++j) {
+    const uint32_t send = hi ? k[j] : k[j + OFF];
+    const uint32_t keep = hi ? k[j + OFF] : k[j];
+    k[j] = max(keep, __shfl_xor_sync(0xffffffffu, send, OFF));
+  }
+}
+template <bool ADDM, bool TWO>
+__device__ __forceinline__ uint32_t l2_col_chunk_redux(const uint32_t (&v0)[32],
+                                                       const uint32_t (&v1)[32], uint32_t mul2,
+                                                       uint32_t cadd0, uint32_t cadd1, int lane) {
+  uint32_t mine = 0u;
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    uint32_t b0 = v0[c], b1 = v1[c];
+    if (ADDM) {
+      b0 = __float_as_uint(__fadd_rn(__uint_as_float(b0), L2_MAGIC));
+      b1 = __float_as_uint(__fadd_rn(__uint_as_float(b1), L2_MAGIC));
+    }
+    uint32_t k = b0 * mul2 + cadd0;
+    if (TWO) k = max(k, b1 * mul2 + cadd1);
+    const uint32_t r = __reduce_max_sync(0xffffffffu, k);
+    mine = (lane == c) ? r : mine;
+  }
+  return mine;
+}
+template <bool ADDM, bool TWO>
+__device__ __forceinline__ uint32_t l2_col_chunk(const uint32_t (&v0)[32], const uint32_t (&v1)[32],
+                                                 uint32_t mul2, uint32_t cadd0, uint32_t cadd1,
+                                                 int lane) {
+  uint32_t k[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    uint32_t b0 = v0[c], b1 = v1[c];
+    if (ADDM) {
+      b0 = __float_as_uint(__fadd_rn(__uint_as_float(b0), L2_MAGIC));
+      b1 = __float_as_uint(__fadd_rn(__uint_as_float(b1), L2_MAGIC));
+    }
+    k[c] = b0 * mul2 + cadd0;
+    if (TWO) k[c] = max(k[c], b1 * mul2 + cadd1);
+  }
+  l2_butterfly<16>(k, lane);
+  l2_butterfly<8>(k, lane);
+  l2_butterfly<4>(k, lane);
+  l2_butterfly<2>(k, lane);
+  l2_butterfly<1>(k, lane);
+  return k[0];
+}
+
 // merge another warp's partial (other column quarter): order = score desc, global column asc
 __device__ __forceinline__ bool l2_before(uint32_t ka, int ta, uint32_t kb, int tb) {
   const uint32_t sa = ka >> 7, sb = kb >> 7;
@@ -320,12 +386,18 @@ __device__ __forceinline__ void l2_insert(L2Top& s, uint32_t k, int t) {
   }
 }
 
-// TOP2 = false: cross-check matching needs only the nearest neighbour of every row (in both
-// directions).  Persistent: CTA c handles work items c, c + gridDim.x, ...
-template <bool TOP2, bool ADDM>
+// MODE: TOP1 = nearest neighbour of every row (cross-check from two directions, fallback for
+// inexact data); TOP2 = two nearest (knn + ratio); TOP1_COLMAX = nearest neighbour of every row
+// AND of every column from the same accumulator (cross-check in ONE pass, exact data only).
+// run_if: -1 always, 0 only when the data is exact (flags[0] == 0), 1 only when it is not.
+// Persistent: CTA c handles work items c, c + gridDim.x, ...
+template <int MODE, bool ADDM>
 __global__ void __launch_bounds__(L2_THREADS, 1)
 l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ pairs, int nblk,
-                  int n_splits, int ndir, int n_items, L2Ws w) {
+                  int n_splits, int ndir, int n_items, int run_if, L2Ws w) {
+  constexpr bool TOP2 = (MODE == L2_MODE_TOP2);
+  constexpr bool COLMAX = (MODE == L2_MODE_TOP1_COLMAX);
+  if (run_if >= 0 && (w.flags[0] != 0) != (run_if != 0)) return;
   extern __shared__ uint8_t smem_raw[];
   L2Smem& S = *reinterpret_cast<L2Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -407,6 +479,7 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
     const int quarter = warp & 3, cq = warp >> 2;
     const int rl = quarter * 32 + lane;
     const uint32_t mul = 128u + (uint32_t)(n_items < 0);   // = 128, opaque to the compiler
+    const uint32_t mul2 = 256u + (uint32_t)(n_items < 0);  // = 256 (column keys)
     const float inv_s2 = 1.f / (l2_scale(w.flags) * l2_scale(w.flags));
     uint32_t g = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
@@ -415,6 +488,18 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
       L2Top st[L2_RBK];
 #pragma unroll
       for (int rb = 0; rb < L2_RBK; ++rb) { st[rb].k1 = st[rb].k2 = 0u; st[rb].t1 = st[rb].t2 = -1; }
+      uint32_t cadd[L2_RBK] = {0u, 0u};
+      if (COLMAX) {
+        const float s2 = l2_scale(w.flags) * l2_scale(w.flags);
+#pragma unroll
+        for (int rb = 0; rb < L2_RBK; ++rb) {
+          const int row = (it.rbp * L2_RBK + rb) * L2_BLK + rl;
+          uint32_t na = L2_PAD_NORM;
+          if (rb < it.nrb && row < it.nq)
+            na = (uint32_t)__float2int_rn(s2 * w.norms[(size_t)it.fq * nblk * L2_BLK + row]);
+          cadd[rb] = (255u - (uint32_t)(rb * L2_BLK + rl)) - ((na + L2_COL_OFFSET) << 8);
+        }
+      }
       for (int t = 0; t < it.ntile; ++t, ++g) {
         const int as = g & 1;
         mbar_wait(&S.tmem_full[as], (g >> 1) & 1);
@@ -444,6 +529,19 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);   // both accumulators are in registers
         if (!(dbg & 2) && it.nrb == 2) l2_rank_chunk<TOP2, ADDM>(st[1], v1, mul, tcol);
+        if (COLMAX && !(dbg & 2)) {
+          uint32_t cm;
+          if (dbg & 32)
+            cm = (it.nrb == 2) ? l2_col_chunk_redux<ADDM, true>(v0, v1, mul2, cadd[0], cadd[1], lane)
+                               : l2_col_chunk_redux<ADDM, false>(v0, v1, mul2, cadd[0], cadd[1], lane);
+          else
+            cm = (it.nrb == 2) ? l2_col_chunk<ADDM, true>(v0, v1, mul2, cadd[0], cadd[1], lane)
+                               : l2_col_chunk<ADDM, false>(v0, v1, mul2, cadd[0], cadd[1], lane);
+          // one coalesced 128 B store per warp: best row of 32 columns among this warp's 64 rows
+          const size_t ncol = (size_t)nblk * L2_BLK;
+          w.colpart[(((size_t)it.pair * nrbp + it.rbp) * 4 + quarter) * ncol +
+                    (size_t)(it.t_lo + t) * L2_BLK + cq * 32 + lane] = cm;
+        }
       }
       // ---- merge the four column quarters of every row, convert, write ----
       if (cq > 0) {
@@ -546,7 +644,7 @@ constexpr int L2C_THREADS = 1024;
 __global__ void __launch_bounds__(L2C_THREADS)
 l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp, int n_cap,
                   const int32_t* __restrict__ pairs, int nblk, int n_splits, int mode, double ratio,
-                  L2Ws w, int32_t* __restrict__ q, int32_t* __restrict__ t,
+                  int colmode, L2Ws w, int32_t* __restrict__ q, int32_t* __restrict__ t,
                   float* __restrict__ dist, int32_t* __restrict__ t2, float* __restrict__ dist2,
                   double* __restrict__ pts, int32_t* __restrict__ n_out) {
   __shared__ int warp_tot[L2C_THREADS / 32];
@@ -558,6 +656,9 @@ l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp,
   const size_t stride = (size_t)nblk * L2_BLK;
   const float4* fwd = w.rowbest + ((size_t)pair * 2 + 0) * n_splits * stride;
   const float4* bwd = w.rowbest + ((size_t)pair * 2 + 1) * n_splits * stride;
+  const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
+  const uint32_t* colp = w.colpart + (size_t)pair * nrbp * 4 * stride;
+  const bool use_col = colmode != 0 && w.flags[0] == 0;
   const size_t ob = (size_t)pair * n_cap;
   const float INF = __int_as_float(0x7f800000);
   if (tid == 0) base_s = 0;
@@ -569,7 +670,21 @@ l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp,
     bool keep = false;
     if (i < n1 && n2 > 0) {
       for (int s = 0; s < n_splits; ++s) merge_top2(fwd[s * stride + i], s1, i1, s2, i2);
-      if (mode == VO_MATCH_MUTUAL) {
+      if (mode == VO_MATCH_MUTUAL && use_col) {
+        // single-pass path: best query row of column i1, folded over the 256-row blocks
+        // (ascending, strict >: the lowest row wins ties, as in OpenCV)
+        int best_row = -1;
+        if (i1 >= 0) {
+          const int nrbp_q = (n1 + L2_RBK * L2_BLK - 1) / (L2_RBK * L2_BLK);
+          uint32_t best = 0u;
+          for (int r = 0; r < nrbp_q * 4; ++r) {   // ascending 256-row blocks; quarters by key
+            const uint32_t k = colp[(size_t)r * stride + i1];
+            const int row = (r >> 2) * L2_RBK * L2_BLK + 255 - (int)(k & 255u);
+            if ((k >> 8) > best || ((k >> 8) == best && row < best_row)) { best = k >> 8; best_row = row; }
+          }
+        }
+        keep = (best_row == i);
+      } else if (mode == VO_MATCH_MUTUAL) {
         float b1 = INF, b2 = INF;
         int j1 = -1, j2 = -1;
         if (i1 >= 0)
@@ -664,35 +779,52 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   if (n_pairs == 0) return VO_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int nblk = (n_cap + L2_BLK - 1) / L2_BLK;
-  const int ndir = (mode == VO_MATCH_MUTUAL) ? 2 : 1;   // knn + ratio needs query -> train only
-  const int splits = l2_pick_splits(n_pairs, ndir, nblk);
+  const int ndir = (mode == VO_MATCH_MUTUAL) ? 2 : 1;   // rerank grid: directions that may exist
+  const int splits = l2_pick_splits(n_pairs, 1, nblk);
   L2Ws w = l2_carve(ws, n_frames, n_pairs, n_cap, splits);
   cudaMemsetAsync(w.flags, 0, 2 * sizeof(int32_t), st);
   l2_norm_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
   l2_tile_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
-  typedef void (*L2Kernel)(const int32_t*, const int32_t*, int, int, int, int, L2Ws);
-  static const L2Kernel kernels[4] = {l2_top2_tc_kernel<false, false>, l2_top2_tc_kernel<true, false>,
-                                      l2_top2_tc_kernel<false, true>, l2_top2_tc_kernel<true, true>};
+  typedef void (*L2Kernel)(const int32_t*, const int32_t*, int, int, int, int, int, L2Ws);
+  static const L2Kernel kernels[6] = {
+      l2_top2_tc_kernel<L2_MODE_TOP1, false>, l2_top2_tc_kernel<L2_MODE_TOP2, false>,
+      l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, false>, l2_top2_tc_kernel<L2_MODE_TOP1, true>,
+      l2_top2_tc_kernel<L2_MODE_TOP2, true>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, true>};
   static bool attr_set = false;
   const int smem = (int)sizeof(L2Smem) + 1024;
   if (!attr_set) {
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 6; ++k)
       if (cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
           cudaSuccess)
         return check_launch("vo_match_l2_batch(smem attribute)");
     attr_set = true;
   }
+  const int addm = (g_l2_debug_host & 8) ? 3 : 0;
+  const bool two_pass_only = (g_l2_debug_host & 16) != 0;   // diagnostics: old mutual path
   {
     ProfScope prof(2, st);
     const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
-    const long n_items = (long)n_pairs * ndir * splits * nrbp;
-    const int grid = (int)(n_items < l2_num_sms() ? n_items : l2_num_sms());
-    const int which = (mode == VO_MATCH_MUTUAL ? 0 : 1) + ((g_l2_debug_host & 8) ? 2 : 0);
-    kernels[which]<<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, ndir, (int)n_items, w);
+    auto launch = [&](int mode_k, int nd, int run_if) {
+      const long n_items = (long)n_pairs * nd * splits * nrbp;
+      const int grid = (int)(n_items < l2_num_sms() ? n_items : l2_num_sms());
+      kernels[mode_k + addm]<<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, nd,
+                                                            (int)n_items, run_if, w);
+    };
+    if (mode != VO_MATCH_MUTUAL) {
+      launch(L2_MODE_TOP2, 1, -1);
+    } else if (two_pass_only) {
+      launch(L2_MODE_TOP1, 2, -1);
+    } else {
+      // exact (integer) data: rows and columns ranked from ONE accumulator pass; anything else:
+      // both directions + fp32 rerank.  The prep kernels decide on the device (flags[0]); the
+      // launch that does not apply exits at once.
+      launch(L2_MODE_TOP1_COLMAX, 1, 0);
+      launch(L2_MODE_TOP1, 2, 1);
+    }
   }
   l2_rerank_kernel<<<dim3((n_cap + 7) / 8, n_pairs * ndir), 256, 0, st>>>(desc, nkp, n_cap, pairs,
                                                                         nblk, splits, ndir, w);
   l2_compact_kernel<<<n_pairs, L2C_THREADS, 0, st>>>(nkp, kp, n_cap, pairs, nblk, splits, mode, ratio,
-                                                    w, q, t, dist, t2, dist2, pts, n_out);
+                                                    two_pass_only ? 0 : -1, w, q, t, dist, t2, dist2, pts, n_out);
   return check_launch("vo_match_l2_batch");
 }
