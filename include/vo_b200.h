@@ -128,6 +128,44 @@ int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int 
                   double reproj_px, double conf, double* rvec, double* tvec, int32_t* inliers,
                   int32_t* n_inl, int32_t* ok, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- N2: reprojection errors of all map observations (Map.calculate_reprojection_error,
+ * Map.remove_observations_with_reprojection_errors_above_threshold; reference src/map.py:46-97,
+ * called at src/visual_slam.py:181,266) ----
+ * points float64 [n_points,3]; poses float64 [n_cams,16] = TrackedCamera.pose() row-major 4x4;
+ * obs_cam / obs_pt int32 [n_obs] = ROW indices into poses / points; obs_xy float64 [n_obs,2].
+ * sqerr float64 [n_obs] = |dx*dx| + |dy*dy| (NaN for an out-of-range index);
+ * keep uint8 [n_obs] = sqerr < threshold (may be NULL); total float64 [1] = sum of sqerr
+ * (fixed-order tree sum); n_keep int32 [1] (may be NULL). */
+size_t vo_reprojection_workspace_bytes(int n_obs);
+int vo_reprojection_errors(const double* points, int n_points, const double* poses, int n_cams,
+                           const int32_t* obs_cam, const int32_t* obs_pt, const double* obs_xy,
+                           int n_obs, const double* K, double threshold, double* sqerr,
+                           uint8_t* keep, double* total, int32_t* n_keep, void* ws,
+                           size_t ws_bytes, void* stream);
+
+/* ---- N1: feature-track bookkeeping + map association (VisualSlam.feature_mapper,
+ * track_feature_back_in_time, mappointdict, MatchWithMap assembly; reference
+ * src/visual_slam.py:46-50, 94-99, 154-156, 183-229) ----
+ * A feature id (frame_id, idx) (src/frame_generator.py:34-36) is the flat index frame*n_cap+idx.
+ * parent / root / root_point int32 [n_features]: parent = feature_mapper (-1 = none), root = the
+ * id track_feature_back_in_time returns, root_point[id] = row of the map point whose feature_id
+ * is id (-1 = none).  vo_tracks_update inserts the links of one pair's matches (q,t int32
+ * [n_match], mask uint8 or NULL, n_match a DEVICE int32); vo_tracks_match_map emits, in match
+ * order, (KeyPoint.pt of frame2 [k,2], map point [k,3], feature id, point row) of every match
+ * whose root owns a map point: the inputs of solvePnPRansac (visual_slam.py:222-235). */
+int vo_tracks_reset(int32_t* parent, int32_t* root, int32_t* root_point, long n_features,
+                    void* stream);
+int vo_tracks_update(const int32_t* q, const int32_t* t, const uint8_t* mask,
+                     const int32_t* n_match, int frame1, int frame2, int n_cap, int32_t* parent,
+                     int32_t* root, void* stream);
+int vo_tracks_set_points(const int32_t* feature_ids, const int32_t* point_rows, int n,
+                         int32_t* root_point, void* stream);
+int vo_tracks_match_map(const int32_t* q, const int32_t* t, const uint8_t* mask,
+                        const int32_t* n_match, int frame1, int frame2, int n_cap,
+                        const int32_t* root, const int32_t* root_point, const float* kp,
+                        const double* map_points, double* img_xy, double* map_xyz, int32_t* feat2,
+                        int32_t* point_row, int32_t* n_out, void* stream);
+
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).

@@ -16,8 +16,9 @@ def available():
     return os.path.isdir(REFERENCE_SRC)
 
 
-def load():
-    """Returns the reference modules dict: image_pair, frame, frame_generator, initials."""
+def load(extra=()):
+    """Returns the reference modules dict: image_pair, frame, frame_generator, initials (+ the
+    module names in `extra`, e.g. ("map", "tracked_camera", "tracked_point", "observation"))."""
     if not available():
         raise RuntimeError("reference sources not present on this machine")
     sys.dont_write_bytecode = True
@@ -49,16 +50,19 @@ def load():
     except Exception:
         stub("codetiming", Timer=_Timer)
     saved = list(sys.path)
-    shadow = [k for k in ("initials", "image_pair", "frame", "frame_generator") if k in sys.modules]
+    names = ("initials", "image_pair", "frame", "frame_generator") + tuple(extra)
+    shadow = [k for k in names if k in sys.modules]
     kept = {k: sys.modules.pop(k) for k in shadow}
     sys.path.insert(0, REFERENCE_SRC)
     try:
         import initials, frame, frame_generator, image_pair  # noqa: E401
         mods = dict(initials=initials, frame=frame, frame_generator=frame_generator,
                     image_pair=image_pair)
+        for name in extra:
+            mods[name] = __import__(name)
     finally:
         sys.path[:] = saved
-        for k in ("initials", "image_pair", "frame", "frame_generator"):
+        for k in names:
             sys.modules.pop(k, None)
         sys.modules.update(kept)
     return mods

@@ -57,6 +57,14 @@ SIGNATURES = {
     "vo_measure_popc_peak": (_i, [_p, _p]),
     "vo_pnp_workspace_bytes": (_sz, [_i, _i]),
     "vo_pnp_ransac": (_i, [_p, _p, _i, _p, _i, _d, _d, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vo_tracks_reset": (_i, [_p, _p, _p, C.c_long, _p]),
+    "vo_tracks_update": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p]),
+    "vo_tracks_set_points": (_i, [_p, _p, _i, _p, _p]),
+    "vo_tracks_match_map": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p,
+                                 _p]),
+    "vo_reprojection_workspace_bytes": (_sz, [_i]),
+    "vo_reprojection_errors": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _p, _d, _p, _p, _p, _p, _p,
+                                    _sz, _p]),
 }
 
 _lib = None
