@@ -40,14 +40,32 @@ __device__ __forceinline__ uint32_t csa_carry(uint32_t a, uint32_t b, uint32_t c
   asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));  // majority
   return r;
 }
+// FOUR = false: 5 POPC + 14 LOP3;  FOUR = true: a fourth adder over the carries gives
+// popc(ones) + popc(x7) + 2 popc(twos) + 4 popc(fours) = 4 POPC + 16 LOP3.  The kernel alternates
+// the two forms over its query rows so that the XU (POPC) and ALU (LOP3) pipes finish together.
+// The weighted sum of the popcounts runs on the FMA pipe (IMAD with multipliers the compiler
+// cannot see through: `one` = 1, `two` = 2), which is otherwise idle; the ALU pipe keeps LOP3/min.
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+template <bool FOUR>
 __device__ __forceinline__ uint32_t hamming256(const uint32_t (&q)[8], const uint4& ta,
-                                               const uint4& tb) {
+                                               const uint4& tb, uint32_t one, uint32_t two) {
   const uint32_t x0 = q[0] ^ ta.x, x1 = q[1] ^ ta.y, x2 = q[2] ^ ta.z, x3 = q[3] ^ ta.w;
   const uint32_t x4 = q[4] ^ tb.x, x5 = q[5] ^ tb.y, x6 = q[6] ^ tb.z, x7 = q[7] ^ tb.w;
   const uint32_t s1 = csa_sum(x0, x1, x2), c1 = csa_carry(x0, x1, x2);
   const uint32_t s2 = csa_sum(x3, x4, x5), c2 = csa_carry(x3, x4, x5);
   const uint32_t ones = csa_sum(s1, s2, x6), c3 = csa_carry(s1, s2, x6);
-  return (__popc(ones) + __popc(x7)) + 2u * (__popc(c1) + __popc(c2) + __popc(c3));
+  const uint32_t p1 = imad(__popc(ones), one, __popc(x7));
+  if (FOUR) {
+    const uint32_t twos = csa_sum(c1, c2, c3), fours = csa_carry(c1, c2, c3);
+    // p1 + 2 * (popc(twos) + 2 * popc(fours))
+    return imad(imad(__popc(fours), two, __popc(twos)), two, p1);
+  }
+  // p1 + 2 * (popc(c1) + popc(c2) + popc(c3))
+  return imad(imad(__popc(c1), one, imad(__popc(c2), one, __popc(c3))), two, p1);
 }
 
 template <int RQ>
@@ -118,20 +136,51 @@ hamming_top2_kernel(const uint8_t* __restrict__ desc, const int32_t* __restrict_
     m2[r] = KEY_INF;
   }
 
+  const uint32_t sh16 = 65536u + (uint32_t)(n_splits < 0);   // = 65536, opaque: keeps the IMAD
+  const uint32_t one = 1u + (uint32_t)(n_splits < 0), two = 2u + (uint32_t)(n_splits < 0);
   for (int k = 0; k < n_tiles; ++k) {
     const int s = k % HM_NSTAGE;
     const int j0 = (tile_lo + k) * HM_TT;
     const int nj = min(HM_TT, n2 - j0);
     mbar_wait(&full[s], (k / HM_NSTAGE) & 1);
     const uint4* tp = &tile[s][0];
-#pragma unroll 2
-    for (int jj = 0; jj < nj; ++jj) {
+    // two train descriptors per step: their keys are ordered once (lo, hi) and folded into the
+    // running top-2 with 5 min/max instead of 6; key packing runs on the FMA pipe (IMAD)
+    int jj = 0;
+    for (; jj + 1 < nj; jj += 2) {
+      const uint4 ta0 = tp[2 * jj], tb0 = tp[2 * jj + 1];
+      const uint4 ta1 = tp[2 * jj + 2], tb1 = tp[2 * jj + 3];
+      const uint32_t jkey = (uint32_t)(j0 + jj);
+      uint32_t ck0 = KEY_INF, ck1 = KEY_INF;
+#pragma unroll
+      for (int r = 0; r < RQ; ++r) {
+        const uint32_t d0 = (r & 1) ? hamming256<true>(qd[r], ta0, tb0, one, two) : hamming256<false>(qd[r], ta0, tb0, one, two);
+        const uint32_t d1 = (r & 1) ? hamming256<true>(qd[r], ta1, tb1, one, two) : hamming256<false>(qd[r], ta1, tb1, one, two);
+        uint32_t rk0, rk1, c0, c1;
+        asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(rk0) : "r"(d0), "r"(sh16), "r"(jkey));
+        asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(rk1) : "r"(d1), "r"(sh16), "r"(jkey + 1u));
+        asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c0) : "r"(d0), "r"(sh16), "r"(qkey[r]));
+        asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c1) : "r"(d1), "r"(sh16), "r"(qkey[r]));
+        const uint32_t lo = min(rk0, rk1), hi = max(rk0, rk1);
+        m2[r] = __vimin3_u32(m2[r], max(m1[r], lo), hi);
+        m1[r] = min(m1[r], lo);
+        ck0 = min(ck0, c0);
+        ck1 = min(ck1, c1);
+      }
+      ck0 = warp_min_u32(ck0);
+      ck1 = warp_min_u32(ck1);
+      if ((tid & 31) == 0) {
+        atomicMin(&cmin[s][jj], ck0);
+        atomicMin(&cmin[s][jj + 1], ck1);
+      }
+    }
+    if (jj < nj) {   // odd tail of the tile
       const uint4 ta = tp[2 * jj], tb = tp[2 * jj + 1];
       const uint32_t jkey = (uint32_t)(j0 + jj);
       uint32_t ck = KEY_INF;
 #pragma unroll
       for (int r = 0; r < RQ; ++r) {
-        const uint32_t d = hamming256(qd[r], ta, tb);
+        const uint32_t d = hamming256<false>(qd[r], ta, tb, one, two);
         const uint32_t rk = (d << 16) | jkey;
         m2[r] = min(m2[r], max(m1[r], rk));
         m1[r] = min(m1[r], rk);
