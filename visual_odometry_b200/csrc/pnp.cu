@@ -91,6 +91,63 @@ __device__ void jacobi_eigen(double* A, double* V, double* d, int n) {
   for (int i = 0; i < n; ++i) d[i] = A[i * n + i];
 }
 
+
+// Warp-cooperative form of jacobi_eigen for the 12x12 EPnP matrix.  Every lane of the warp runs
+// the same hypothesis (identical local copies); the matrix lives in shared memory and lane k < 12
+// owns element k of the two columns / rows a rotation touches.  The (p, q) order, the formulas
+// and the column-then-row update order are those of the serial routine, so the result is
+// bit-identical to it; only the 3 x 12-element inner loops run in parallel.
+struct Jac12Smem {
+  double A[144], V[144];
+};
+__device__ void jacobi_eigen12_warp(double* Aloc, double* Vloc, double* dloc, Jac12Smem& S) {
+  const int lane = threadIdx.x & 31;
+  const int n = 12;
+  __syncwarp();
+  for (int e = lane; e < 144; e += 32) {
+    S.A[e] = Aloc[e];
+    S.V[e] = ((e / n) == (e % n)) ? 1.0 : 0.0;
+  }
+  __syncwarp();
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    // serial summation order of the reference loop (cheap: 78 adds), done redundantly per lane
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < n; ++i) {
+      diag += S.A[i * n + i] * S.A[i * n + i];
+      for (int j = i + 1; j < n; ++j) off += S.A[i * n + j] * S.A[i * n + j];
+    }
+    if (off <= 1e-30 * diag || off == 0.0) break;
+    for (int p = 0; p < n - 1; ++p)
+      for (int q = p + 1; q < n; ++q) {
+        const double apq = S.A[p * n + q];
+        if (fabs(apq) < 1e-300) continue;
+        const double theta = (S.A[q * n + q] - S.A[p * n + p]) / (2.0 * apq);
+        const double t = copysign(1.0, theta) / (fabs(theta) + sqrt(1.0 + theta * theta));
+        const double c = rsqrt(1.0 + t * t), s = c * t;
+        __syncwarp();
+        if (lane < n) {  // columns p,q
+          const double akp = S.A[lane * n + p], akq = S.A[lane * n + q];
+          S.A[lane * n + p] = c * akp - s * akq;
+          S.A[lane * n + q] = s * akp + c * akq;
+          const double vkp = S.V[lane * n + p], vkq = S.V[lane * n + q];
+          S.V[lane * n + p] = c * vkp - s * vkq;
+          S.V[lane * n + q] = s * vkp + c * vkq;
+        }
+        __syncwarp();
+        if (lane < n) {  // rows p,q
+          const double apk = S.A[p * n + lane], aqk = S.A[q * n + lane];
+          S.A[p * n + lane] = c * apk - s * aqk;
+          S.A[q * n + lane] = s * apk + c * aqk;
+        }
+        __syncwarp();
+      }
+  }
+  __syncwarp();
+  for (int e = 0; e < 144; ++e) Vloc[e] = S.V[e];
+  for (int i = 0; i < n; ++i) dloc[i] = S.A[i * n + i];
+  __syncwarp();
+}
+
 // least squares min |A x - b| for m x n (m >= n, n <= 5) by Householder QR (A, b destroyed)
 __device__ bool ls_solve(double* A, double* b, double* x, int m, int n) {
   for (int k = 0; k < n; ++k) {
@@ -219,7 +276,7 @@ __device__ void epnp_gauss_newton(const Epnp5& E, double* b) {
 }
 
 // full EPnP (epnp.cpp compute_pose) for 5 points; returns false on numerical failure
-__device__ bool epnp5(Epnp5& E, const double* K, double* R, double* t) {
+__device__ bool epnp5(Epnp5& E, const double* K, double* R, double* t, Jac12Smem& S) {
   const double fu = K[0], fv = K[4], uc = K[2], vc = K[5];
   // control points: centroid + principal axes scaled by sqrt(lambda / n)
   double c0[3] = {0, 0, 0};
@@ -271,7 +328,7 @@ __device__ bool epnp5(Epnp5& E, const double* K, double* R, double* t) {
     for (int i = 0; i < 12; ++i)
       for (int j = 0; j < 12; ++j) E.MtM[12 * i + j] += m1[i] * m1[j] + m2[i] * m2[j];
   }
-  jacobi_eigen(E.MtM, E.V, E.ev, 12);
+  jacobi_eigen12_warp(E.MtM, E.V, E.ev, S);
   {  // four smallest eigenvalues, ascending (selection)
     bool used[12];
     for (int i = 0; i < 12; ++i) used[i] = false;
@@ -369,10 +426,15 @@ __global__ void pnp_sample_kernel(int n, int iters, PnpWs w) {
   }
 }
 
-// one thread per RANSAC iteration: EPnP on its 5-point sample
-__global__ void __launch_bounds__(32)
+// one WARP per RANSAC iteration: EPnP on its 5-point sample.  All lanes carry the hypothesis
+// (identical scalar work, same latency as one thread); the 12x12 eigen-decomposition, which is
+// ~90 % of the serial solve, is spread over the lanes in shared memory.
+constexpr int PNP_SOLVE_WARPS = 4;
+__global__ void __launch_bounds__(PNP_SOLVE_WARPS * 32)
 pnp_solve_kernel(const double* __restrict__ K, int iters, PnpWs w) {
-  const int it = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ Jac12Smem sm[PNP_SOLVE_WARPS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int it = blockIdx.x * PNP_SOLVE_WARPS + warp;
   if (it >= iters) return;
   Epnp5 E;
   for (int p = 0; p < 5; ++p) {
@@ -382,11 +444,13 @@ pnp_solve_kernel(const double* __restrict__ K, int iters, PnpWs w) {
   }
   double Kl[9], R[9], t[3];
   for (int e = 0; e < 9; ++e) Kl[e] = K[e];
-  const bool ok = epnp5(E, Kl, R, t);
-  w.valid[it] = ok ? 1 : 0;
-  if (ok) {
-    for (int e = 0; e < 9; ++e) w.models[12 * it + e] = R[e];
-    for (int e = 0; e < 3; ++e) w.models[12 * it + 9 + e] = t[e];
+  const bool ok = epnp5(E, Kl, R, t, sm[warp]);
+  if (lane == 0) {
+    w.valid[it] = ok ? 1 : 0;
+    if (ok) {
+      for (int e = 0; e < 9; ++e) w.models[12 * it + e] = R[e];
+      for (int e = 0; e < 3; ++e) w.models[12 * it + 9 + e] = t[e];
+    }
   }
 }
 
@@ -672,7 +736,7 @@ extern "C" int vo_pnp_ransac(const double* X, const double* x, int n, const doub
   const float thr2 = (float)(reproj_px * reproj_px);
   pnp_prepare_kernel<<<(n + 255) / 256, 256, 0, st>>>(X, x, n, w);
   pnp_sample_kernel<<<1, 32, 0, st>>>(n, iters, w);
-  pnp_solve_kernel<<<(iters + 31) / 32, 32, 0, st>>>(K, iters, w);
+  pnp_solve_kernel<<<(iters + PNP_SOLVE_WARPS - 1) / PNP_SOLVE_WARPS, PNP_SOLVE_WARPS * 32, 0, st>>>(K, iters, w);
   pnp_score_kernel<<<(iters + 7) / 8, 256, 0, st>>>(K, n, iters, thr2, w);
   pnp_select_kernel<<<1, 1024, 0, st>>>(K, n, iters, conf, thr2, w, inliers, n_inl, ok);
   pnp_refine_kernel<<<1, REFINE_THREADS, 0, st>>>(K, w, inliers, rvec, tvec);

@@ -33,23 +33,27 @@ def solve_pnp_ransac(objectPoints, imagePoints, cameraMatrix, distCoeffs=None, r
         raise NotImplementedError("libvo_b200 PnP: the n == 4 (P3P) special case is not implemented")
     lib = _lib.load()
     dev = torch.device("cuda")
-    Xd, xd = torch.from_numpy(X).to(dev), torch.from_numpy(x).to(dev)
-    Kd = torch.from_numpy(np.ascontiguousarray(np.asarray(cameraMatrix, np.float64))).to(dev)
-    rv = torch.zeros(3, dtype=torch.float64, device=dev)
-    tv = torch.zeros(3, dtype=torch.float64, device=dev)
-    inl = torch.empty(n, dtype=torch.int32, device=dev)
-    cnt = torch.zeros(2, dtype=torch.int32, device=dev)
+    # one upload (X | x | K packed as float64) and one download (rvec, tvec | n_inl, ok | inliers)
+    host_in = np.concatenate([X.ravel(), x.ravel(),
+                              np.asarray(cameraMatrix, np.float64).ravel()])
+    din = torch.from_numpy(host_in).to(dev)
+    base = din.data_ptr()
+    out = torch.zeros(48 + 8 + 4 * n, dtype=torch.uint8, device=dev)
+    ob = out.data_ptr()
+    vp = _lib.C.c_void_p
     wsb = lib.vo_pnp_workspace_bytes(n, int(iterationsCount))
     ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
-    _lib.check(lib.vo_pnp_ransac(_lib.ptr(Xd), _lib.ptr(xd), n, _lib.ptr(Kd), int(iterationsCount),
-                                 float(reprojectionError), float(confidence), _lib.ptr(rv),
-                                 _lib.ptr(tv), _lib.ptr(inl), _lib.ptr(cnt[0:1]), _lib.ptr(cnt[1:2]),
+    _lib.check(lib.vo_pnp_ransac(vp(base), vp(base + 24 * n), n, vp(base + 40 * n),
+                                 int(iterationsCount), float(reprojectionError), float(confidence),
+                                 vp(ob), vp(ob + 24), vp(ob + 56), vp(ob + 48), vp(ob + 52),
                                  _lib.ptr(ws), wsb, _lib.cur_stream()))
-    n_inl, ok = (int(v) for v in cnt.tolist())
+    host = out.cpu().numpy()
+    rt = host[:48].view(np.float64)
+    n_inl, ok = (int(v) for v in host[48:56].view(np.int32))
     if not ok:
         return False, np.zeros((3, 1)), np.zeros((3, 1)), None
-    return (True, rv.cpu().numpy().reshape(3, 1), tv.cpu().numpy().reshape(3, 1),
-            inl[:n_inl].cpu().numpy().reshape(-1, 1))
+    return (True, rt[:3].copy().reshape(3, 1), rt[3:6].copy().reshape(3, 1),
+            host[56:56 + 4 * n_inl].view(np.int32).copy().reshape(-1, 1))
 
 
 def rodrigues(src):
