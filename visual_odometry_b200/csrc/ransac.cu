@@ -62,8 +62,15 @@ static RansacWs carve(void* base, int P, int n_cap, int C, int max_iters) {
 constexpr int RANSAC_CHUNK0 = 16;    // first rounds (adaptive runs usually stop inside them)
 constexpr int RANSAC_CHUNK_MAX = 256;
 
-static inline int chunk_cap(int max_iters) {
-  return max_iters < RANSAC_CHUNK_MAX ? (max_iters < 1 ? 1 : max_iters) : RANSAC_CHUNK_MAX;
+// Iterations solved + scored per round.  256 for big batches; for few pairs the cap grows (up to
+// the whole budget) so that a fixed-hypothesis run (config C3: 4096 hypotheses, adaptive stop
+// off) needs one or two rounds instead of sixteen latency-bound ones.  Bounded so that the
+// per-round model store (720 B per iteration per pair) stays below ~190 MB.
+static inline int chunk_cap(int max_iters, int n_pairs) {
+  long cap = 262144L / (n_pairs > 0 ? n_pairs : 1);
+  if (cap < RANSAC_CHUNK_MAX) cap = RANSAC_CHUNK_MAX;
+  if (cap > max_iters) cap = max_iters;
+  return cap < 1 ? 1 : (int)cap;
 }
 
 __device__ __forceinline__ double4 ldg_d4(const double4* p) {
@@ -287,37 +294,76 @@ __device__ int ransac_update_num_iters(double p, double ep, int model_points, in
   return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
 }
 
-__global__ void ransac_scan_kernel(const int32_t* __restrict__ m, int round, int n_pairs, int it0,
-                                   int chunk, int chunk_stride, double conf, int adaptive,
-                                   RansacWs w, double* __restrict__ E_out) {
+// One WARP per active pair.  OpenCV's rule is sequential (strict-greater best, bound shrinks after
+// every improvement, iterations at or beyond the bound never run), but it reduces to prefix
+// maxima: a sample improves the best iff its top count exceeds the running maximum before it, the
+// bound after an improvement is min(previous, f(count)) with f decreasing in the count, so the
+// bound in force at sample s is min(carry, f(running max before s)).  Per block of 32 samples:
+// lane = sample, warp prefix max, f evaluated only by lanes that follow an improvement, first
+// dead sample by ballot, winner = last improving live lane.
+constexpr int SCAN_WARPS = 4;
+__global__ void __launch_bounds__(SCAN_WARPS * 32)
+ransac_scan_kernel(const int32_t* __restrict__ m, int round, int n_pairs, int it0, int chunk,
+                   int chunk_stride, double conf, int adaptive, RansacWs w,
+                   double* __restrict__ E_out) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
   const int n_act = w.n_active[round];
   const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
   int32_t* next = w.active + (size_t)((round + 1) & 1) * n_pairs;
-  for (int a = blockIdx.x * blockDim.x + threadIdx.x; a < n_act; a += gridDim.x * blockDim.x) {
+  for (int a = blockIdx.x * SCAN_WARPS + (threadIdx.x >> 5); a < n_act; a += gridDim.x * SCAN_WARPS) {
     const int p = list[a];
     int niters = w.niters[p], maxgood = w.maxgood[p];
     const int count = m[p];
     int bs = -1, bk = -1;
-    for (int s = 0; s < chunk; ++s) {
-      if (it0 + s >= niters) break;
-      const int nm = w.nmodels[(size_t)p * chunk_stride + s];
-      for (int k = 0; k < nm; ++k) {
-        const int c = w.counts[((size_t)p * chunk_stride + s) * 10 + k];
-        if (c > max(maxgood, 4)) {
-          maxgood = c; bs = s; bk = k;
-          if (adaptive)
-            niters = ransac_update_num_iters(conf, (double)(count - c) / count, 5, niters);
+    bool stop = false;
+    for (int s0 = 0; s0 < chunk && !stop; s0 += 32) {
+      const int s = s0 + lane;
+      // this sample's best count (first k on ties = the one the sequential rule keeps)
+      int c = -1, k_best = 0;
+      if (s < chunk) {
+        const int nm = w.nmodels[(size_t)p * chunk_stride + s];
+        for (int k = 0; k < nm; ++k) {
+          const int ck = w.counts[((size_t)p * chunk_stride + s) * 10 + k];
+          if (ck > c) { c = ck; k_best = k; }
         }
       }
+      // inclusive prefix max over the lanes, then the running max BEFORE this lane
+      int incl = c;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= o) incl = max(incl, v);
+      }
+      int before = __shfl_up_sync(FULL, incl, 1);
+      before = (lane == 0) ? maxgood : max(before, maxgood);
+      // bound in force at this sample
+      int bound = niters;
+      if (adaptive && before > max(maxgood, 4))
+        bound = ransac_update_num_iters(conf, (double)(count - before) / count, 5, niters);
+      const bool dead = (s >= chunk) || (it0 + s >= bound);
+      const unsigned dead_mask = __ballot_sync(FULL, dead);
+      const int first_dead = dead_mask ? __ffs(dead_mask) - 1 : 32;
+      const bool improves = (lane < first_dead) && (c > max(before, 4));
+      const unsigned imp = __ballot_sync(FULL, improves);
+      if (imp) {
+        const int win = 31 - __clz(imp);          // last improvement = highest count so far
+        maxgood = __shfl_sync(FULL, c, win);
+        bs = s0 + win;
+        bk = __shfl_sync(FULL, k_best, win);
+        if (adaptive) niters = ransac_update_num_iters(conf, (double)(count - maxgood) / count, 5, niters);
+      }
+      if (first_dead < 32) stop = true;
     }
-    if (bs >= 0) {
+    if (bs >= 0 && lane < 9) {
       const double* src = w.models + ((size_t)p * chunk_stride + bs) * 90 + 9 * bk;
-      for (int e = 0; e < 9; ++e) E_out[(size_t)p * 9 + e] = src[e];
+      E_out[(size_t)p * 9 + lane] = src[lane];
     }
-    w.niters[p] = niters;
-    w.maxgood[p] = maxgood;
-    if (it0 + chunk >= niters) w.done[p] = 1;
-    else next[atomicAdd(&w.n_active[round + 1], 1)] = p;
+    if (lane == 0) {
+      w.niters[p] = niters;
+      w.maxgood[p] = maxgood;
+      if (it0 + chunk >= niters) w.done[p] = 1;
+      else next[atomicAdd(&w.n_active[round + 1], 1)] = p;
+    }
   }
 }
 
@@ -362,7 +408,7 @@ extern "C" int vo_debug_ransac(int solve_minb) {
 
 extern "C" size_t vo_essential_workspace_bytes(int n_pairs, int n_cap, int max_iters) {
   if (n_pairs <= 0 || n_cap <= 0) return 0;
-  return carve(nullptr, n_pairs, n_cap, chunk_cap(max_iters), max_iters).bytes;
+  return carve(nullptr, n_pairs, n_cap, chunk_cap(max_iters, n_pairs), max_iters).bytes;
 }
 
 extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, int n_cap,
@@ -376,8 +422,14 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
              "vo_essential_ransac_batch: bad sizes");
   VO_REQUIRE(n_pairs <= 65535, VO_ERR_INVALID_ARG,
              "vo_essential_ransac_batch: at most 65535 pairs per call");
-  const int C = chunk_cap(max_iters);
+  // the caller may have sized the workspace for a larger batch (smaller per-round cap): shrink
+  // the cap until the carve fits
+  int C = chunk_cap(max_iters, n_pairs);
   RansacWs w = carve(ws, n_pairs, n_cap, C, max_iters);
+  while (w.bytes > ws_bytes && C > RANSAC_CHUNK_MAX) {
+    C = C / 2 > RANSAC_CHUNK_MAX ? C / 2 : RANSAC_CHUNK_MAX;
+    w = carve(ws, n_pairs, n_cap, C, max_iters);
+  }
   VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_essential_ransac_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
   cudaStream_t st = (cudaStream_t)stream;
@@ -422,8 +474,11 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
       ransac_score_kernel<<<sg, SCORE_WARPS * 32, 0, st>>>(m, n_cap, round, n_pairs, chunk, C, K,
                                                           thr_px, w);
     }
-    ransac_scan_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, it0, chunk, C, conf, adaptive,
-                                                  w, E);
+    {
+      const int want = (n_pairs + SCAN_WARPS - 1) / SCAN_WARPS;
+      ransac_scan_kernel<<<want < sms * 8 ? want : sms * 8, SCAN_WARPS * 32, 0, st>>>(
+          m, round, n_pairs, it0, chunk, C, conf, adaptive, w, E);
+    }
     it0 += chunk;
     ++round;
     if (adaptive) {

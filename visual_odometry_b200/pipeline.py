@@ -103,10 +103,12 @@ class PairPipeline:
         if self.do_chain if chain is None else chain:
             _lib.check(lib.vo_chain_poses(g(self.R), g(self.t), a + B, None, g(self.poses), st))
 
-    def launches_per_run(self):
-        """Number of libvo_b200 kernels one run_device issues (memset excluded)."""
-        rounds, it0, chunk, r = 0, 0, min(16, self.max_iters), 0
-        cap = min(256, self.max_iters)
+    def launches_per_run(self, n_pairs=None):
+        """Number of libvo_b200 kernels one run_device issues (memsets excluded); mirrors the
+        round schedule of vo_essential_ransac_batch (csrc/ransac.cu)."""
+        n_pairs = self.P if n_pairs is None else int(n_pairs)
+        cap = min(self.max_iters, max(256, 262144 // max(n_pairs, 1)))
+        rounds, it0, chunk, r = 0, 0, min(16, cap), 0
         while it0 < self.max_iters:
             chunk = min(chunk, self.max_iters - it0)
             it0 += chunk
