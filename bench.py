@@ -25,7 +25,7 @@ if ROOT not in sys.path:
 N_FRAMES = 1000
 N_KP = 2000
 SEED = 20261104 + 1     # seed = 20261104 + config index
-K1_DRAM_BYTES_PER_LAUNCH = 117627392   # ncu capture of the 999-pair launch (96.6 MB rd + 21.0 MB wr)
+K1_DRAM_BYTES_PER_LAUNCH = 101683200   # ncu capture of the 999-pair launch (85.3 MB rd + 16.4 MB wr)
 METRIC = "frame-pairs/sec (match+E-RANSAC+pose)"
 WORKLOAD = "configs[1]: 1000-frame synthetic drone sequence, ORB 2000 kp, consecutive-pair VO " \
            "with trajectory chaining"
@@ -289,7 +289,7 @@ def run_ours(args, rank, world, local_rank):
                              "(profiles/): XU and ALU pipes both > 80 % busy - together they are "
                              "the bound now",
                      "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum "
-                                       "of this launch (profiles/r1e_k1_hamming_ncu_full_raw.csv); "
+                                       "of this launch (profiles/r1h_k1_hamming_ncu_full_raw.csv); "
                                        "algorithmic 64 MB descriptors + 40 MB keys",
                      "peak_source": "vo_measure_popc_peak live on this GPU (xor+popc+add body); "
                                     "MEASURED_PEAKS.json has no integer entry",
