@@ -121,16 +121,33 @@ class ImagePair():
     def match_features(self):
         dmatches = self.matcher.match(self.frame1.descriptors, self.frame2.descriptors)
         feats1, feats2 = self.frame1.features, self.frame2.features
-
-        def as_match(dm):
+        # colour is unseeded random in the reference too (:250) — excluded from parity; drawn in
+        # one call instead of once per match
+        colors = np.random.random((len(dmatches), 3))
+        raw = []
+        for k, dm in enumerate(dmatches):
             a, b = feats1[dm.queryIdx], feats2[dm.trainIdx]
-            # colour is unseeded random in the reference too (:250) — excluded from parity
-            return Match(a.feature_id, b.feature_id, a.keypoint.pt, b.keypoint.pt,
-                         a.descriptor, b.descriptor, dm.distance, np.random.random((3)))
-
-        self.raw_matches = list(map(as_match, dmatches))
+            raw.append(Match(a.feature_id, b.feature_id, a.keypoint.pt, b.keypoint.pt,
+                             a.descriptor, b.descriptor, dm.distance, colors[k]))
+        self.raw_matches = raw
         # the reference's crude distance gate (src/image_pair.py:254-258; a no-op in practice)
         self.filtered_matches = [mt for mt in self.raw_matches if mt.distance < 1130]
+        self._points_cache = []
+        p1, p2 = getattr(self.frame1, "points", None), getattr(self.frame2, "points", None)
+        if p1 is not None and p2 is not None and len(self.filtered_matches) == len(raw):
+            qi = np.fromiter((dm.queryIdx for dm in dmatches), np.int64, len(dmatches))
+            ti = np.fromiter((dm.trainIdx for dm in dmatches), np.int64, len(dmatches))
+            self._remember_points(self.filtered_matches, p1[qi].astype(np.float64),
+                                  p2[ti].astype(np.float64))
+
+    # pixel coordinates of match lists this object produced itself (identity-keyed, so a list
+    # built or edited by the caller always takes the generic path below)
+    def _remember_points(self, matches, pa, pb):
+        cache = getattr(self, "_points_cache", None)
+        if cache is None:
+            cache = self._points_cache = []
+        cache.append((matches, len(matches), np.ascontiguousarray(pa), np.ascontiguousarray(pb)))
+        del cache[:-4]
 
     def visualize_matches(self, matches):
         """side-by-side canvas with one line per match (reference :260-273)"""
@@ -144,6 +161,9 @@ class ImagePair():
 
     def get_image_points(self, matches):
         """two float64 [M,2] arrays of pixel coordinates (reference :294-299)"""
+        for lst, n, pa, pb in getattr(self, "_points_cache", ()):
+            if lst is matches and n == len(matches):
+                return pa, pb
         both = np.array([tuple(mt.keypoint1) + tuple(mt.keypoint2) for mt in matches],
                         dtype=np.float64).reshape(-1, 4)
         return np.ascontiguousarray(both[:, :2]), np.ascontiguousarray(both[:, 2:])
@@ -155,7 +175,9 @@ class ImagePair():
         # confidence 0.99, threshold 1 px: the reference's constants (:278-279)
         self.essential_matrix, mask = find_essential_mat(pa, pb, self.camera_matrix, 0.99, 1)
         keep = mask.ravel() == 1
-        return [mt for mt, inlier in zip(matches, keep) if inlier]
+        inliers = [mt for mt, inlier in zip(matches, keep) if inlier]
+        self._remember_points(inliers, pa[keep], pb[keep])
+        return inliers
 
     def estimate_camera_movement(self, matches=None):
         if self._legacy:

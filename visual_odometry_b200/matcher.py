@@ -6,6 +6,8 @@ src/image_and_keypoints.py:9,13).  `.match` = mutual nearest neighbour when cros
 nearest neighbour; `.knnMatch(k=2)` = two best, stable by (distance, index); `.ratio_match`
 = Lowe ratio test as in src/feature_detection.py:20-26.  All arithmetic runs in libvo_b200.
 """
+import weakref
+
 import numpy as np
 import torch
 
@@ -29,11 +31,27 @@ class DMatch:
         return f"DMatch(q={self.queryIdx}, t={self.trainIdx}, d={self.distance})"
 
 
+# Device copies of descriptor arrays, keyed by the identity of the host array (a Frame's
+# descriptors are matched twice: as frame2 of one pair, then as frame1 of the next).  Entries die
+# with their array (weakref callback); arrays are treated as immutable once matched.
+_DEV_CACHE = {}
+
+
 def _dev(a, dtype):
     if isinstance(a, torch.Tensor):
         return a.to(device="cuda", dtype=dtype).contiguous()
-    return torch.from_numpy(np.ascontiguousarray(a, dtype={torch.uint8: np.uint8,
-                                                          torch.float32: np.float32}[dtype])).cuda()
+    key = id(a)
+    hit = _DEV_CACHE.get(key)
+    if hit is not None and hit[0]() is a and hit[1].dtype == dtype:
+        return hit[1]
+    t = torch.from_numpy(np.ascontiguousarray(a, dtype={torch.uint8: np.uint8,
+                                                        torch.float32: np.float32}[dtype])).cuda()
+    if isinstance(a, np.ndarray):
+        try:
+            _DEV_CACHE[key] = (weakref.ref(a, lambda _r, k=key: _DEV_CACHE.pop(k, None)), t)
+        except TypeError:
+            pass
+    return t
 
 
 class B200Matcher:
@@ -78,13 +96,20 @@ class B200Matcher:
         return q[:n], t[:n], dist[:n], t2[:n], dist2[:n]
 
     # ---- cv2.BFMatcher surface ----
-    def match(self, queryDescriptors, trainDescriptors, mask=None):
+    def match_host(self, queryDescriptors, trainDescriptors):
+        """(queryIdx, trainIdx, distance) as three Python lists — one device->host transfer."""
         if self.crossCheck:
             q, t, d, _, _ = self.match_arrays(queryDescriptors, trainDescriptors,
                                               _lib.MATCH_MUTUAL)
         else:
             q, t, d, _, _ = self._all_nn(queryDescriptors, trainDescriptors)
-        q, t, d = q.tolist(), t.tolist(), d.tolist()
+        if q.numel() == 0:
+            return [], [], []
+        packed = torch.stack((q, t, d.view(torch.int32))).cpu().numpy()
+        return packed[0].tolist(), packed[1].tolist(), packed[2].view(np.float32).tolist()
+
+    def match(self, queryDescriptors, trainDescriptors, mask=None):
+        q, t, d = self.match_host(queryDescriptors, trainDescriptors)
         return [DMatch(a, b, c) for a, b, c in zip(q, t, d)]
 
     def _all_nn(self, d1, d2):
