@@ -2,8 +2,10 @@
 structures (Python dicts keyed by (frame_id, idx) tuples), restated from src/visual_slam.py:
   update_feature_mapper :183-188, track_feature_back_in_time :94-99,
   mappointdict :154-156 / :193-196, MatchWithMap assembly :202-229.
-"parity unpinned" by the reference (it has no tests or fixtures for this); the
-restatement follows the cited lines statement by statement.  Only tests/ may import this."""
+Pinned: tests/golden/tracks.npz holds the roots and the solvePnPRansac argument arrays produced by
+the reference's own VisualSlam on a seeded match sequence (tests/golden/make_golden_tracks.py runs
+/root/reference/src/visual_slam.py unmodified); tests/test_oracle_tracks.py checks this file
+against it.  Only tests/ may import this."""
 
 
 class TracksOracle:

@@ -84,3 +84,38 @@ def test_tracks_feed_pnp_on_device(cuda_dev):
     okr, rr, tr_, inr = cv2.solvePnPRansac(xyz.cpu().numpy(), img.cpu().numpy(), seq.K, np.zeros(4))
     ang = lambda A, B: np.arccos(np.clip((np.trace(A.T @ B) - 1) / 2, -1, 1))
     assert ang(cv2.Rodrigues(rvec)[0], cv2.Rodrigues(rr)[0]) < 1e-3
+
+
+def test_tracks_equal_reference_golden(cuda_dev):
+    """tests/golden/tracks.npz (made by the reference's own VisualSlam): the device bookkeeping
+    returns the same roots and the same solvePnPRansac argument arrays, bit for bit."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tracks.npz"))
+    F, N = int(g["F"]), int(g["N"])
+    cap = N + 8                                   # some map points carry idx >= N
+    tr = FeatureTracks(F, cap)
+    kp = np.zeros((F, cap, 2), np.float32)
+    for b in range(F - 1):
+        kp[b + 1, g[f"f2_{b}"][:, 1]] = g[f"kp2_{b}"]
+    kp_d = torch.from_numpy(kp).cuda()
+    n_calls = 0
+    for b in range(F - 1):
+        f1, f2 = g[f"f1_{b}"], g[f"f2_{b}"]
+        assert (f1[:, 0] == b).all() and (f2[:, 0] == b + 1).all()
+        q = torch.from_numpy(f1[:, 1].astype(np.int32)).cuda()
+        t = torch.from_numpy(f2[:, 1].astype(np.int32)).cuda()
+        n = torch.tensor([len(f1)], dtype=torch.int32, device="cuda")
+        tr.update(q, t, None, n, b, b + 1)
+        n_map = int(g[f"n_map_{b}"])
+        ids = g["map_ids"][:n_map]
+        tr.set_map_points(ids[:, 0] * cap + ids[:, 1])
+        roots = tr.root_of([tr.feature_id(b + 1, i) for i in range(N)]).cpu().numpy()
+        want = g[f"roots_{b}"]
+        assert np.array_equal(roots, want[:, 0] * cap + want[:, 1])
+        if int(g[f"called_{b}"]):
+            xyz_d = torch.from_numpy(g["map_xyz"][:n_map]).cuda()
+            img, xyz, _, _ = tr.matches_with_map(q, t, None, n, b, b + 1, kp_d, xyz_d)
+            assert np.array_equal(img.cpu().numpy(), g[f"img_{b}"])
+            assert np.array_equal(xyz.cpu().numpy(), g[f"obj_{b}"])
+            n_calls += 1
+    assert n_calls == F - 2
