@@ -166,6 +166,32 @@ int vo_tracks_match_map(const int32_t* q, const int32_t* t, const uint8_t* mask,
                         const double* map_points, double* img_xy, double* map_xyz, int32_t* feat2,
                         int32_t* point_row, int32_t* n_out, void* stream);
 
+/* ---- N1/N2: map growth and pruning on the flat, device-resident map ----
+ * vo_map_extend = the loop of VisualSlam.add_information_to_map (src/visual_slam.py:172-179,
+ * with :100-150) and, on an empty map with max_norm = +inf, of initialize_map (:49-52, :69-83).
+ * For the masked matches of one pair, in match order: skip if |X| > max_norm (X = row r of the
+ * triangulated points, r = rank among the masked matches, x_stride doubles per row); if the
+ * track root of (frame2, t[i]) owns a map point append Observation(point, cam2_row, pt2), else
+ * append a point (X, feature id frame1*n_cap+q[i]) and two observations (cam1_row pt1, cam2_row
+ * pt2).  n_points / n_obs are DEVICE counters, read and advanced by the call; lookups never see
+ * the points appended by the same call (the reference builds mappointdict before the loop);
+ * publish != 0 writes root_point[] for the new points afterwards (the rebuild at :193-196).
+ * *status (device int32) is set to 1 and nothing is committed if cap_points / cap_obs is too small.
+ * vo_map_prune_observations = Map.remove_observations_with_reprojection_errors_above_threshold
+ * (src/map.py:46-70) given the keep flags of vo_reprojection_errors: stable compaction of the
+ * observation rows into a second set of arrays (must not alias); n_out a device int32. */
+int vo_map_extend(const int32_t* q, const int32_t* t, const uint8_t* mask, const int32_t* n_match,
+                  int frame1, int frame2, int n_cap, const int32_t* root, int32_t* root_point,
+                  const float* kp, const double* X, int x_stride, int cam1_row, int cam2_row,
+                  double max_norm, double* points, int32_t* point_fid, int32_t* n_points,
+                  int cap_points, double* obs_xy, int32_t* obs_cam, int32_t* obs_pt,
+                  int32_t* n_obs, int cap_obs, int publish, int32_t* status, void* stream);
+size_t vo_map_prune_workspace_bytes(int n_obs);
+int vo_map_prune_observations(const uint8_t* keep, int n_obs, const int32_t* obs_cam_in,
+                              const int32_t* obs_pt_in, const double* obs_xy_in,
+                              int32_t* obs_cam_out, int32_t* obs_pt_out, double* obs_xy_out,
+                              int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).

@@ -65,6 +65,10 @@ SIGNATURES = {
     "vo_reprojection_workspace_bytes": (_sz, [_i]),
     "vo_reprojection_errors": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _p, _d, _p, _p, _p, _p, _p,
                                     _sz, _p]),
+    "vo_map_extend": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _i, _i, _i, _d, _p, _p, _p,
+                           _i, _p, _p, _p, _p, _i, _i, _p, _p]),
+    "vo_map_prune_workspace_bytes": (_sz, [_i]),
+    "vo_map_prune_observations": (_i, [_p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
 }
 
 _lib = None

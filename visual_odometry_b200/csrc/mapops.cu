@@ -127,3 +127,236 @@ extern "C" int vo_reprojection_errors(const double* points, int n_points, const 
   reproj_total_kernel<<<1, 32, 0, st>>>(block_sums, block_keep, nb, total, n_keep);
   return check_launch("vo_reprojection_errors");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Map growth and pruning on the device-resident structure-of-arrays map.
+//
+// vo_map_extend = the loop of VisualSlam.add_information_to_map (src/visual_slam.py:172-179) with
+// add_point_observation_to_map / add_new_observation_of_existing_point / add_new_match_to_map
+// (:100-150), and, with max_norm = +inf on an empty map, the two loops of initialize_map
+// (:49-52, :69-83).  For every 3-D match, in match order:
+//     if |point| > 50: skip
+//     root = track_feature_back_in_time(featureid2)
+//     root in mappointdict ? append Observation(point, camera2, keypoint2)
+//                          : append TrackedPoint(point, featureid1), Observation(.., camera1,
+//                            keypoint1), Observation(.., camera2, keypoint2)
+// mappointdict is built BEFORE the loop (:154-156) and not touched inside it, so the lookups of
+// one call never see the points the same call appends; the new points are published to
+// root_point[] after the loop (what the rebuilds at :193-196 / :238-240 do next).
+// One block: an ordered (stable) compaction with two running offsets, n <= a few thousand.
+namespace vo {
+
+constexpr int EXT_THREADS = 1024;
+
+__device__ __forceinline__ int2 block_excl_scan2(int a, int b, int2* warp_tot, int2& total) {
+  // exclusive prefix sums of (a, b) over the block, in thread order
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int sa = a, sb = b;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int ua = __shfl_up_sync(0xffffffffu, sa, o), ub = __shfl_up_sync(0xffffffffu, sb, o);
+    if (lane >= o) { sa += ua; sb += ub; }
+  }
+  if (lane == 31) warp_tot[wid] = make_int2(sa, sb);
+  __syncthreads();
+  int oa = 0, ob = 0, ta = 0, tb = 0;
+  for (int w = 0; w < EXT_THREADS / 32; ++w) {
+    const int2 v = warp_tot[w];
+    if (w < wid) { oa += v.x; ob += v.y; }
+    ta += v.x; tb += v.y;
+  }
+  __syncthreads();
+  total = make_int2(ta, tb);
+  return make_int2(oa + sa - a, ob + sb - b);
+}
+
+__global__ void __launch_bounds__(EXT_THREADS)
+map_extend_kernel(const int32_t* __restrict__ q, const int32_t* __restrict__ t,
+                  const uint8_t* __restrict__ mask, const int32_t* __restrict__ n_match, int f1,
+                  int f2, int n_cap, const int32_t* __restrict__ root, int32_t* root_point,
+                  const float* __restrict__ kp, const double* __restrict__ X, int x_stride,
+                  int cam1, int cam2, double max_norm, double* __restrict__ points,
+                  int32_t* point_fid, int32_t* n_points, int cap_points,
+                  double* __restrict__ obs_xy, int32_t* __restrict__ obs_cam,
+                  int32_t* __restrict__ obs_pt, int32_t* n_obs, int cap_obs, int publish,
+                  int32_t* __restrict__ status) {
+  __shared__ int2 warp_tot[EXT_THREADS / 32];
+  const int tid = threadIdx.x;
+  const int n = *n_match;
+  const int p0 = *n_points, o0 = *n_obs;
+  int rank_base = 0, p_base = 0, o_base = 0;
+  bool overflow = false;
+  for (int i0 = 0; i0 < n; i0 += EXT_THREADS) {
+    const int i = i0 + tid;
+    const bool inl = i < n && (!mask || mask[i]);
+    int2 tot;
+    const int rank = rank_base + block_excl_scan2(inl, 0, warp_tot, tot).x;
+    rank_base += tot.x;
+    bool live = false, existing = false;
+    int prow = -1;
+    double P[3] = {0.0, 0.0, 0.0};
+    if (inl) {
+      const double* x = X + (size_t)rank * x_stride;
+      P[0] = x[0]; P[1] = x[1]; P[2] = x[2];
+      // np.linalg.norm: sqrt of the sum of squares; `norm > 50` is false for NaN
+      const double nrm = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(P[0], P[0]), __dmul_rn(P[1], P[1])),
+                                        __dmul_rn(P[2], P[2])));
+      live = !(nrm > max_norm);
+      if (live) {
+        prow = root_point[root[f2 * n_cap + t[i]]];
+        existing = prow >= 0;
+      }
+    }
+    const int no = live ? (existing ? 1 : 2) : 0, np = (live && !existing) ? 1 : 0;
+    const int2 off = block_excl_scan2(no, np, warp_tot, tot);
+    const int oi = o0 + o_base + off.x, pi = p0 + p_base + off.y;
+    o_base += tot.x;
+    p_base += tot.y;
+    if (live) {
+      const float2 k2 = reinterpret_cast<const float2*>(kp)[(size_t)f2 * n_cap + t[i]];
+      if (existing) {
+        if (oi < cap_obs) {
+          obs_pt[oi] = prow; obs_cam[oi] = cam2;
+          obs_xy[2 * oi] = (double)k2.x; obs_xy[2 * oi + 1] = (double)k2.y;
+        } else overflow = true;
+      } else {
+        if (pi < cap_points && oi + 1 < cap_obs) {
+          const float2 k1 = reinterpret_cast<const float2*>(kp)[(size_t)f1 * n_cap + q[i]];
+          points[3 * (size_t)pi] = P[0]; points[3 * (size_t)pi + 1] = P[1];
+          points[3 * (size_t)pi + 2] = P[2];
+          point_fid[pi] = f1 * n_cap + q[i];
+          obs_pt[oi] = pi; obs_cam[oi] = cam1;
+          obs_xy[2 * oi] = (double)k1.x; obs_xy[2 * oi + 1] = (double)k1.y;
+          obs_pt[oi + 1] = pi; obs_cam[oi + 1] = cam2;
+          obs_xy[2 * oi + 2] = (double)k2.x; obs_xy[2 * oi + 3] = (double)k2.y;
+        } else overflow = true;
+      }
+    }
+  }
+  const int any_over = __syncthreads_or(overflow);
+  const int p1 = min(p0 + p_base, cap_points), o1 = min(o0 + o_base, cap_obs);
+  if (publish && !any_over)
+    for (int r = p0 + tid; r < p1; r += EXT_THREADS) root_point[point_fid[r]] = r;
+  if (tid == 0) {
+    if (any_over) {            // nothing is committed when the arrays are too small
+      *status = 1;
+    } else {
+      *n_points = p1;
+      *n_obs = o1;
+    }
+  }
+}
+
+// remove_observations_with_reprojection_errors_above_threshold (src/map.py:46-70) on the flat
+// arrays: stable compaction of the observation rows by keep flags (the flags come from
+// vo_reprojection_errors).  count -> scan -> scatter, output in a second set of arrays.
+__global__ void __launch_bounds__(MAPOPS_THREADS)
+prune_count_kernel(const uint8_t* __restrict__ keep, int n, int32_t* __restrict__ block_cnt) {
+  const int i = blockIdx.x * MAPOPS_THREADS + threadIdx.x;
+  const int c = __syncthreads_count(i < n && keep[i]);
+  if (threadIdx.x == 0) block_cnt[blockIdx.x] = c;
+}
+
+__global__ void __launch_bounds__(1024)
+prune_scan_kernel(int32_t* __restrict__ block_cnt, int nb, int32_t* __restrict__ n_out) {
+  // in-place exclusive scan of the block counts, one block, tiles of 1024 with a running base
+  __shared__ int wsum[32];
+  __shared__ int base_s;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) base_s = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < nb; b0 += 1024) {
+    const int b = b0 + tid;
+    const int v = b < nb ? block_cnt[b] : 0;
+    int s = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, s, o);
+      if (lane >= o) s += u;
+    }
+    if (lane == 31) wsum[wid] = s;
+    __syncthreads();
+    int off = base_s;
+    for (int w = 0; w < wid; ++w) off += wsum[w];
+    if (b < nb) block_cnt[b] = off + s - v;
+    __syncthreads();
+    if (tid == 1023) base_s = off + s;
+    __syncthreads();
+  }
+  if (tid == 0) *n_out = base_s;
+}
+
+__global__ void __launch_bounds__(MAPOPS_THREADS)
+prune_scatter_kernel(const uint8_t* __restrict__ keep, int n, const int32_t* __restrict__ block_off,
+                     const int32_t* __restrict__ cam_in, const int32_t* __restrict__ pt_in,
+                     const double* __restrict__ xy_in, int32_t* __restrict__ cam_out,
+                     int32_t* __restrict__ pt_out, double* __restrict__ xy_out) {
+  __shared__ int wcnt[MAPOPS_THREADS / 32];
+  const int i = blockIdx.x * MAPOPS_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const bool k = i < n && keep[i];
+  const unsigned bal = __ballot_sync(0xffffffffu, k);
+  if (lane == 0) wcnt[wid] = __popc(bal);
+  __syncthreads();
+  if (!k) return;
+  int off = block_off[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
+  for (int w = 0; w < wid; ++w) off += wcnt[w];
+  cam_out[off] = cam_in[i];
+  pt_out[off] = pt_in[i];
+  reinterpret_cast<double2*>(xy_out)[off] = reinterpret_cast<const double2*>(xy_in)[i];
+}
+
+}  // namespace vo
+
+extern "C" int vo_map_extend(const int32_t* q, const int32_t* t, const uint8_t* mask,
+                             const int32_t* n_match, int frame1, int frame2, int n_cap,
+                             const int32_t* root, int32_t* root_point, const float* kp,
+                             const double* X, int x_stride, int cam1_row, int cam2_row,
+                             double max_norm, double* points, int32_t* point_fid,
+                             int32_t* n_points, int cap_points, double* obs_xy, int32_t* obs_cam,
+                             int32_t* obs_pt, int32_t* n_obs, int cap_obs, int publish,
+                             int32_t* status, void* stream) {
+  VO_REQUIRE(q && t && n_match && root && root_point && kp && X && points && point_fid &&
+                 n_points && obs_xy && obs_cam && obs_pt && n_obs && status,
+             VO_ERR_INVALID_ARG, "vo_map_extend: null pointer");
+  VO_REQUIRE(n_cap > 0 && frame1 >= 0 && frame2 >= 0 && x_stride >= 3 && cap_points >= 0 &&
+                 cap_obs >= 0 && cam1_row >= 0 && cam2_row >= 0,
+             VO_ERR_INVALID_ARG, "vo_map_extend: bad sizes");
+  map_extend_kernel<<<1, EXT_THREADS, 0, (cudaStream_t)stream>>>(
+      q, t, mask, n_match, frame1, frame2, n_cap, root, root_point, kp, X, x_stride, cam1_row,
+      cam2_row, max_norm, points, point_fid, n_points, cap_points, obs_xy, obs_cam, obs_pt, n_obs,
+      cap_obs, publish, status);
+  return check_launch("vo_map_extend");
+}
+
+extern "C" size_t vo_map_prune_workspace_bytes(int n_obs) {
+  const size_t nb = (size_t)((n_obs > 0 ? n_obs : 0) + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
+  return nb * sizeof(int32_t) + 256;
+}
+
+extern "C" int vo_map_prune_observations(const uint8_t* keep, int n_obs, const int32_t* obs_cam_in,
+                                         const int32_t* obs_pt_in, const double* obs_xy_in,
+                                         int32_t* obs_cam_out, int32_t* obs_pt_out,
+                                         double* obs_xy_out, int32_t* n_out, void* ws,
+                                         size_t ws_bytes, void* stream) {
+  VO_REQUIRE(n_obs >= 0 && n_out, VO_ERR_INVALID_ARG, "vo_map_prune_observations: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_obs == 0) {
+    cudaMemsetAsync(n_out, 0, sizeof(int32_t), st);
+    return check_launch("vo_map_prune_observations");
+  }
+  VO_REQUIRE(keep && obs_cam_in && obs_pt_in && obs_xy_in && obs_cam_out && obs_pt_out &&
+                 obs_xy_out && ws,
+             VO_ERR_INVALID_ARG, "vo_map_prune_observations: null pointer");
+  VO_REQUIRE(obs_cam_in != obs_cam_out && obs_pt_in != obs_pt_out && obs_xy_in != obs_xy_out,
+             VO_ERR_INVALID_ARG, "vo_map_prune_observations: output must not alias the input");
+  VO_REQUIRE(ws_bytes >= vo_map_prune_workspace_bytes(n_obs), VO_ERR_WORKSPACE,
+             "vo_map_prune_observations: workspace too small");
+  const int nb = (n_obs + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
+  int32_t* cnt = (int32_t*)ws;
+  prune_count_kernel<<<nb, MAPOPS_THREADS, 0, st>>>(keep, n_obs, cnt);
+  prune_scan_kernel<<<1, 1024, 0, st>>>(cnt, nb, n_out);
+  prune_scatter_kernel<<<nb, MAPOPS_THREADS, 0, st>>>(keep, n_obs, cnt, obs_cam_in, obs_pt_in,
+                                                     obs_xy_in, obs_cam_out, obs_pt_out, obs_xy_out);
+  return check_launch("vo_map_prune_observations");
+}
