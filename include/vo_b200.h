@@ -192,6 +192,23 @@ int vo_map_prune_observations(const uint8_t* keep, int n_obs, const int32_t* obs
                               int32_t* obs_cam_out, int32_t* obs_pt_out, double* obs_xy_out,
                               int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- N3: local bundle adjustment (Map.optimize_map, reference src/map.py:104-186: g2o
+ * Levenberg + BlockSolverSE3 (Schur complement on the points) + EdgeProjectXYZ2UV + Huber,
+ * optimize(iterations)) on the flat map.  poses double [n_cams,16] (row-major 4x4, world->camera)
+ * and points double [n_points,3] are updated in place; fixed uint8 [n_cams] (TrackedCamera.fixed);
+ * observations as for vo_reprojection_errors; focal / cx / cy as g2o.CameraParameters (ONE focal
+ * length); huber_delta = 1 is g2o's RobustKernelHuber default (<= 0: no robust kernel).
+ * n_cams <= 24.  log_chi2 / log_lambda / log_trials (HOST arrays [iterations], may be NULL),
+ * n_iterations and chi2_initial (HOST, may be NULL) report the run.  Sums run in a fixed order:
+ * results are reproducible.  UNLIKE the other entry points this one SYNCHRONISES its stream: the
+ * LM accept / reject decision is taken on the host from one 32-byte read-back per trial. */
+size_t vo_bundle_adjust_workspace_bytes(int n_cams, int n_points, int n_obs);
+int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams, double* points, int n_points,
+                     const int32_t* obs_cam, const int32_t* obs_pt, const double* obs_xy, int n_obs,
+                     double focal, double cx, double cy, double huber_delta, int iterations,
+                     double* log_chi2, double* log_lambda, int32_t* log_trials, int* n_iterations,
+                     double* chi2_initial, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).

@@ -37,6 +37,7 @@ class DeviceMap:
         self._cur = 0
         self.poses = torch.zeros(self.cap_cams, 16, dtype=F64, device=self.dev)
         self.cam_frame = []                                   # frame id of every camera row
+        self.fixed = torch.zeros(self.cap_cams, dtype=U8, device=self.dev)
         self.n_points = torch.zeros(1, dtype=I32, device=self.dev)
         self.n_obs = torch.zeros(1, dtype=I32, device=self.dev)
         self.status = torch.zeros(1, dtype=I32, device=self.dev)
@@ -68,8 +69,8 @@ class DeviceMap:
         return c[0], c[1]
 
     # ------------------------------------------------------------------ cameras
-    def add_camera(self, R, t, frame_id):
-        """map.add_camera(TrackedCamera(R, t, frame_id, ...)): returns the camera row."""
+    def add_camera(self, R, t, frame_id, fixed=False):
+        """map.add_camera(TrackedCamera(R, t, frame_id, ..., fixed)): returns the camera row."""
         row = len(self.cam_frame)
         if row >= self.cap_cams:
             raise RuntimeError("DeviceMap: cap_cams exceeded")
@@ -78,7 +79,28 @@ class DeviceMap:
         T[:3, 3] = np.asarray(t, np.float64).ravel()[:3]
         self.poses[row].copy_(torch.from_numpy(T.reshape(16)))
         self.cam_frame.append(int(frame_id))
+        self.fixed[row] = int(bool(fixed))
         return row
+
+    def freeze_nonlast_cameras(self):
+        """VisualSlam.freeze_nonlast_cameras (src/visual_slam.py:270-275): only the last camera
+        (and the one before it when there are more than two) stays free."""
+        n = len(self.cam_frame)
+        f = torch.ones(n, dtype=U8)
+        f[n - 1] = 0
+        if n > 2:
+            f[n - 2] = 0
+        self.fixed[:n].copy_(f)
+
+    def optimize(self, iterations=40, huber_delta=1.0):
+        """Map.optimize_map (src/map.py:104-186) on the device arrays, in place."""
+        from .ba import bundle_adjust
+        n_pts, n_obs = self.counts()
+        if n_obs == 0:
+            return None
+        return bundle_adjust(self.poses, self.fixed, self.points, self.obs_cam, self.obs_pt,
+                             self.obs_xy, self.K.reshape(3, 3), iterations, huber_delta,
+                             n_cams=len(self.cam_frame), n_points=n_pts, n_obs=n_obs)
 
     def camera_row(self, frame_id):
         return self.cam_frame.index(int(frame_id))
@@ -111,8 +133,8 @@ class DeviceMap:
         self.cam_frame = []
         self.tracks.reset()
         self.update_tracks(q, t, mask, n_match, frame1, frame2)
-        self.add_camera(np.eye(3), np.zeros(3), frame1)
-        self.add_camera(R, t_vec, frame2)
+        self.add_camera(np.eye(3), np.zeros(3), frame1, fixed=True)
+        self.add_camera(R, t_vec, frame2, fixed=False)
         self.extend(q, t, mask, n_match, frame1, frame2, kp, X, max_norm=float("inf"))
 
     # ------------------------------------------------------------------ reprojection

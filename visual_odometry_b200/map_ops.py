@@ -92,8 +92,12 @@ def calculate_reprojection_error_for_point(self, point, camera_pose, image_coord
     return float(out["sqerr"][0])
 
 
-def patch_map(MapClass):
-    """Rebind the reprojection methods of the reference's Map class to the GPU versions."""
+def patch_map(MapClass, bundle_adjustment=True):
+    """Rebind the reprojection methods (and optimize_map) of the reference's Map class to the GPU
+    versions."""
+    if bundle_adjustment:
+        from .ba import optimize_map
+        MapClass.optimize_map = optimize_map
     MapClass.calculate_reprojection_error = calculate_reprojection_error
     MapClass.remove_observations_with_reprojection_errors_above_threshold = \
         remove_observations_with_reprojection_errors_above_threshold
