@@ -14,8 +14,10 @@ base_binary_edge.hpp (robustified quadratic form: first-order weight only), robu
 CameraParameters::cam_map uses ONE focal length for both axes), types/slam3d/se3quat.h (exp map,
 update = exp(dx) * T with dx = (omega, upsilon))).
 PARITY UNPINNED against g2o itself (the reference holds no BA fixture: test.g2o is a one-line
-parameter dump).  Independent check in tests/test_oracle_ba.py: the minimum found agrees with
-scipy.optimize.least_squares(loss="huber") on the same cost.  Only tests/ may import this module.
+parameter dump).  Independent checks in tests/test_oracle_ba.py: analytic Jacobians against central
+differences of the error under the update rule, the Schur solution against the full damped system,
+first-order optimality of the result, and scipy.optimize.least_squares started from the result
+being unable to lower the same robust cost.  Only tests/ may import this module.
 """
 import numpy as np
 
@@ -53,6 +55,22 @@ def huber(e2, delta=HUBER_DELTA):
     s = np.sqrt(np.maximum(e2, 1e-300))
     out = e2 > d2
     return np.where(out, 2 * s * delta - d2, e2), np.where(out, delta / s, 1.0)
+
+
+def inv3(V):
+    """3x3 inverses by cofactors / determinant (what Eigen's fixed-size inverse() does): a
+    singular block gives inf / nan instead of raising, and the LM loop then rejects the step."""
+    a, b, c = V[:, 0, 0], V[:, 0, 1], V[:, 0, 2]
+    d, e, g = V[:, 1, 1], V[:, 1, 2], V[:, 2, 2]
+    c00, c01, c02 = d * g - e * e, c * e - b * g, b * e - c * d
+    with np.errstate(all="ignore"):
+        idet = 1.0 / (a * c00 + b * c01 + c * c02)
+        out = np.empty_like(V)
+        out[:, 0, 0], out[:, 0, 1], out[:, 0, 2] = c00 * idet, c01 * idet, c02 * idet
+        out[:, 1, 1], out[:, 1, 2], out[:, 2, 2] = (a * g - c * c) * idet, (b * c - a * e) * idet, \
+            (a * d - b * b) * idet
+    out[:, 1, 0], out[:, 2, 0], out[:, 2, 1] = out[:, 0, 1], out[:, 0, 2], out[:, 1, 2]
+    return out
 
 
 class BAState:
@@ -134,7 +152,7 @@ class BAProblem:
         cam_free = self.cam_active & ~self.fixed
         V = Hll + lam * np.eye(3)
         V[~self.pt_active] = np.eye(3)
-        Vinv = np.linalg.inv(V)
+        Vinv = inv3(V)
         Y = np.einsum("mij,mjk->mik", Hpl, Vinv[self.obs_pt])          # Hpl * Hll^-1
         S = np.zeros((C, 6, C, 6))
         for c in range(C):
@@ -153,6 +171,8 @@ class BAProblem:
                         continue
                     S[self.obs_cam[i], :, self.obs_cam[j], :] -= Y[i] @ Hpl[j].T
         S2 = S.reshape(6 * C, 6 * C)
+        if not np.all(np.isfinite(S2)):
+            return None, None, False
         try:
             L = np.linalg.cholesky(S2)
         except np.linalg.LinAlgError:

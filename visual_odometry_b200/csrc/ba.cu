@@ -29,15 +29,22 @@ namespace vo {
 constexpr int BA_THREADS = 256;
 constexpr int BA_MAX_CAMS = 24;
 constexpr int BA_LM_MAX_TRIALS = 10;
+constexpr int BA_PT_LANES = 4;            // lanes that share one point's observation list
+
+constexpr int BA_TARGET_BLOCKS = 296;     // 2 x 148 SMs: how far the per-camera loops are split
+constexpr int BA_MAX_SPLIT = 64;
+constexpr int BA_SPART_ROWS = BA_TARGET_BLOCKS + BA_MAX_CAMS * (BA_MAX_CAMS + 1) / 2 + 8;
+constexpr int BA_CPART_ROWS = BA_TARGET_BLOCKS + BA_MAX_CAMS + 8;
 
 struct BAWs {
-  int32_t *pt_start, *pt_cursor, *pt_obs, *cam_start, *cam_obs, *cam_count, *bad;
-  double *JA, *JB, *we, *W, *Y;           // per observation, component-major [k * M + i]
+  int32_t *pt_start, *pt_cursor, *pt_obs, *cam_start, *cam_obs, *cam_count, *bad, *flist;
+  double *OA, *OB, *OW;                   // per-observation records [M,10] [M,12] [M,18]
   double *Hll, *bl, *Hpp, *bp;            // [P,6] [P,3] [C,21] [C,6]
-  double *S, *bs, *xp;                    // [C,C,36] [6C] [6C]
+  double *Spart, *Cpart, *xp;             // [pairs*NS,42] [nf*NSc,27] [6C]
   double *trial_points, *trial_poses;     // [P,3] [C,16]
   double *chi_part, *scale_part, *stats;  // block partials; stats[0..7]
   unsigned long long* maxdiag;
+  unsigned int* ticket;
   size_t bytes;
 };
 
@@ -53,24 +60,24 @@ static BAWs ba_carve(void* base, int C, int P, int M) {
   w.cam_obs = (int32_t*)take(sizeof(int32_t) * (size_t)M);
   w.cam_count = (int32_t*)take(sizeof(int32_t) * (C + 1));
   w.bad = (int32_t*)take(sizeof(int32_t));
-  w.JA = (double*)take(sizeof(double) * 6 * (size_t)M);
-  w.JB = (double*)take(sizeof(double) * 12 * (size_t)M);
-  w.we = (double*)take(sizeof(double) * 3 * (size_t)M);
-  w.W = (double*)take(sizeof(double) * 18 * (size_t)M);
-  w.Y = (double*)take(sizeof(double) * 18 * (size_t)M);
+  w.flist = (int32_t*)take(sizeof(int32_t) * (C + 1));
+  w.OA = (double*)take(sizeof(double) * 10 * (size_t)M);
+  w.OB = (double*)take(sizeof(double) * 12 * (size_t)M);
+  w.OW = (double*)take(sizeof(double) * 18 * (size_t)M);
   w.Hll = (double*)take(sizeof(double) * 6 * (size_t)P);
   w.bl = (double*)take(sizeof(double) * 3 * (size_t)P);
   w.Hpp = (double*)take(sizeof(double) * 21 * C);
   w.bp = (double*)take(sizeof(double) * 6 * C);
-  w.S = (double*)take(sizeof(double) * 36 * C * C);
-  w.bs = (double*)take(sizeof(double) * 6 * C);
+  w.Spart = (double*)take(sizeof(double) * 42 * BA_SPART_ROWS);
+  w.Cpart = (double*)take(sizeof(double) * 27 * BA_CPART_ROWS);
   w.xp = (double*)take(sizeof(double) * 6 * C);
   w.trial_points = (double*)take(sizeof(double) * 3 * (size_t)P);
   w.trial_poses = (double*)take(sizeof(double) * 16 * C);
   w.chi_part = (double*)take(sizeof(double) * (nbo + 1));
-  w.scale_part = (double*)take(sizeof(double) * (nbp + 1));
+  w.scale_part = (double*)take(sizeof(double) * ((size_t)nbp * BA_PT_LANES + 2));
   w.stats = (double*)take(sizeof(double) * 8);
   w.maxdiag = (unsigned long long*)take(sizeof(unsigned long long));
+  w.ticket = (unsigned int*)take(sizeof(unsigned int));
   w.bytes = (size_t)(p - (char*)base);
   return w;
 }
@@ -90,15 +97,22 @@ __global__ void ba_count_kernel(const int32_t* __restrict__ obs_cam, const int32
 __global__ void __launch_bounds__(1024)
 ba_scan_kernel(int32_t* __restrict__ pt_start /* in: counts, out: exclusive scan [P+1] */, int P,
                int32_t* __restrict__ pt_cursor, const int32_t* __restrict__ cam_count,
-               int32_t* __restrict__ cam_start, int C) {
+               int32_t* __restrict__ cam_start, int C, const uint8_t* __restrict__ fixed,
+               int32_t* __restrict__ flist /* [0] = count, then the camera rows */) {
   __shared__ int wsum[32];
   __shared__ int base_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   if (tid == 0) {
     base_s = 0;
     int s = 0;
-    for (int c = 0; c < C; ++c) { cam_start[c] = s; s += cam_count[c]; }
+    int nf = 0;
+    for (int c = 0; c < C; ++c) {
+      cam_start[c] = s;
+      s += cam_count[c];
+      if (!fixed[c] && cam_count[c] > 0) flist[1 + nf++] = c;
+    }
     cam_start[C] = s;
+    flist[0] = nf;
   }
   __syncthreads();
   for (int b0 = 0; b0 <= P; b0 += 1024) {
@@ -201,12 +215,37 @@ __device__ __forceinline__ double block_sum_ordered(double v, double* red) {
   return s;
 }
 
+template <int N>
+__device__ __forceinline__ void block_sum_ordered_n(double (&acc)[N], double* red /* [8][N] smem */) {
+  // N sums at once: shuffle tree per warp, one barrier, then threads 0..N-1 add the warps in
+  // order; the totals come back in acc[] of thread k for value k (k < N)
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    double v = acc[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[(threadIdx.x >> 5) * N + k] = v;
+  }
+  __syncthreads();
+}
+
+template <int N2>
+__device__ __forceinline__ void load_rec(const double* __restrict__ src, double* dst) {
+  // 16-byte vector loads of one observation record (records are 16 B aligned)
+  const double2* s2 = reinterpret_cast<const double2*>(src);
+#pragma unroll
+  for (int k = 0; k < N2; ++k) { const double2 v = s2[k]; dst[2 * k] = v.x; dst[2 * k + 1] = v.y; }
+}
+
 __global__ void __launch_bounds__(BA_THREADS)
 ba_chi_kernel(const double* __restrict__ poses, const double* __restrict__ points,
               const int32_t* __restrict__ obs_cam, const int32_t* __restrict__ obs_pt,
               const double* __restrict__ obs_xy, int M, double f, double cx, double cy,
-              double delta, double* __restrict__ chi_part) {
+              double delta, double* chi_part, const double* scale_part, int nbp, double* stats,
+              unsigned int* ticket) {
+  // robust chi2 of a state; the LAST block to finish adds the block partials (and the partials of
+  // g2o's computeScale from ba_back_kernel) in a fixed order: stats[0] = chi2, stats[1] = scale
   __shared__ double red[BA_THREADS / 32];
+  __shared__ int last_s;
   const int i = blockIdx.x * BA_THREADS + threadIdx.x;
   double r0 = 0.0;
   if (i < M) {
@@ -216,15 +255,35 @@ ba_chi_kernel(const double* __restrict__ poses, const double* __restrict__ point
     ba_huber(p.ex * p.ex + p.ey * p.ey, delta, r0, w);
   }
   const double s = block_sum_ordered(r0, red);
-  if (threadIdx.x == 0) chi_part[blockIdx.x] = s;
+  if (threadIdx.x == 0) {
+    chi_part[blockIdx.x] = s;
+    __threadfence();
+    last_s = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last_s || threadIdx.x >= 32) return;
+  __threadfence();
+  const int lane = threadIdx.x;
+  double c = 0.0, sc = 0.0;
+  for (int b = lane; b < (int)gridDim.x; b += 32) c += __ldcg(chi_part + b);
+  for (int b = lane; b < nbp; b += 32) sc += __ldcg(scale_part + b);
+  for (int o = 16; o > 0; o >>= 1) {
+    c += __shfl_down_sync(0xffffffffu, c, o);
+    sc += __shfl_down_sync(0xffffffffu, sc, o);
+  }
+  if (lane == 0) { stats[0] = c; stats[1] = sc + stats[3]; *ticket = 0u; }
 }
 
+// per-observation records (gathered through the point / camera lists, so array-of-records):
+//   OA[i][10] = d e / d point (2x3), Huber weight, e_x, e_y, pad      (80 B)
+//   OB[i][12] = d e / d pose (2x6)                                    (96 B)
+//   OW[i][18] = w * B^T A (6x3), zero for a fixed camera              (144 B)
 __global__ void __launch_bounds__(BA_THREADS)
 ba_linearize_kernel(const double* __restrict__ poses, const uint8_t* __restrict__ fixed,
                     const double* __restrict__ points, const int32_t* __restrict__ obs_cam,
                     const int32_t* __restrict__ obs_pt, const double* __restrict__ obs_xy, int M,
-                    double f, double cx, double cy, double delta, double* __restrict__ JA,
-                    double* __restrict__ JB, double* __restrict__ we, double* __restrict__ W) {
+                    double f, double cx, double cy, double delta, double* __restrict__ OA,
+                    double* __restrict__ OB, double* __restrict__ OW) {
   const int i = blockIdx.x * BA_THREADS + threadIdx.x;
   if (i >= M) return;
   const int c = obs_cam[i];
@@ -245,81 +304,111 @@ ba_linearize_kernel(const double* __restrict__ poses, const uint8_t* __restrict_
   B[0][3] = -1.0 / z * f;          B[0][4] = 0.0;                     B[0][5] = x / z2 * f;
   B[1][0] = (1.0 + y * y / z2) * f; B[1][1] = -x * y / z2 * f;        B[1][2] = -x / z * f;
   B[1][3] = 0.0;                   B[1][4] = -1.0 / z * f;            B[1][5] = y / z2 * f;
+  double2* oa = reinterpret_cast<double2*>(OA + 10 * (size_t)i);
+  oa[0] = make_double2(A[0][0], A[0][1]); oa[1] = make_double2(A[0][2], A[1][0]);
+  oa[2] = make_double2(A[1][1], A[1][2]); oa[3] = make_double2(w, p.ex);
+  oa[4] = make_double2(p.ey, 0.0);
+  double2* ob = reinterpret_cast<double2*>(OB + 12 * (size_t)i);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) { JA[(size_t)k * M + i] = A[0][k]; JA[(size_t)(3 + k) * M + i] = A[1][k]; }
-#pragma unroll
-  for (int k = 0; k < 6; ++k) { JB[(size_t)k * M + i] = B[0][k]; JB[(size_t)(6 + k) * M + i] = B[1][k]; }
-  we[i] = w; we[(size_t)M + i] = p.ex; we[2 * (size_t)M + i] = p.ey;
+  for (int k = 0; k < 3; ++k) {
+    ob[k] = make_double2(B[0][2 * k], B[0][2 * k + 1]);
+    ob[3 + k] = make_double2(B[1][2 * k], B[1][2 * k + 1]);
+  }
   const bool free_cam = !fixed[c];
+  double wv[18];
 #pragma unroll
   for (int r = 0; r < 6; ++r)
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-      W[(size_t)(r * 3 + k) * M + i] = free_cam ? w * (B[0][r] * A[0][k] + B[1][r] * A[1][k]) : 0.0;
+      wv[r * 3 + k] = free_cam ? w * (B[0][r] * A[0][k] + B[1][r] * A[1][k]) : 0.0;
+  double2* ow = reinterpret_cast<double2*>(OW + 18 * (size_t)i);
+#pragma unroll
+  for (int k = 0; k < 9; ++k) ow[k] = make_double2(wv[2 * k], wv[2 * k + 1]);
+}
+
+// points are handled by groups of 4 lanes: the lanes stride over the point's observation list,
+// partial sums are combined by two xor-shuffles ((l0+l1)+(l2+l3)): a fixed order
+__device__ __forceinline__ double group4_sum(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
 }
 
 __global__ void __launch_bounds__(BA_THREADS)
 ba_point_blocks_kernel(const int32_t* __restrict__ pt_start, const int32_t* __restrict__ pt_obs, int P,
-                       int M, const double* __restrict__ JA, const double* __restrict__ we,
-                       double* __restrict__ Hll, double* __restrict__ bl) {
-  const int p = blockIdx.x * BA_THREADS + threadIdx.x;
-  if (p >= P) return;
+                       const double* __restrict__ OA, double* __restrict__ Hll,
+                       double* __restrict__ bl) {
+  const int t = blockIdx.x * BA_THREADS + threadIdx.x, p = t / BA_PT_LANES, sub = t % BA_PT_LANES;
   double h[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-  for (int a = pt_start[p]; a < pt_start[p + 1]; ++a) {
-    const int i = pt_obs[a];
-    double A0[3], A1[3];
+  if (p < P) {
+    for (int a = pt_start[p] + sub; a < pt_start[p + 1]; a += BA_PT_LANES) {
+      double r[10];
+      load_rec<5>(OA + 10 * (size_t)pt_obs[a], r);
+      const double w = r[6], ex = r[7], ey = r[8];
+      h[0] += w * (r[0] * r[0] + r[3] * r[3]);
+      h[1] += w * (r[0] * r[1] + r[3] * r[4]);
+      h[2] += w * (r[0] * r[2] + r[3] * r[5]);
+      h[3] += w * (r[1] * r[1] + r[4] * r[4]);
+      h[4] += w * (r[1] * r[2] + r[4] * r[5]);
+      h[5] += w * (r[2] * r[2] + r[5] * r[5]);
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { A0[k] = JA[(size_t)k * M + i]; A1[k] = JA[(size_t)(3 + k) * M + i]; }
-    const double w = we[i], ex = we[(size_t)M + i], ey = we[2 * (size_t)M + i];
-    h[0] += w * (A0[0] * A0[0] + A1[0] * A1[0]);
-    h[1] += w * (A0[0] * A0[1] + A1[0] * A1[1]);
-    h[2] += w * (A0[0] * A0[2] + A1[0] * A1[2]);
-    h[3] += w * (A0[1] * A0[1] + A1[1] * A1[1]);
-    h[4] += w * (A0[1] * A0[2] + A1[1] * A1[2]);
-    h[5] += w * (A0[2] * A0[2] + A1[2] * A1[2]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k) b[k] -= w * (A0[k] * ex + A1[k] * ey);
+      for (int k = 0; k < 3; ++k) b[k] -= w * (r[k] * ex + r[3 + k] * ey);
+    }
   }
 #pragma unroll
-  for (int k = 0; k < 6; ++k) Hll[6 * (size_t)p + k] = h[k];
+  for (int k = 0; k < 6; ++k) h[k] = group4_sum(h[k]);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) bl[3 * (size_t)p + k] = b[k];
+  for (int k = 0; k < 3; ++k) b[k] = group4_sum(b[k]);
+  if (p < P && sub == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Hll[6 * (size_t)p + k] = h[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) bl[3 * (size_t)p + k] = b[k];
+  }
 }
 
 __global__ void __launch_bounds__(BA_THREADS)
 ba_camera_blocks_kernel(const int32_t* __restrict__ cam_start, const int32_t* __restrict__ cam_obs,
-                        const uint8_t* __restrict__ fixed, int M, const double* __restrict__ JB,
-                        const double* __restrict__ we, double* __restrict__ Hpp,
-                        double* __restrict__ bp) {
-  // block = camera; 21 + 6 sums, each thread strides over the camera's list, ordered block sums
-  __shared__ double red[BA_THREADS / 32];
-  const int c = blockIdx.x;
+                        const int32_t* __restrict__ flist, int NS, const double* __restrict__ OA,
+                        const double* __restrict__ OB, double* __restrict__ Cpart) {
+  // block (f, s): chunk s of the observation list of the f-th free camera; 21 + 6 ordered sums
+  __shared__ double red[(BA_THREADS / 32) * 27];
+  const int c = flist[1 + blockIdx.x], sp = blockIdx.y;
+  const int beg = cam_start[c], end = cam_start[c + 1], chunk = (end - beg + NS - 1) / NS;
+  const int lo = beg + sp * chunk, hi = min(lo + chunk, end);
   double acc[27];
 #pragma unroll
   for (int k = 0; k < 27; ++k) acc[k] = 0.0;
-  if (!fixed[c]) {
-    for (int a = cam_start[c] + threadIdx.x; a < cam_start[c + 1]; a += BA_THREADS) {
-      const int i = cam_obs[a];
-      double B0[6], B1[6];
+  for (int a = lo + threadIdx.x; a < hi; a += BA_THREADS) {
+    const int i = cam_obs[a];
+    double B[12], r[4];
+    load_rec<6>(OB + 12 * (size_t)i, B);
+    load_rec<2>(OA + 10 * (size_t)i + 6, r);
+    const double w = r[0], ex = r[1], ey = r[2];
+    int q = 0;
 #pragma unroll
-      for (int k = 0; k < 6; ++k) { B0[k] = JB[(size_t)k * M + i]; B1[k] = JB[(size_t)(6 + k) * M + i]; }
-      const double w = we[i], ex = we[(size_t)M + i], ey = we[2 * (size_t)M + i];
-      int q = 0;
+    for (int rr = 0; rr < 6; ++rr)
 #pragma unroll
-      for (int r = 0; r < 6; ++r)
+      for (int s = rr; s < 6; ++s) acc[q++] += w * (B[rr] * B[s] + B[6 + rr] * B[6 + s]);
 #pragma unroll
-        for (int s = r; s < 6; ++s) acc[q++] += w * (B0[r] * B0[s] + B1[r] * B1[s]);
-#pragma unroll
-      for (int r = 0; r < 6; ++r) acc[21 + r] -= w * (B0[r] * ex + B1[r] * ey);
-    }
+    for (int rr = 0; rr < 6; ++rr) acc[21 + rr] -= w * (B[rr] * ex + B[6 + rr] * ey);
   }
-#pragma unroll
-  for (int k = 0; k < 27; ++k) {
-    const double s = block_sum_ordered(acc[k], red);
-    if (threadIdx.x == 0) {
-      if (k < 21) Hpp[21 * c + k] = s; else bp[6 * c + (k - 21)] = s;
-    }
+  block_sum_ordered_n<27>(acc, red);
+  if (threadIdx.x < 27) {
+    double s = 0.0;
+    for (int w = 0; w < BA_THREADS / 32; ++w) s += red[w * 27 + threadIdx.x];
+    Cpart[((size_t)blockIdx.x * NS + sp) * 27 + threadIdx.x] = s;
   }
+}
+
+__global__ void ba_camera_fold_kernel(const int32_t* __restrict__ flist, int NS,
+                                      const double* __restrict__ Cpart, double* __restrict__ Hpp,
+                                      double* __restrict__ bp) {
+  const int c = flist[1 + blockIdx.x], k = threadIdx.x;
+  if (k >= 27) return;
+  double s = 0.0;
+  for (int sp = 0; sp < NS; ++sp) s += Cpart[((size_t)blockIdx.x * NS + sp) * 27 + k];
+  if (k < 21) Hpp[21 * c + k] = s; else bp[6 * c + (k - 21)] = s;
 }
 
 __global__ void ba_maxdiag_kernel(const double* __restrict__ Hll, const int32_t* __restrict__ pt_start,
@@ -355,77 +444,59 @@ __device__ __forceinline__ void sym3_inverse(const double* h, double lam, double
 }
 
 __global__ void __launch_bounds__(BA_THREADS)
-ba_y_kernel(const int32_t* __restrict__ obs_pt, int M, const double* __restrict__ Hll, double lam,
-            const double* __restrict__ W, double* __restrict__ Y) {
-  const int i = blockIdx.x * BA_THREADS + threadIdx.x;
-  if (i >= M) return;
-  double v[6];
-  sym3_inverse(Hll + 6 * (size_t)obs_pt[i], lam, v);
-#pragma unroll
-  for (int r = 0; r < 6; ++r) {
-    const double w0 = W[(size_t)(r * 3) * M + i], w1 = W[(size_t)(r * 3 + 1) * M + i],
-                 w2 = W[(size_t)(r * 3 + 2) * M + i];
-    Y[(size_t)(r * 3) * M + i] = w0 * v[0] + w1 * v[1] + w2 * v[2];
-    Y[(size_t)(r * 3 + 1) * M + i] = w0 * v[1] + w1 * v[3] + w2 * v[4];
-    Y[(size_t)(r * 3 + 2) * M + i] = w0 * v[2] + w1 * v[4] + w2 * v[5];
-  }
-}
-
-__global__ void __launch_bounds__(BA_THREADS)
 ba_schur_kernel(const int32_t* __restrict__ cam_start, const int32_t* __restrict__ cam_obs,
                 const int32_t* __restrict__ pt_start, const int32_t* __restrict__ pt_obs,
                 const int32_t* __restrict__ obs_cam, const int32_t* __restrict__ obs_pt,
-                const uint8_t* __restrict__ fixed, int C, int M, const double* __restrict__ W,
-                const double* __restrict__ Y, const double* __restrict__ bl,
-                const double* __restrict__ Hpp, const double* __restrict__ bp, double lam,
-                double* __restrict__ S, double* __restrict__ bs) {
-  // block (a, b), a <= b: S_ab = [a==b](Hpp_a + lam I) - sum_{i in obs(a)} Y_i * sum_{j in
-  // obs(point_i), cam_j == b} W_j^T;  bs_a = bp_a - sum_i Y_i bl[point_i]
-  __shared__ double red[BA_THREADS / 32];
-  const int a = blockIdx.x, b = blockIdx.y;
-  if (a > b || fixed[a] || fixed[b]) return;
-  if (cam_start[a + 1] == cam_start[a] || cam_start[b + 1] == cam_start[b]) return;
+                const int32_t* __restrict__ flist, int NS, const double* __restrict__ OW,
+                const double* __restrict__ Hll, const double* __restrict__ bl, double lam,
+                double* __restrict__ Spart) {
+  // block (fa, fb, s), fa <= fb over the FREE cameras: chunk s of camera a's observation list.
+  //   partial of  sum_{i in obs(a)} Y_i * sum_{j in obs(point_i), cam_j == b} W_j^T   (36 values)
+  //   and, on the diagonal, of  sum_i Y_i bl[point_i]  (6 values),  Y_i = W_i (Hll + lam I)^-1
+  __shared__ double red[(BA_THREADS / 32) * 42];
+  const int fa = blockIdx.x, fb = blockIdx.y, sp = blockIdx.z, nf = gridDim.x;
+  if (fa > fb) return;
+  const int a = flist[1 + fa], b = flist[1 + fb];
+  const int beg = cam_start[a], end = cam_start[a + 1], chunk = (end - beg + NS - 1) / NS;
+  const int lo = beg + sp * chunk, hi = min(lo + chunk, end);
   double acc[42];
 #pragma unroll
   for (int k = 0; k < 42; ++k) acc[k] = 0.0;
-  for (int idx = cam_start[a] + threadIdx.x; idx < cam_start[a + 1]; idx += BA_THREADS) {
+  for (int idx = lo + threadIdx.x; idx < hi; idx += BA_THREADS) {
     const int i = cam_obs[idx], p = obs_pt[i];
-    double y[18];
+    double v[6], wi[18], y[18];
+    sym3_inverse(Hll + 6 * (size_t)p, lam, v);
+    load_rec<9>(OW + 18 * (size_t)i, wi);
 #pragma unroll
-    for (int k = 0; k < 18; ++k) y[k] = Y[(size_t)k * M + i];
-    for (int l = pt_start[p]; l < pt_start[p + 1]; ++l) {
-      const int j = pt_obs[l];
-      if (obs_cam[j] != b) continue;
-#pragma unroll
-      for (int s = 0; s < 6; ++s) {
-        const double w0 = W[(size_t)(s * 3) * M + j], w1 = W[(size_t)(s * 3 + 1) * M + j],
-                     w2 = W[(size_t)(s * 3 + 2) * M + j];
-#pragma unroll
-        for (int r = 0; r < 6; ++r) acc[r * 6 + s] += y[r * 3] * w0 + y[r * 3 + 1] * w1 + y[r * 3 + 2] * w2;
-      }
+    for (int r = 0; r < 6; ++r) {
+      const double w0 = wi[r * 3], w1 = wi[r * 3 + 1], w2 = wi[r * 3 + 2];
+      y[r * 3] = w0 * v[0] + w1 * v[1] + w2 * v[2];
+      y[r * 3 + 1] = w0 * v[1] + w1 * v[3] + w2 * v[4];
+      y[r * 3 + 2] = w0 * v[2] + w1 * v[4] + w2 * v[5];
     }
     if (a == b) {
       const double b0 = bl[3 * (size_t)p], b1 = bl[3 * (size_t)p + 1], b2 = bl[3 * (size_t)p + 2];
 #pragma unroll
       for (int r = 0; r < 6; ++r) acc[36 + r] += y[r * 3] * b0 + y[r * 3 + 1] * b1 + y[r * 3 + 2] * b2;
     }
-  }
+    for (int l = pt_start[p]; l < pt_start[p + 1]; ++l) {
+      const int j = pt_obs[l];
+      if (obs_cam[j] != b) continue;
+      double wj[18];
+      load_rec<9>(OW + 18 * (size_t)j, wj);
 #pragma unroll
-  for (int k = 0; k < 42; ++k) {
-    if (k >= 36 && a != b) break;
-    const double s = block_sum_ordered(acc[k], red);
-    if (threadIdx.x == 0) {
-      if (k < 36) {
-        double h = 0.0;
-        if (a == b) {
-          const int r = k / 6, c = k % 6, lo = r < c ? r : c, hi = r < c ? c : r;
-          h = Hpp[21 * a + (lo * 6 - lo * (lo - 1) / 2 + (hi - lo))] + (r == c ? lam : 0.0);
-        }
-        S[((size_t)a * C + b) * 36 + k] = h - s;
-      } else {
-        bs[6 * a + (k - 36)] = bp[6 * a + (k - 36)] - s;
-      }
+      for (int s = 0; s < 6; ++s)
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+          acc[r * 6 + s] += y[r * 3] * wj[s * 3] + y[r * 3 + 1] * wj[s * 3 + 1] + y[r * 3 + 2] * wj[s * 3 + 2];
     }
+  }
+  const size_t pair = (size_t)fa * nf - (size_t)fa * (fa - 1) / 2 + (fb - fa);
+  block_sum_ordered_n<42>(acc, red);
+  if (threadIdx.x < (a == b ? 42 : 36)) {
+    double s = 0.0;
+    for (int w = 0; w < BA_THREADS / 32; ++w) s += red[w * 42 + threadIdx.x];
+    Spart[(pair * NS + sp) * 42 + threadIdx.x] = s;
   }
 }
 
@@ -462,64 +533,66 @@ __device__ void ba_se3_exp_apply(const double* dx, const double* T, double* out)
 }
 
 __global__ void __launch_bounds__(BA_THREADS)
-ba_solve_kernel(const double* __restrict__ S, const double* __restrict__ bs,
-                const int32_t* __restrict__ cam_start, const uint8_t* __restrict__ fixed, int C,
-                const double* __restrict__ bp, double lam, const double* __restrict__ poses,
-                double* __restrict__ trial_poses, double* __restrict__ xp,
-                double* __restrict__ stats) {
-  // dense Cholesky of the reduced camera system in shared memory (n = 6C <= 144), triangular
-  // solves by warp 0, pose update exp(dx) * T, camera part of g2o's computeScale()
+ba_solve_kernel(const double* __restrict__ Spart, int NS, const int32_t* __restrict__ flist, int C,
+                const double* __restrict__ Hpp, const double* __restrict__ bp, double lam,
+                const double* __restrict__ poses, double* __restrict__ trial_poses,
+                double* __restrict__ xp, double* __restrict__ stats) {
+  // reduced camera system over the nf free cameras (n = 6 nf <= 144) in shared memory:
+  // S = Hpp + lam I - sum of the Schur partials (folded in split order), dense Cholesky (two
+  // barriers per column), triangular solves by warp 0, pose update exp(dx) * T, camera part of
+  // g2o's computeScale()
   extern __shared__ double sm[];
-  const int n = 6 * C, ld = n + 1;
-  double* A = sm;               // [n][ld]
-  double* x = sm + (size_t)n * ld;   // [n]
-  __shared__ int ok_s;
+  const int nf = flist[0], n = 6 * nf, ld = n + 1;
+  double* A = sm;                        // [n][ld]
+  double* x = sm + (size_t)n * ld;       // [n]
+  double* diag = x + n;                  // [n]
   const int tid = threadIdx.x;
-  if (tid == 0) ok_s = 1;
   for (int e = tid; e < n * n; e += BA_THREADS) {
-    const int r = e / n, c = e % n, a = r / 6, b = c / 6;
-    const bool act_a = !fixed[a] && cam_start[a + 1] > cam_start[a];
-    const bool act_b = !fixed[b] && cam_start[b + 1] > cam_start[b];
-    double v;
-    if (!act_a || !act_b) v = (r == c) ? 1.0 : 0.0;
-    else if (a <= b) v = S[((size_t)a * C + b) * 36 + (r % 6) * 6 + (c % 6)];
-    else v = S[((size_t)b * C + a) * 36 + (c % 6) * 6 + (r % 6)];
-    A[r * ld + c] = v;
+    const int r = e / n, c = e % n;
+    int fa = r / 6, fb = c / 6, rr = r % 6, cc = c % 6;
+    if (fa > fb) { int t = fa; fa = fb; fb = t; t = rr; rr = cc; cc = t; }
+    const size_t pair = (size_t)fa * nf - (size_t)fa * (fa - 1) / 2 + (fb - fa);
+    double sub = 0.0;
+    for (int sp = 0; sp < NS; ++sp) sub += Spart[(pair * NS + sp) * 42 + rr * 6 + cc];
+    double h = 0.0;
+    if (fa == fb) {
+      const int lo = rr < cc ? rr : cc, hi = rr < cc ? cc : rr;
+      h = Hpp[21 * flist[1 + fa] + (lo * 6 - lo * (lo - 1) / 2 + (hi - lo))] + (rr == cc ? lam : 0.0);
+    }
+    A[r * ld + c] = h - sub;
   }
   for (int r = tid; r < n; r += BA_THREADS) {
-    const int a = r / 6;
-    x[r] = (!fixed[a] && cam_start[a + 1] > cam_start[a]) ? bs[r] : 0.0;
+    const int fa = r / 6;
+    const size_t pair = (size_t)fa * nf - (size_t)fa * (fa - 1) / 2;
+    double sub = 0.0;
+    for (int sp = 0; sp < NS; ++sp) sub += Spart[(pair * NS + sp) * 42 + 36 + r % 6];
+    x[r] = bp[6 * flist[1 + fa] + r % 6] - sub;
   }
   __syncthreads();
   const int tx = tid & 15, ty = tid >> 4;
+  int ok = 1;
   for (int k = 0; k < n; ++k) {
-    if (tid == 0) {
-      const double d = A[k * ld + k];
-      if (!(d > 0.0)) ok_s = 0;
-      A[k * ld + k] = sqrt(d);
-    }
-    __syncthreads();
-    if (!ok_s) break;
-    const double dk = A[k * ld + k];
-    __syncthreads();
-    for (int i = k + 1 + tid; i < n; i += BA_THREADS) A[i * ld + k] /= dk;
+    const double d = A[k * ld + k];          // final since the barrier that ended step k-1
+    if (!(d > 0.0)) { ok = 0; break; }       // same value in every thread
+    const double sd = sqrt(d);
+    if (tid == 0) diag[k] = sd;
+    for (int i = k + 1 + tid; i < n; i += BA_THREADS) A[i * ld + k] /= sd;
     __syncthreads();
     for (int i = k + 1 + ty; i < n; i += 16)
       for (int j = k + 1 + tx; j <= i; j += 16) A[i * ld + j] -= A[i * ld + k] * A[j * ld + k];
     __syncthreads();
   }
-  const int ok = ok_s;
   if (tid < 32) {
     if (ok) {
       for (int k = 0; k < n; ++k) {           // L y = b
-        if (tid == 0) x[k] /= A[k * ld + k];
+        if (tid == 0) x[k] /= diag[k];
         __syncwarp();
         const double yk = x[k];
         for (int i = k + 1 + tid; i < n; i += 32) x[i] -= A[i * ld + k] * yk;
         __syncwarp();
       }
       for (int k = n - 1; k >= 0; --k) {      // L^T x = y
-        if (tid == 0) x[k] /= A[k * ld + k];
+        if (tid == 0) x[k] /= diag[k];
         __syncwarp();
         const double xk = x[k];
         for (int i = tid; i < k; i += 32) x[i] -= A[k * ld + i] * xk;
@@ -530,22 +603,19 @@ ba_solve_kernel(const double* __restrict__ S, const double* __restrict__ bs,
     }
   }
   __syncthreads();
-  for (int r = tid; r < n; r += BA_THREADS) xp[r] = x[r];
-  if (tid < C) {
-    const int c = tid;
-    const bool act = !fixed[c] && cam_start[c + 1] > cam_start[c];
-    if (act && ok) {
-      ba_se3_exp_apply(x + 6 * c, poses + 16 * c, trial_poses + 16 * c);
-    } else {
-      for (int k = 0; k < 16; ++k) trial_poses[16 * c + k] = poses[16 * c + k];
-    }
+  for (int r = tid; r < 6 * C; r += BA_THREADS) xp[r] = 0.0;
+  for (int r = tid; r < 16 * C; r += BA_THREADS) trial_poses[r] = poses[r];
+  __syncthreads();
+  for (int r = tid; r < n; r += BA_THREADS) xp[6 * flist[1 + r / 6] + r % 6] = x[r];
+  if (tid < nf && ok) {
+    const int c = flist[1 + tid];
+    ba_se3_exp_apply(x + 6 * tid, poses + 16 * c, trial_poses + 16 * c);
   }
   if (tid == 0) {
     double sc = 0.0;
-    for (int c = 0; c < C; ++c) {
-      if (fixed[c] || cam_start[c + 1] == cam_start[c]) continue;
-      for (int r = 0; r < 6; ++r) sc += x[6 * c + r] * (lam * x[6 * c + r] + bp[6 * c + r]);
-    }
+    for (int f = 0; f < nf; ++f)
+      for (int r = 0; r < 6; ++r)
+        sc += x[6 * f + r] * (lam * x[6 * f + r] + bp[6 * flist[1 + f] + r]);
     stats[3] = sc;
     stats[2] = (double)ok;
   }
@@ -553,29 +623,42 @@ ba_solve_kernel(const double* __restrict__ S, const double* __restrict__ bs,
 
 __global__ void __launch_bounds__(BA_THREADS)
 ba_back_kernel(const int32_t* __restrict__ pt_start, const int32_t* __restrict__ pt_obs,
-               const int32_t* __restrict__ obs_cam, int P, int M, const double* __restrict__ W,
-               const double* __restrict__ Hll, const double* __restrict__ bl, double lam,
-               const double* __restrict__ xp, const double* __restrict__ points,
-               double* __restrict__ trial_points, double* __restrict__ scale_part) {
+               const int32_t* __restrict__ obs_cam, const uint8_t* __restrict__ fixed, int P,
+               const double* __restrict__ OW, const double* __restrict__ Hll,
+               const double* __restrict__ bl, double lam, const double* __restrict__ xp,
+               const double* __restrict__ points, double* __restrict__ trial_points,
+               double* __restrict__ scale_part) {
+  // 4 lanes per point: dx_l = (Hll + lam I)^-1 (bl - sum_j W_j^T dx_cam(j)); X <- X + dx_l;
+  // point part of g2o's computeScale()
   __shared__ double red[BA_THREADS / 32];
-  const int p = blockIdx.x * BA_THREADS + threadIdx.x;
-  double sc = 0.0;
+  const int t = blockIdx.x * BA_THREADS + threadIdx.x, p = t / BA_PT_LANES, sub = t % BA_PT_LANES;
+  double cp[3] = {0.0, 0.0, 0.0};
+  bool active = false;
   if (p < P) {
-    double X[3] = {points[3 * (size_t)p], points[3 * (size_t)p + 1], points[3 * (size_t)p + 2]};
-    if (pt_start[p + 1] > pt_start[p]) {
-      double cp[3] = {bl[3 * (size_t)p], bl[3 * (size_t)p + 1], bl[3 * (size_t)p + 2]};
-      const double b0 = cp[0], b1 = cp[1], b2 = cp[2];
-      for (int l = pt_start[p]; l < pt_start[p + 1]; ++l) {
-        const int j = pt_obs[l];
-        const double* d = xp + 6 * obs_cam[j];
+    active = pt_start[p + 1] > pt_start[p];
+    for (int l = pt_start[p] + sub; l < pt_start[p + 1]; l += BA_PT_LANES) {
+      const int j = pt_obs[l], c = obs_cam[j];
+      if (fixed[c]) continue;              // W_j = 0 and dx = 0 there
+      double wj[18];
+      load_rec<9>(OW + 18 * (size_t)j, wj);
+      const double* d = xp + 6 * c;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-          const double dr = d[r];
-          cp[0] -= W[(size_t)(r * 3) * M + j] * dr;
-          cp[1] -= W[(size_t)(r * 3 + 1) * M + j] * dr;
-          cp[2] -= W[(size_t)(r * 3 + 2) * M + j] * dr;
-        }
+      for (int r = 0; r < 6; ++r) {
+        const double dr = d[r];
+        cp[0] -= wj[r * 3] * dr;
+        cp[1] -= wj[r * 3 + 1] * dr;
+        cp[2] -= wj[r * 3 + 2] * dr;
       }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) cp[k] = group4_sum(cp[k]);
+  double sc = 0.0;
+  if (p < P && sub == 0) {
+    double X[3] = {points[3 * (size_t)p], points[3 * (size_t)p + 1], points[3 * (size_t)p + 2]};
+    if (active) {
+      const double b0 = bl[3 * (size_t)p], b1 = bl[3 * (size_t)p + 1], b2 = bl[3 * (size_t)p + 2];
+      cp[0] += b0; cp[1] += b1; cp[2] += b2;
       double v[6];
       sym3_inverse(Hll + 6 * (size_t)p, lam, v);
       const double d0 = v[0] * cp[0] + v[1] * cp[1] + v[2] * cp[2];
@@ -590,21 +673,6 @@ ba_back_kernel(const int32_t* __restrict__ pt_start, const int32_t* __restrict__
   }
   const double s = block_sum_ordered(sc, red);
   if (threadIdx.x == 0) scale_part[blockIdx.x] = s;
-}
-
-__global__ void ba_final_kernel(const double* __restrict__ chi_part, int nbo,
-                                const double* __restrict__ scale_part, int nbp,
-                                double* __restrict__ stats) {
-  // one warp: strided partial sums in fixed order, shuffle tree
-  const int lane = threadIdx.x;
-  double c = 0.0, s = 0.0;
-  for (int b = lane; b < nbo; b += 32) c += chi_part[b];
-  for (int b = lane; b < nbp; b += 32) s += scale_part[b];
-  for (int o = 16; o > 0; o >>= 1) {
-    c += __shfl_down_sync(0xffffffffu, c, o);
-    s += __shfl_down_sync(0xffffffffu, s, o);
-  }
-  if (lane == 0) { stats[0] = c; stats[1] = s + stats[3]; }
 }
 
 }  // namespace vo
@@ -638,11 +706,11 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
   char* base = (char*)(((uintptr_t)ws + 255) / 256 * 256);
   BAWs w = ba_carve(base, C, P, M);
   const int nbo = (M + BA_THREADS - 1) / BA_THREADS, nbp = (P + BA_THREADS - 1) / BA_THREADS;
-  const size_t solve_smem = sizeof(double) * ((size_t)6 * C * (6 * C + 1) + 6 * C);
+  const int nbp4 = (int)(((size_t)P * BA_PT_LANES + BA_THREADS - 1) / BA_THREADS);
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(ba_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)(sizeof(double) * ((size_t)6 * BA_MAX_CAMS * (6 * BA_MAX_CAMS + 1) + 6 * BA_MAX_CAMS)));
+                         (int)(sizeof(double) * ((size_t)6 * BA_MAX_CAMS * (6 * BA_MAX_CAMS + 1) + 12 * BA_MAX_CAMS)));
     attr_done = true;
   }
 
@@ -652,12 +720,27 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
   cudaMemsetAsync(w.bad, 0, sizeof(int32_t), st);
   cudaMemsetAsync(w.maxdiag, 0, sizeof(unsigned long long), st);
   cudaMemsetAsync(w.stats, 0, sizeof(double) * 8, st);
+  cudaMemsetAsync(w.ticket, 0, sizeof(unsigned int), st);
   ba_count_kernel<<<nbo, BA_THREADS, 0, st>>>(obs_cam, obs_pt, M, C, P, w.pt_start, w.cam_count, w.bad);
-  int32_t h_bad = 0;
+  int32_t h_bad = 0, h_count[BA_MAX_CAMS];
+  uint8_t h_fixed[BA_MAX_CAMS];
   cudaMemcpyAsync(&h_bad, w.bad, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  cudaMemcpyAsync(h_count, w.cam_count, sizeof(int32_t) * C, cudaMemcpyDeviceToHost, st);
+  cudaMemcpyAsync(h_fixed, fixed, C, cudaMemcpyDeviceToHost, st);
   if (cudaStreamSynchronize(st) != cudaSuccess) return check_launch("vo_bundle_adjust(count)");
   VO_REQUIRE(!h_bad, VO_ERR_INVALID_ARG, "vo_bundle_adjust: observation index out of range");
-  ba_scan_kernel<<<1, 1024, 0, st>>>(w.pt_start, P, w.pt_cursor, w.cam_count, w.cam_start, C);
+  // free, observed cameras: the unknowns of the reduced system; how far their lists are split
+  int nf = 0;
+  for (int c = 0; c < C; ++c) nf += (!h_fixed[c] && h_count[c] > 0);
+  const int npairs = nf * (nf + 1) / 2;
+  auto split_for = [](int units) {
+    int ns = units > 0 ? (BA_TARGET_BLOCKS + units - 1) / units : 1;
+    return ns < 1 ? 1 : (ns > BA_MAX_SPLIT ? BA_MAX_SPLIT : ns);
+  };
+  const int NS = split_for(npairs), NSc = split_for(nf);
+  const size_t solve_smem = sizeof(double) * ((size_t)6 * nf * (6 * nf + 1) + 12 * nf + 2);
+  ba_scan_kernel<<<1, 1024, 0, st>>>(w.pt_start, P, w.pt_cursor, w.cam_count, w.cam_start, C, fixed,
+                                     w.flist);
   ba_fill_pts_kernel<<<nbo, BA_THREADS, 0, st>>>(obs_pt, M, w.pt_cursor, w.pt_obs);
   ba_sort_pts_kernel<<<nbp, BA_THREADS, 0, st>>>(w.pt_start, P, w.pt_obs);
   ba_fill_cams_kernel<<<C, 1024, 0, st>>>(obs_cam, M, w.cam_start, w.cam_obs);
@@ -665,12 +748,12 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
   double* cur_pts = points;  double* tri_pts = w.trial_points;
   double* cur_pos = poses;   double* tri_pos = w.trial_poses;
   double h_stats[4];
-  auto chi_of = [&](const double* ps, const double* pt) {
+  auto chi_of = [&](const double* ps, const double* pt, int n_scale_parts) {
     ba_chi_kernel<<<nbo, BA_THREADS, 0, st>>>(ps, pt, obs_cam, obs_pt, obs_xy, M, focal, cx, cy,
-                                              huber_delta, w.chi_part);
+                                              huber_delta, w.chi_part, w.scale_part, n_scale_parts,
+                                              w.stats, w.ticket);
   };
-  chi_of(cur_pos, cur_pts);
-  ba_final_kernel<<<1, 32, 0, st>>>(w.chi_part, nbo, w.scale_part, 0, w.stats);
+  chi_of(cur_pos, cur_pts, 0);
   cudaMemcpyAsync(h_stats, w.stats, sizeof(double) * 4, cudaMemcpyDeviceToHost, st);
   if (cudaStreamSynchronize(st) != cudaSuccess) return check_launch("vo_bundle_adjust(setup)");
   double current = h_stats[0];
@@ -680,10 +763,13 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
   int it = 0;
   for (; it < iterations; ++it) {
     ba_linearize_kernel<<<nbo, BA_THREADS, 0, st>>>(cur_pos, fixed, cur_pts, obs_cam, obs_pt, obs_xy,
-                                                    M, focal, cx, cy, huber_delta, w.JA, w.JB, w.we, w.W);
-    ba_point_blocks_kernel<<<nbp, BA_THREADS, 0, st>>>(w.pt_start, w.pt_obs, P, M, w.JA, w.we, w.Hll, w.bl);
-    ba_camera_blocks_kernel<<<C, BA_THREADS, 0, st>>>(w.cam_start, w.cam_obs, fixed, M, w.JB, w.we,
-                                                      w.Hpp, w.bp);
+                                                    M, focal, cx, cy, huber_delta, w.OA, w.OB, w.OW);
+    ba_point_blocks_kernel<<<nbp4, BA_THREADS, 0, st>>>(w.pt_start, w.pt_obs, P, w.OA, w.Hll, w.bl);
+    if (nf > 0) {
+      ba_camera_blocks_kernel<<<dim3(nf, NSc), BA_THREADS, 0, st>>>(w.cam_start, w.cam_obs, w.flist, NSc,
+                                                                    w.OA, w.OB, w.Cpart);
+      ba_camera_fold_kernel<<<nf, 32, 0, st>>>(w.flist, NSc, w.Cpart, w.Hpp, w.bp);
+    }
     if (it == 0) {
       ba_maxdiag_kernel<<<(P + C + 255) / 256, 256, 0, st>>>(w.Hll, w.pt_start, P, w.Hpp, w.cam_start,
                                                             fixed, C, w.maxdiag);
@@ -698,16 +784,15 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
     double rho = 0.0;
     int qmax = 0;
     do {
-      ba_y_kernel<<<nbo, BA_THREADS, 0, st>>>(obs_pt, M, w.Hll, lambda, w.W, w.Y);
-      ba_schur_kernel<<<dim3(C, C), BA_THREADS, 0, st>>>(w.cam_start, w.cam_obs, w.pt_start, w.pt_obs,
-                                                        obs_cam, obs_pt, fixed, C, M, w.W, w.Y, w.bl,
-                                                        w.Hpp, w.bp, lambda, w.S, w.bs);
-      ba_solve_kernel<<<1, BA_THREADS, solve_smem, st>>>(w.S, w.bs, w.cam_start, fixed, C, w.bp, lambda,
+      if (nf > 0)
+        ba_schur_kernel<<<dim3(nf, nf, NS), BA_THREADS, 0, st>>>(
+            w.cam_start, w.cam_obs, w.pt_start, w.pt_obs, obs_cam, obs_pt, w.flist, NS, w.OW, w.Hll,
+            w.bl, lambda, w.Spart);
+      ba_solve_kernel<<<1, BA_THREADS, solve_smem, st>>>(w.Spart, NS, w.flist, C, w.Hpp, w.bp, lambda,
                                                         cur_pos, tri_pos, w.xp, w.stats);
-      ba_back_kernel<<<nbp, BA_THREADS, 0, st>>>(w.pt_start, w.pt_obs, obs_cam, P, M, w.W, w.Hll, w.bl,
-                                                lambda, w.xp, cur_pts, tri_pts, w.scale_part);
-      chi_of(tri_pos, tri_pts);
-      ba_final_kernel<<<1, 32, 0, st>>>(w.chi_part, nbo, w.scale_part, nbp, w.stats);
+      ba_back_kernel<<<nbp4, BA_THREADS, 0, st>>>(w.pt_start, w.pt_obs, obs_cam, fixed, P, w.OW, w.Hll,
+                                                 w.bl, lambda, w.xp, cur_pts, tri_pts, w.scale_part);
+      chi_of(tri_pos, tri_pts, nbp4);
       cudaMemcpyAsync(h_stats, w.stats, sizeof(double) * 4, cudaMemcpyDeviceToHost, st);
       if (cudaStreamSynchronize(st) != cudaSuccess) return check_launch("vo_bundle_adjust(trial)");
       const bool ok = h_stats[2] != 0.0;
