@@ -6,7 +6,8 @@ Exports the same names.  Differences, all outside the hot path:
     no-ops when OpenCV was built without a GUI, everything else forwards to the real cv2;
   * GUI / BA / plotting dependencies that are not installed (OpenGL, g2o, pygame viewer,
     matplotlib, plotly, codetiming) are replaced by inert stand-ins — graphics are unavailable on
-    this box and bundle adjustment (g2o) is out of scope.
+    this box; bundle adjustment runs through `map_ops.patch_map(Map)` -> vo_bundle_adjust instead of
+    g2o (which is not installable here).
 """
 import collections
 import glob
