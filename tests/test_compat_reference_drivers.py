@@ -59,3 +59,17 @@ def test_reference_entry_points_import(compat_path):
     from image_pair import ImagePair
     legacy = ImagePair("ORB")                                # the shape main_triangulate.py needs
     assert hasattr(legacy, "standard_pipeline") and hasattr(legacy, "set_images")
+
+
+def test_install_can_patch_the_reference_map(compat_path):
+    """compat.install(patch_map=True): the reference's own Map class gets the GPU optimize_map and
+    reprojection methods (binding only: no GPU call here)."""
+    from visual_odometry_b200 import compat, ba, map_ops
+    sys.modules.pop("map", None)
+    compat.install(reference_src=REF, patch_map=True)
+    ref_map = importlib.import_module("map")
+    assert ref_map.__file__.startswith(REF)
+    assert ref_map.Map.optimize_map is ba.optimize_map
+    assert ref_map.Map.calculate_reprojection_error is map_ops.calculate_reprojection_error
+    m = ref_map.Map()                         # the rest of the class is the reference's own
+    assert m.increment_id() == 0 and m.increment_id() == 1
