@@ -192,6 +192,22 @@ int vo_map_prune_observations(const uint8_t* keep, int n_obs, const int32_t* obs
                               int32_t* obs_cam_out, int32_t* obs_pt_out, double* obs_xy_out,
                               int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
+/* vo_map_remove_camera = Map.remove_camera_from_map (src/map.py:188-232; what
+ * limit_number_of_camera_in_map(18), :301-318, does to the oldest camera): removes camera row
+ * cam_row and its observations, every point left with exactly ONE observation (points left with
+ * none are kept, as in the reference) and the observations of those points; order is preserved,
+ * rows are renumbered, poses / fixed are shifted in place, root_point[] is rebuilt for the new
+ * point rows.  Point and observation arrays are compacted into a second set (must not alias);
+ * n_points_out / n_obs_out are device int32. */
+size_t vo_map_remove_camera_workspace_bytes(int n_points, int n_obs);
+int vo_map_remove_camera(int cam_row, double* poses, uint8_t* fixed, int n_cams,
+                         const double* points_in, const int32_t* fid_in, int n_points,
+                         double* points_out, int32_t* fid_out, int32_t* n_points_out,
+                         const int32_t* obs_cam_in, const int32_t* obs_pt_in, const double* obs_xy_in,
+                         int n_obs, int32_t* obs_cam_out, int32_t* obs_pt_out, double* obs_xy_out,
+                         int32_t* n_obs_out, int32_t* root_point, void* ws, size_t ws_bytes,
+                         void* stream);
+
 /* ---- N3: local bundle adjustment (Map.optimize_map, reference src/map.py:104-186: g2o
  * Levenberg + BlockSolverSE3 (Schur complement on the points) + EdgeProjectXYZ2UV + Huber,
  * optimize(iterations)) on the flat map.  poses double [n_cams,16] (row-major 4x4, world->camera)

@@ -166,6 +166,13 @@ def main():
         save[f"s{b}_pnp_obj"] = captured.get("obj", np.zeros((0, 3))).reshape(-1, 3)
         save[f"s{b}_pnp_img"] = captured.get("img", np.zeros((0, 2))).reshape(-1, 2)
         save[f"s{b}_totals"] = np.array(totals)
+    # map culling by the reference's own Map.limit_number_of_camera_in_map / remove_camera_from_map
+    # (src/map.py:188-232, 301-318): twice, so camera 0 and then the next-oldest go
+    for k, limit in enumerate((len(slam.map.cameras) - 1, len(slam.map.cameras) - 2)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            slam.map.limit_number_of_camera_in_map(limit)
+        snap_map(f"cull{k}")
+        save[f"cull{k}_limit"] = limit
     save.update(snaps)
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "slam_map.npz")
     np.savez_compressed(out, **save)
@@ -174,6 +181,9 @@ def main():
               "points", len(snaps[f"s{b}_end_pt_xyz"]), "obs", len(snaps[f"s{b}_end_obs_pt"]),
               "before prune", len(snaps.get(f"s{b}_before_prune_obs_pt", [])),
               "totals", save[f"s{b}_totals"])
+    for k in range(2):
+        print("cull", k, "cams", len(snaps[f"cull{k}_cam_frame"]), "points", len(snaps[f"cull{k}_pt_xyz"]),
+              "obs", len(snaps[f"cull{k}_obs_pt"]))
     print("wrote", out, os.path.getsize(out), "bytes")
 
 

@@ -65,6 +65,16 @@ def test_device_map_equals_reference_golden(cuda_dev):
             dm.prune(float(g[f"s{b}_prune_thr"]))
         same(f"s{b}_end")
         assert np.array_equal(dm.poses[:len(dm.cam_frame)].cpu().numpy(), g[f"s{b}_end_cam_pose"])
+    # map culling by the reference's own limit_number_of_camera_in_map, twice
+    for k in range(2):
+        dm.limit_number_of_cameras(int(g[f"cull{k}_limit"]))
+        same(f"cull{k}")
+        assert dm.cam_frame == g[f"cull{k}_cam_frame"].tolist()
+        assert np.array_equal(dm.poses[:len(dm.cam_frame)].cpu().numpy(), g[f"cull{k}_cam_pose"])
+    # mappointdict after culling: every surviving point is found through its feature id
+    n_p, _ = dm.counts()
+    rp = dm.tracks.root_point[dm.point_fid[:n_p].long()].cpu().numpy()
+    assert np.array_equal(rp, np.arange(n_p))
 
 
 def test_device_map_equals_oracle_large_scene(cuda_dev):
@@ -110,6 +120,14 @@ def test_device_map_equals_oracle_large_scene(cuda_dev):
         pts, _poses, oc, op, xy = o.flat()
         _same(dm, np.array([f[0] * N + f[1] for f, _x in o.points]), pts, oc, op, xy)
     assert n_pnp > 5000
+    for row in (0, 2, -1):                               # oldest, a middle one, the newest
+        row = row % len(o.cameras)
+        o.remove_camera_from_map(row)
+        dm.remove_camera(row)
+        pts, poses, oc, op, xy = o.flat()
+        _same(dm, np.array([f[0] * N + f[1] for f, _x in o.points]), pts, oc, op, xy)
+        assert np.array_equal(dm.poses[:len(dm.cam_frame)].cpu().numpy(), poses)
+        assert dm.cam_frame == [f for f, _T in o.cameras]
 
 
 def test_device_map_overflow_is_reported_not_written(cuda_dev):

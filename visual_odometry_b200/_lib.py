@@ -67,6 +67,9 @@ SIGNATURES = {
                                     _sz, _p]),
     "vo_map_extend": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _i, _i, _i, _d, _p, _p, _p,
                            _i, _p, _p, _p, _p, _i, _i, _p, _p]),
+    "vo_map_remove_camera_workspace_bytes": (_sz, [_i, _i]),
+    "vo_map_remove_camera": (_i, [_i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p,
+                                  _p, _p, _sz, _p]),
     "vo_bundle_adjust_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_bundle_adjust": (_i, [_p, _p, _i, _p, _i, _p, _p, _p, _i, _d, _d, _d, _d, _i, _p, _p, _p, _p,
                               _p, _p, _sz, _p]),

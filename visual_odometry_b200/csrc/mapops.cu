@@ -360,3 +360,162 @@ extern "C" int vo_map_prune_observations(const uint8_t* keep, int n_obs, const i
                                                      obs_xy_in, obs_cam_out, obs_pt_out, obs_xy_out);
   return check_launch("vo_map_prune_observations");
 }
+
+// ---------------------------------------------------------------------------------------------
+// vo_map_remove_camera = Map.remove_camera_from_map (reference src/map.py:188-232), what
+// limit_number_of_camera_in_map(18) (:301-318, called at src/visual_slam.py:307) does to the
+// oldest camera: drop the camera and its observations, drop every point that is left with exactly
+// ONE observation (points left with none are kept: the reference only looks at points that still
+// occur in an observation), drop the observations of the dropped points; everything else keeps
+// its order.  Rows are renumbered (cameras above the removed one move down by one, points are
+// compacted), and root_point[] (mappointdict) is rebuilt for the new point rows.
+namespace vo {
+
+__global__ void rc_count_kernel(const int32_t* __restrict__ obs_cam, const int32_t* __restrict__ obs_pt,
+                                int n_obs, int cam, int32_t* cnt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_obs && obs_cam[i] != cam) atomicAdd(&cnt[obs_pt[i]], 1);
+}
+
+__global__ void rc_flags_kernel(const int32_t* __restrict__ cnt, int n_points,
+                                const int32_t* __restrict__ obs_cam, const int32_t* __restrict__ obs_pt,
+                                int n_obs, int cam, uint8_t* __restrict__ keep_pt,
+                                uint8_t* __restrict__ keep_obs) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_points) keep_pt[i] = cnt[i] != 1;
+  if (i < n_obs) keep_obs[i] = obs_cam[i] != cam && cnt[obs_pt[i]] != 1;
+}
+
+__global__ void __launch_bounds__(MAPOPS_THREADS)
+rc_scatter_points_kernel(const uint8_t* __restrict__ keep, int n, const int32_t* __restrict__ block_off,
+                         const double* __restrict__ pts_in, const int32_t* __restrict__ fid_in,
+                         double* __restrict__ pts_out, int32_t* __restrict__ fid_out,
+                         int32_t* __restrict__ new_row, int32_t* __restrict__ root_point) {
+  __shared__ int wcnt[MAPOPS_THREADS / 32];
+  const int i = blockIdx.x * MAPOPS_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const bool k = i < n && keep[i];
+  const unsigned bal = __ballot_sync(0xffffffffu, k);
+  if (lane == 0) wcnt[wid] = __popc(bal);
+  __syncthreads();
+  if (i >= n) return;
+  root_point[fid_in[i]] = -1;          // mappointdict is rebuilt from the surviving points below
+  if (!k) { new_row[i] = -1; return; }
+  int off = block_off[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
+  for (int w = 0; w < wid; ++w) off += wcnt[w];
+  new_row[i] = off;
+  pts_out[3 * (size_t)off] = pts_in[3 * (size_t)i];
+  pts_out[3 * (size_t)off + 1] = pts_in[3 * (size_t)i + 1];
+  pts_out[3 * (size_t)off + 2] = pts_in[3 * (size_t)i + 2];
+  fid_out[off] = fid_in[i];
+}
+
+__global__ void rc_publish_kernel(const int32_t* __restrict__ fid, const int32_t* __restrict__ n_ptr,
+                                  int32_t* root_point) {
+  // mappointdict[point.feature_id] = point in list order: the LAST point with an id wins
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < *n_ptr) atomicMax(&root_point[fid[i]], i);
+}
+
+__global__ void __launch_bounds__(MAPOPS_THREADS)
+rc_scatter_obs_kernel(const uint8_t* __restrict__ keep, int n, const int32_t* __restrict__ block_off,
+                      int cam, const int32_t* __restrict__ new_row, const int32_t* __restrict__ cam_in,
+                      const int32_t* __restrict__ pt_in, const double* __restrict__ xy_in,
+                      int32_t* __restrict__ cam_out, int32_t* __restrict__ pt_out,
+                      double* __restrict__ xy_out) {
+  __shared__ int wcnt[MAPOPS_THREADS / 32];
+  const int i = blockIdx.x * MAPOPS_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const bool k = i < n && keep[i];
+  const unsigned bal = __ballot_sync(0xffffffffu, k);
+  if (lane == 0) wcnt[wid] = __popc(bal);
+  __syncthreads();
+  if (!k) return;
+  int off = block_off[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
+  for (int w = 0; w < wid; ++w) off += wcnt[w];
+  const int c = cam_in[i];
+  cam_out[off] = c - (c > cam);
+  pt_out[off] = new_row[pt_in[i]];
+  reinterpret_cast<double2*>(xy_out)[off] = reinterpret_cast<const double2*>(xy_in)[i];
+}
+
+__global__ void __launch_bounds__(512)
+rc_shift_cameras_kernel(double* poses, uint8_t* fixed, int n_cams, int cam) {
+  // rows above `cam` move down by one; one block, values pass through registers
+  const int t = threadIdx.x;
+  const int n = (n_cams - 1 - cam) * 16;
+  double v = 0.0;
+  uint8_t f = 0;
+  if (t < n) v = poses[(cam + 1) * 16 + t];
+  if (t < n_cams - 1 - cam) f = fixed[cam + 1 + t];
+  __syncthreads();
+  if (t < n) poses[cam * 16 + t] = v;
+  if (t < n_cams - 1 - cam) fixed[cam + t] = f;
+}
+
+}  // namespace vo
+
+extern "C" size_t vo_map_remove_camera_workspace_bytes(int n_points, int n_obs) {
+  const size_t P = n_points > 0 ? n_points : 0, M = n_obs > 0 ? n_obs : 0;
+  const size_t nbp = (P + MAPOPS_THREADS - 1) / MAPOPS_THREADS, nbo = (M + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
+  auto up = [](size_t n) { return (n + 255) / 256 * 256; };
+  return up(P * 4) + up(P * 4) + up(P) + up(M) + up(nbp * 4 + 4) + up(nbo * 4 + 4) + 512;
+}
+
+extern "C" int vo_map_remove_camera(int cam_row, double* poses, uint8_t* fixed, int n_cams,
+                                    const double* points_in, const int32_t* fid_in, int n_points,
+                                    double* points_out, int32_t* fid_out, int32_t* n_points_out,
+                                    const int32_t* obs_cam_in, const int32_t* obs_pt_in,
+                                    const double* obs_xy_in, int n_obs, int32_t* obs_cam_out,
+                                    int32_t* obs_pt_out, double* obs_xy_out, int32_t* n_obs_out,
+                                    int32_t* root_point, void* ws, size_t ws_bytes, void* stream) {
+  VO_REQUIRE(n_cams > 0 && n_cams <= 32 && cam_row >= 0 && cam_row < n_cams && n_points >= 0 && n_obs >= 0,
+             VO_ERR_INVALID_ARG, "vo_map_remove_camera: bad sizes");
+  VO_REQUIRE(poses && fixed && n_points_out && n_obs_out && root_point && ws, VO_ERR_INVALID_ARG,
+             "vo_map_remove_camera: null pointer");
+  VO_REQUIRE(n_points == 0 || (points_in && fid_in && points_out && fid_out && points_in != points_out),
+             VO_ERR_INVALID_ARG, "vo_map_remove_camera: point arrays");
+  VO_REQUIRE(n_obs == 0 || (obs_cam_in && obs_pt_in && obs_xy_in && obs_cam_out && obs_pt_out &&
+                            obs_xy_out && obs_cam_in != obs_cam_out),
+             VO_ERR_INVALID_ARG, "vo_map_remove_camera: observation arrays");
+  VO_REQUIRE(ws_bytes >= vo_map_remove_camera_workspace_bytes(n_points, n_obs), VO_ERR_WORKSPACE,
+             "vo_map_remove_camera: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int P = n_points, M = n_obs;
+  const int nbp = (P + MAPOPS_THREADS - 1) / MAPOPS_THREADS, nbo = (M + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
+  char* p = (char*)(((uintptr_t)ws + 255) / 256 * 256);
+  auto take = [&](size_t n) { char* r = p; p += (n + 255) / 256 * 256; return (void*)r; };
+  int32_t* cnt = (int32_t*)take((size_t)P * 4);
+  int32_t* new_row = (int32_t*)take((size_t)P * 4);
+  uint8_t* keep_pt = (uint8_t*)take(P);
+  uint8_t* keep_obs = (uint8_t*)take(M);
+  int32_t* off_pt = (int32_t*)take((size_t)nbp * 4 + 4);
+  int32_t* off_obs = (int32_t*)take((size_t)nbo * 4 + 4);
+  if (P > 0) cudaMemsetAsync(cnt, 0, (size_t)P * 4, st);
+  if (M > 0) rc_count_kernel<<<nbo, MAPOPS_THREADS, 0, st>>>(obs_cam_in, obs_pt_in, M, cam_row, cnt);
+  const int nmax = P > M ? P : M;
+  if (nmax > 0)
+    rc_flags_kernel<<<(nmax + 255) / 256, 256, 0, st>>>(cnt, P, obs_cam_in, obs_pt_in, M, cam_row, keep_pt,
+                                                       keep_obs);
+  if (P > 0) {
+    prune_count_kernel<<<nbp, MAPOPS_THREADS, 0, st>>>(keep_pt, P, off_pt);
+    prune_scan_kernel<<<1, 1024, 0, st>>>(off_pt, nbp, n_points_out);
+    rc_scatter_points_kernel<<<nbp, MAPOPS_THREADS, 0, st>>>(keep_pt, P, off_pt, points_in, fid_in, points_out,
+                                                            fid_out, new_row, root_point);
+    // every surviving point publishes its new row (the new count stays on the device)
+    rc_publish_kernel<<<nbp, MAPOPS_THREADS, 0, st>>>(fid_out, n_points_out, root_point);
+  } else {
+    cudaMemsetAsync(n_points_out, 0, 4, st);
+  }
+  if (M > 0) {
+    prune_count_kernel<<<nbo, MAPOPS_THREADS, 0, st>>>(keep_obs, M, off_obs);
+    prune_scan_kernel<<<1, 1024, 0, st>>>(off_obs, nbo, n_obs_out);
+    rc_scatter_obs_kernel<<<nbo, MAPOPS_THREADS, 0, st>>>(keep_obs, M, off_obs, cam_row, new_row, obs_cam_in,
+                                                         obs_pt_in, obs_xy_in, obs_cam_out, obs_pt_out,
+                                                         obs_xy_out);
+  } else {
+    cudaMemsetAsync(n_obs_out, 0, 4, st);
+  }
+  rc_shift_cameras_kernel<<<1, 512, 0, st>>>(poses, fixed, n_cams, cam_row);
+  return check_launch("vo_map_remove_camera");
+}

@@ -29,9 +29,10 @@ class DeviceMap:
         self.K = torch.as_tensor(np.asarray(K, np.float64).reshape(9)).to(self.dev)
         self.cap_points, self.cap_obs, self.cap_cams = int(cap_points), int(cap_obs), int(cap_cams)
         e = lambda *s, dt: torch.empty(*s, dtype=dt, device=self.dev)
-        self.points = e(self.cap_points, 3, dt=F64)
-        self.point_fid = e(self.cap_points, dt=I32)
-        # observation arrays are double-buffered: pruning compacts from one set into the other
+        # point and observation arrays are double-buffered: compactions write the other set
+        self._pts = [dict(xyz=e(self.cap_points, 3, dt=F64), fid=e(self.cap_points, dt=I32))
+                     for _ in range(2)]
+        self._pcur = 0
         self._obs = [dict(xy=e(self.cap_obs, 2, dt=F64), cam=e(self.cap_obs, dt=I32),
                           pt=e(self.cap_obs, dt=I32)) for _ in range(2)]
         self._cur = 0
@@ -49,6 +50,14 @@ class DeviceMap:
                          self.lib.vo_map_prune_workspace_bytes(self.cap_obs)), dt=U8)
 
     # ------------------------------------------------------------------ views
+    @property
+    def points(self):
+        return self._pts[self._pcur]["xyz"]
+
+    @property
+    def point_fid(self):
+        return self._pts[self._pcur]["fid"]
+
     @property
     def obs_xy(self):
         return self._obs[self._cur]["xy"]
@@ -101,6 +110,29 @@ class DeviceMap:
         return bundle_adjust(self.poses, self.fixed, self.points, self.obs_cam, self.obs_pt,
                              self.obs_xy, self.K.reshape(3, 3), iterations, huber_delta,
                              n_cams=len(self.cam_frame), n_points=n_pts, n_obs=n_obs)
+
+    def remove_camera(self, row=0):
+        """Map.remove_camera_from_map (src/map.py:188-232) for camera `row`."""
+        n_pts, n_obs = self.counts()
+        n_cams = len(self.cam_frame)
+        wsb = self.lib.vo_map_remove_camera_workspace_bytes(n_pts, n_obs)
+        ws = torch.empty(wsb, dtype=U8, device=self.dev)
+        ps, pd = self._pts[self._pcur], self._pts[1 - self._pcur]
+        os_, od = self._obs[self._cur], self._obs[1 - self._cur]
+        _lib.check(self.lib.vo_map_remove_camera(
+            int(row), _lib.ptr(self.poses), _lib.ptr(self.fixed), n_cams, _lib.ptr(ps["xyz"]),
+            _lib.ptr(ps["fid"]), n_pts, _lib.ptr(pd["xyz"]), _lib.ptr(pd["fid"]),
+            _lib.ptr(self.n_points), _lib.ptr(os_["cam"]), _lib.ptr(os_["pt"]), _lib.ptr(os_["xy"]),
+            n_obs, _lib.ptr(od["cam"]), _lib.ptr(od["pt"]), _lib.ptr(od["xy"]), _lib.ptr(self.n_obs),
+            _lib.ptr(self.tracks.root_point), _lib.ptr(ws), wsb, _lib.cur_stream()))
+        self._pcur, self._cur = 1 - self._pcur, 1 - self._cur
+        del self.cam_frame[int(row)]
+
+    def limit_number_of_cameras(self, max_cameras=18):
+        """Map.limit_number_of_camera_in_map (src/map.py:301-318): drop the oldest camera when
+        there are more than `max_cameras`."""
+        if len(self.cam_frame) > max_cameras:
+            self.remove_camera(0)
 
     def camera_row(self, frame_id):
         return self.cam_frame.index(int(frame_id))
