@@ -81,3 +81,30 @@ def rodrigues(src):
         t[2] *= -1 if R[0, 2] < 0 else 1
         return (t * (th / np.linalg.norm(t))).reshape(3, 1), None
     return (r * (0.5 / s) * th).reshape(3, 1), None
+
+
+def solve_pnp_ransac_device(X, x, K_dev, iterationsCount=100, reprojectionError=8.0, confidence=0.99):
+    """solvePnPRansac on DEVICE inputs (X [n,3], x [n,2] float64 CUDA tensors, K_dev [9] float64 on
+    the device): no upload; one 56-byte read-back.  -> (retval, rvec [3,1], tvec [3,1], n_inliers)."""
+    n = int(X.shape[0])
+    if n < 4 or int(x.shape[0]) != n:
+        raise CvError("solvePnPRansac: npoints >= 4 && npoints == max(ipoints.checkVector(2))")
+    if n < 5:
+        raise NotImplementedError("libvo_b200 PnP: the n == 4 (P3P) special case is not implemented")
+    lib = _lib.load()
+    X, x = X.contiguous(), x.contiguous()
+    out = torch.zeros(48 + 8 + 4 * n, dtype=torch.uint8, device=X.device)
+    ob = out.data_ptr()
+    vp = _lib.C.c_void_p
+    wsb = lib.vo_pnp_workspace_bytes(n, int(iterationsCount))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=X.device)
+    _lib.check(lib.vo_pnp_ransac(_lib.ptr(X), _lib.ptr(x), n, _lib.ptr(K_dev), int(iterationsCount),
+                                 float(reprojectionError), float(confidence), vp(ob), vp(ob + 24),
+                                 vp(ob + 56), vp(ob + 48), vp(ob + 52), _lib.ptr(ws), wsb,
+                                 _lib.cur_stream()))
+    host = out[:56].cpu().numpy()
+    rt = host[:48].view(np.float64)
+    n_inl, ok = (int(v) for v in host[48:56].view(np.int32))
+    if not ok:
+        return False, np.zeros((3, 1)), np.zeros((3, 1)), 0
+    return True, rt[:3].copy().reshape(3, 1), rt[3:6].copy().reshape(3, 1), n_inl
