@@ -81,3 +81,20 @@ def test_device_slam_tracks_the_true_trajectory(cuda_dev):
     s = (S * np.diag(D)).sum() / (A ** 2).sum()
     err = np.linalg.norm(s * (Rr @ A.T).T - B, axis=1)
     assert err.max() < 0.03 * np.linalg.norm(B, axis=1).max()
+
+
+def test_streaming_equals_batch(cuda_dev):
+    """add_frame (one pair at a time, as the reference consumes a video) gives the same map as
+    the batched pass over the whole sequence, bit for bit."""
+    F, N = 6, 1200
+    seq = make_sequence(F, N, 5, descriptor="orb")
+    a = DeviceSlam(seq.K, N, F, descriptor="orb")
+    a.run(seq.desc, seq.kp, seq.nkp)
+    b = DeviceSlam(seq.K, N, F, descriptor="orb")
+    for f in range(F):
+        b.add_frame(seq.desc[f, :seq.nkp[f]], seq.kp[f, :seq.nkp[f]])
+    (pa, oa), (pb, ob) = a.map.counts(), b.map.counts()
+    assert (pa, oa) == (pb, ob) and a.map.cam_frame == b.map.cam_frame
+    assert np.array_equal(a.map.poses[:F].cpu().numpy(), b.map.poses[:F].cpu().numpy())
+    assert np.array_equal(a.map.points[:pa].cpu().numpy(), b.map.points[:pb].cpu().numpy())
+    assert np.array_equal(a.map.obs_pt[:oa].cpu().numpy(), b.map.obs_pt[:ob].cpu().numpy())

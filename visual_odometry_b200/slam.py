@@ -44,6 +44,26 @@ class DeviceSlam:
         self.pipe.run_host(desc, kp, nkp, pairs)
         return [self.step(b) for b in range(F - 1)]
 
+    # ------------------------------------------------------------------ streaming
+    def add_frame(self, desc, kp):
+        """VisualSlam.add_to_list_of_frames + match_current_and_previous_frame for ONE new frame
+        (src/visual_slam.py:39-41, 286-307): upload its descriptors / keypoints, run the hot path
+        on the pair (previous, new), then the map stage.  Returns None for the first frame."""
+        p = self.pipe
+        f = getattr(self, "_n_frames", 0)
+        if f >= self.max_frames:
+            raise RuntimeError("DeviceSlam: max_frames exceeded")
+        n = int(desc.shape[0])
+        p.desc[f, :n].copy_(torch.from_numpy(np.ascontiguousarray(desc)))
+        p.kp[f, :n].copy_(torch.from_numpy(np.ascontiguousarray(kp, np.float32)))
+        p.nkp[f] = n
+        self._n_frames = f + 1
+        if f == 0:
+            return None
+        p.pairs[f - 1].copy_(torch.tensor([f - 1, f], dtype=torch.int32))
+        p.run_device(1, p0=f - 1, chain=False)
+        return self.step(f - 1)
+
     # ------------------------------------------------------------------ one new frame (b + 1)
     def step(self, b):
         p, m = self.pipe, self.map
