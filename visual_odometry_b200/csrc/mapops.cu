@@ -16,8 +16,9 @@
 namespace vo {
 
 constexpr int MAPOPS_THREADS = 256;
+constexpr int REPROJ_SMEM_CAMS = 128;
 
-__global__ void __launch_bounds__(MAPOPS_THREADS)
+__global__ void __launch_bounds__(MAPOPS_THREADS, 8)
 reproj_kernel(const double* __restrict__ points, const double* __restrict__ poses,
               const int32_t* __restrict__ obs_cam, const int32_t* __restrict__ obs_pt,
               const double* __restrict__ obs_xy, int n_obs, int n_points, int n_cams,
@@ -26,29 +27,50 @@ reproj_kernel(const double* __restrict__ points, const double* __restrict__ pose
               int32_t* __restrict__ block_keep) {
   __shared__ double red[MAPOPS_THREADS / 32];
   __shared__ int redk[MAPOPS_THREADS / 32];
-  const int i = blockIdx.x * MAPOPS_THREADS + threadIdx.x;
+  // camera poses (rows 0..2) and K staged in shared memory, pose stride 13 doubles so lanes that
+  // look at different cameras hit different banks (global loads of 18 scattered 128-byte pose
+  // rows per instruction made the kernel LSU-bound: 1.0 of 6.5 TB/s)
+  __shared__ double sT[REPROJ_SMEM_CAMS * 13];
+  __shared__ double sK[9];
+  const bool staged = n_cams <= REPROJ_SMEM_CAMS;
+  if (staged)
+    for (int e = threadIdx.x; e < n_cams * 12; e += MAPOPS_THREADS)
+      sT[(e / 12) * 13 + e % 12] = poses[(size_t)(e / 12) * 16 + e % 12];
+  if (threadIdx.x < 9) sK[threadIdx.x] = K[threadIdx.x];
+  __syncthreads();
+  // persistent blocks: tile = 256 consecutive observations; the per-tile partial sums (and so the
+  // summation order of the total) do not depend on the grid size
+  const int n_tiles = (n_obs + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  const int i = tile * MAPOPS_THREADS + threadIdx.x;
   double e = 0.0;
   int kept = 0;
   if (i < n_obs) {
     const int c = obs_cam[i], p = obs_pt[i];
     double err = __longlong_as_double(0x7ff8000000000000ll);   // NaN: bad index
     if (c >= 0 && c < n_cams && p >= 0 && p < n_points) {
-      const double* T = poses + (size_t)c * 16;
+      double T[12];
+      if (staged) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) T[k] = sT[c * 13 + k];
+      } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) T[k] = __ldg(poses + (size_t)c * 16 + k);
+      }
       const double X = __ldg(points + 3 * (size_t)p), Y = __ldg(points + 3 * (size_t)p + 1),
                    Z = __ldg(points + 3 * (size_t)p + 2);
       // row-times-column in index order, no FMA contraction (numpy's small matmul order)
       double pc[3];
 #pragma unroll
       for (int r = 0; r < 3; ++r)
-        pc[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(__ldg(T + 4 * r), X),
-                                              __dmul_rn(__ldg(T + 4 * r + 1), Y)),
-                                    __dmul_rn(__ldg(T + 4 * r + 2), Z)),
-                          __ldg(T + 4 * r + 3));
+        pc[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(T[4 * r], X), __dmul_rn(T[4 * r + 1], Y)),
+                                    __dmul_rn(T[4 * r + 2], Z)),
+                          T[4 * r + 3]);
       double t[3];
 #pragma unroll
       for (int r = 0; r < 3; ++r)
-        t[r] = __dadd_rn(__dadd_rn(__dmul_rn(__ldg(K + 3 * r), pc[0]), __dmul_rn(__ldg(K + 3 * r + 1), pc[1])),
-                         __dmul_rn(__ldg(K + 3 * r + 2), pc[2]));
+        t[r] = __dadd_rn(__dadd_rn(__dmul_rn(sK[3 * r], pc[0]), __dmul_rn(sK[3 * r + 1], pc[1])),
+                         __dmul_rn(sK[3 * r + 2], pc[2]));
       const double2 xy = reinterpret_cast<const double2*>(obs_xy)[i];
       const double dx = __dsub_rn(__ddiv_rn(t[0], t[2]), xy.x);
       const double dy = __dsub_rn(__ddiv_rn(t[1], t[2]), xy.y);
@@ -70,24 +92,36 @@ reproj_kernel(const double* __restrict__ points, const double* __restrict__ pose
     double s = 0.0;
     int k = 0;
     for (int w = 0; w < MAPOPS_THREADS / 32; ++w) { s += red[w]; k += redk[w]; }
-    block_sums[blockIdx.x] = s;
-    block_keep[blockIdx.x] = k;
+    block_sums[tile] = s;
+    block_keep[tile] = k;
+  }
+  __syncthreads();
   }
 }
 
-__global__ void reproj_total_kernel(const double* __restrict__ block_sums,
-                                    const int32_t* __restrict__ block_keep, int n_blocks,
-                                    double* __restrict__ total, int32_t* __restrict__ n_keep) {
-  // one warp, strided partial sums in fixed order, then a shuffle tree
-  const int lane = threadIdx.x;
+__global__ void __launch_bounds__(1024)
+reproj_total_kernel(const double* __restrict__ block_sums, const int32_t* __restrict__ block_keep,
+                    int n_blocks, double* __restrict__ total, int32_t* __restrict__ n_keep) {
+  // one block: strided partial sums in a fixed order, shuffle tree, warps in order
+  __shared__ double red[32];
+  __shared__ int redk[32];
+  const int tid = threadIdx.x;
   double s = 0.0;
   int k = 0;
-  for (int b = lane; b < n_blocks; b += 32) { s += block_sums[b]; k += block_keep[b]; }
+  for (int b = tid; b < n_blocks; b += 1024) { s += block_sums[b]; k += block_keep[b]; }
   for (int o = 16; o > 0; o >>= 1) {
     s += __shfl_down_sync(0xffffffffu, s, o);
     k += __shfl_down_sync(0xffffffffu, k, o);
   }
-  if (lane == 0) { *total = s; if (n_keep) *n_keep = k; }
+  if ((tid & 31) == 0) { red[tid >> 5] = s; redk[tid >> 5] = k; }
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    int c = 0;
+    for (int w = 0; w < 32; ++w) { t += red[w]; c += redk[w]; }
+    *total = t;
+    if (n_keep) *n_keep = c;
+  }
 }
 
 }  // namespace vo
@@ -121,10 +155,11 @@ extern "C" int vo_reprojection_errors(const double* points, int n_points, const 
   const int nb = (n_obs + MAPOPS_THREADS - 1) / MAPOPS_THREADS;
   double* block_sums = (double*)ws;
   int32_t* block_keep = (int32_t*)(block_sums + nb);
-  reproj_kernel<<<nb, MAPOPS_THREADS, 0, st>>>(points, poses, obs_cam, obs_pt, obs_xy, n_obs,
+  const int grid = nb < 148 * 8 ? nb : 148 * 8;       // 8 resident blocks per SM
+  reproj_kernel<<<grid, MAPOPS_THREADS, 0, st>>>(points, poses, obs_cam, obs_pt, obs_xy, n_obs,
                                               n_points, n_cams, K, threshold, sqerr, keep,
                                               block_sums, block_keep);
-  reproj_total_kernel<<<1, 32, 0, st>>>(block_sums, block_keep, nb, total, n_keep);
+  reproj_total_kernel<<<1, 1024, 0, st>>>(block_sums, block_keep, nb, total, n_keep);
   return check_launch("vo_reprojection_errors");
 }
 
