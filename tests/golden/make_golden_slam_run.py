@@ -26,7 +26,7 @@ from visual_odometry_b200.frame import SyntheticDetector   # noqa: E402
 from visual_odometry_b200.synth import K_REFERENCE, make_sequence  # noqa: E402
 
 F, N, SEED, MAX_CAMS = 8, 400, 20261104 + 9, 5
-BA_LOG, PNP_LOG = [], []
+BA_LOG, PNP_LOG, PNP_ARGS = [], [], []
 
 
 def oracle_optimize_map(self, postfix=""):
@@ -80,6 +80,8 @@ def main():
             r = cv2.solvePnPRansac(obj, img, Kc, dist)
             PNP_LOG.append(np.r_[len(obj), float(r[0]), r[1].ravel(), r[2].ravel(),
                                  0 if r[3] is None else len(r[3])])
+            PNP_ARGS[:] = [np.array(obj, np.float64), np.array(img, np.float64),
+                           np.zeros(0, np.int32) if r[3] is None else r[3].ravel().astype(np.int32)]
             return r
 
         @staticmethod
@@ -101,6 +103,7 @@ def main():
     for f in range(F):
         BA_LOG.clear()
         PNP_LOG.clear()
+        PNP_ARGS.clear()
         with contextlib.redirect_stdout(io.StringIO()):
             slam.add_to_list_of_frames(None)
             slam.match_current_and_previous_frame()
@@ -122,6 +125,8 @@ def main():
         ipair = slam.current_image_pair
         save[tag + "_ba_log"] = np.array(BA_LOG, np.float64).reshape(-1, 6)
         save[tag + "_pnp_log"] = np.array(PNP_LOG, np.float64).reshape(-1, 9)
+        if PNP_ARGS:
+            save[tag + "_pnp_obj"], save[tag + "_pnp_img"], save[tag + "_pnp_inliers"] = PNP_ARGS
         save[tag + "_n_matches"] = len(ipair.filtered_matches)
         save[tag + "_n_3d"] = len(ipair.matches_with_3d_information)
         gt = np.eye(4)

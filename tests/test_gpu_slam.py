@@ -98,3 +98,77 @@ def test_streaming_equals_batch(cuda_dev):
     assert np.array_equal(a.map.poses[:F].cpu().numpy(), b.map.poses[:F].cpu().numpy())
     assert np.array_equal(a.map.points[:pa].cpu().numpy(), b.map.points[:pb].cpu().numpy())
     assert np.array_equal(a.map.obs_pt[:oa].cpu().numpy(), b.map.obs_pt[:ob].cpu().numpy())
+
+
+def _load_golden_state(slam, g, tag, N, b):
+    """put the reference's map after frame b (golden `tag`) into the device map and replay the
+    feature_mapper links of pairs 0..b-1 from the hot-path results"""
+    import torch
+    m, p = slam.map, slam.pipe
+    m.tracks.reset()
+    for k in range(b):
+        m.update_tracks(p.q[k], p.t_idx[k], p.mask[k], p.n_match[k:k + 1], k, k + 1)
+    fid = g[tag + "_pt_fid"]
+    n_p, n_o, n_c = len(fid), len(g[tag + "_obs_pt"]), len(g[tag + "_cam_frame"])
+    dev = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dt).cuda()
+    m.points[:n_p].copy_(dev(g[tag + "_pt_xyz"], torch.float64))
+    m.point_fid[:n_p].copy_(dev(fid[:, 0] * N + fid[:, 1], torch.int32))
+    m.obs_cam[:n_o].copy_(dev(g[tag + "_obs_cam"], torch.int32))
+    m.obs_pt[:n_o].copy_(dev(g[tag + "_obs_pt"], torch.int32))
+    m.obs_xy[:n_o].copy_(dev(g[tag + "_obs_xy"], torch.float64))
+    m.poses[:n_c].copy_(dev(g[tag + "_cam_pose"], torch.float64))
+    m.fixed[:n_c].copy_(dev(g[tag + "_cam_fixed"], torch.uint8))
+    m.cam_frame = g[tag + "_cam_frame"].tolist()
+    m.n_points.fill_(n_p); m.n_obs.fill_(n_o); m.status.zero_()
+    m.tracks.set_map_points(m.point_fid[:n_p])
+
+
+def test_each_frame_from_the_reference_state(cuda_dev):
+    """Teacher-forced: every frame's map stage starts from the REFERENCE's map after the previous
+    frame (golden), so rounding differences cannot accumulate.  Where PnP-RANSAC settles on cv2's
+    consensus set (pose equal to 1e-6) the whole stage is compared tightly: adjustment problem going
+    in (robust chi2 1e-8), cost coming out (1e-6), map sizes after pruning and culling (exact),
+    points and poses (1e-6).  On this poor map (the reference's own two-view initialisation) many
+    points sit near the 8 px threshold and cv2 / the kernel pick different, equally supported sets on
+    some frames; there the adjusted cost and the map sizes must still agree to a few percent."""
+    import cv2
+    z = np.load(os.path.join(GOLDEN, "slam_run.npz"))
+    g = {k: z[k] for k in z.files}
+    F, N = int(g["F"]), int(g["N"])
+    seq = make_sequence(F, N, int(g["seed"]), descriptor="sift", K=g["K"])
+    slam = DeviceSlam(g["K"], N, F, descriptor="sift", max_cameras=int(g["max_cams"]))
+    pairs = np.stack([np.arange(F - 1), np.arange(1, F)], 1).astype(np.int32)
+    slam.pipe.run_host(seq.desc, seq.kp, seq.nkp, pairs)
+    checked = 0
+    for b in range(1, F - 1):
+        prev, tag = f"f{b}", f"f{b + 1}"
+        pnp_ref = g[tag + "_pnp_log"]
+        if len(pnp_ref) == 0 or pnp_ref[0][1] != 1 or pnp_ref[0][0] < 20:
+            continue                       # the reference did not localise this frame (tiny map)
+        _load_golden_state(slam, g, prev, N, b)
+        info = slam.step(b)
+        assert info["pnp_points"] == int(pnp_ref[0][0])
+        assert info["pnp_ok"]
+        d_pose = np.abs(info["pnp_pose"] - pnp_ref[0][2:8]).max()
+        ba_ref = g[tag + "_ba_log"][-1]
+        n_p, n_o = slam.map.counts()
+        ref_p, ref_o = len(g[tag + "_pt_xyz"]), len(g[tag + "_obs_pt"])
+        assert info["cameras"] == g[tag + "_cam_frame"].tolist()
+        if d_pose < 1e-6:
+            # same consensus set as cv2: everything downstream is the same problem
+            assert abs(info["ba"]["chi2_initial"] - ba_ref[3]) <= 1e-8 * ba_ref[3]
+            assert abs(info["ba"]["chi2"][-1] - ba_ref[4]) <= 1e-6 * ba_ref[4]
+            assert (n_p, n_o) == (ref_p, ref_o)
+            X, Xr = slam.map.points[:n_p].cpu().numpy(), g[tag + "_pt_xyz"]
+            assert np.abs(X - Xr).max() <= 1e-6 * np.abs(Xr).max()
+            poses = slam.map.poses[:len(slam.map.cam_frame)].cpu().numpy()
+            assert np.abs(poses - g[tag + "_cam_pose"]).max() < 1e-6
+            checked += 1
+        else:
+            # a different (equally supported) consensus set: the adjusted cost and the map sizes
+            # must still be close
+            assert abs(info["ba"]["chi2"][-1] - ba_ref[4]) <= 5e-2 * ba_ref[4]
+            assert abs(n_p - ref_p) <= max(2, ref_p // 20) and abs(n_o - ref_o) <= max(4, ref_o // 20)
+        print(tag, "pnp pose diff", d_pose, "chi2 in", info["ba"]["chi2_initial"], ba_ref[3], "out",
+              float(info["ba"]["chi2"][-1]), ba_ref[4], "sizes", (n_p, n_o), (ref_p, ref_o))
+    assert checked >= 1
