@@ -101,6 +101,12 @@ class DeviceMap:
             f[n - 2] = 0
         self.fixed[:n].copy_(f)
 
+    def unfreeze_cameras(self, number_of_fixed_cameras=5):
+        """VisualSlam.unfreeze_cameras (src/visual_slam.py:281-286): camera rows above
+        `number_of_fixed_cameras` become free, the others fixed."""
+        n = len(self.cam_frame)
+        self.fixed[:n].copy_((torch.arange(n) <= number_of_fixed_cameras).to(U8))
+
     def optimize(self, iterations=40, huber_delta=1.0):
         """Map.optimize_map (src/map.py:104-186) on the device arrays, in place."""
         from .ba import bundle_adjust
