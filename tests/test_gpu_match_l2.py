@@ -95,6 +95,24 @@ def test_large_norm_descriptors_take_the_rerank_path(cuda_dev):
     assert _triples(ref) == _triples(got)
 
 
+def test_fragment_layout_epilogue_equal_cv2(cuda_dev):
+    """the experimental epilogue of the one-pass mutual kernel (tcgen05.ld 16x256b fragments, behind
+    vo_debug_l2(64); not the default: measured 3 % slower) returns the same matches"""
+    import ctypes
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    try:
+        assert raw.vo_debug_l2(64) == 0
+        for n1, n2 in [(129, 513), (300, 257), (2000, 1777)]:
+            seq = _sift(max(n1, n2), n1 * 31 + n2 + 1)
+            d1, d2 = seq.desc[0][:n1].copy(), seq.desc[1][:n2].copy()
+            d1[5], d2[7], d1[9] = d1[3], d2[2], d2[2]
+            ref = cv2.BFMatcher(cv2.NORM_L2, crossCheck=True).match(d1, d2)
+            got = B200Matcher(NORM_L2, crossCheck=True).match(d1, d2)
+            assert _triples(ref) == _triples(got)
+    finally:
+        raw.vo_debug_l2(0)
+
+
 def test_batched_ragged_frames_pair_list_and_points(cuda_dev):
     """batched entry: ragged keypoint counts, arbitrary pair list (both modes), fused gather."""
     lib = _lib.load()

@@ -59,7 +59,7 @@ constexpr float L2_PAD_SCORE = 4194304.0f;        // MAGIC - 2^21: below every r
 // = nearest query row, lowest row on ties.  Padded rows carry |a|^2 := 2^22 + 2^21 and always lose.
 constexpr uint32_t L2_COL_OFFSET = L2_MAGIC_BITS - (1u << 23);
 constexpr uint32_t L2_PAD_NORM = (1u << 22) + (1u << 21);
-enum { L2_MODE_TOP1 = 0, L2_MODE_TOP2 = 1, L2_MODE_TOP1_COLMAX = 2 };
+enum { L2_MODE_TOP1 = 0, L2_MODE_TOP2 = 1, L2_MODE_TOP1_COLMAX = 2, L2_MODE_TOP1_COLMAX_FRAG = 3 };
 
 struct L2Ws {
   __nv_bfloat16* tiles;   // [F][nblk][20480]
@@ -386,6 +386,135 @@ __device__ __forceinline__ void l2_insert(L2Top& s, uint32_t k, int t) {
   }
 }
 
+// IMAD forms the compiler must not take apart (it would split the addend off or fuse it into a
+// VIADDMNMX chain, which defeats the 3-input max trees): d = a * b + c
+__device__ __forceinline__ uint32_t imad_r(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+// row keys of one fragment row p of a 16-lane half (8 columns 8 i + 2 j4 + e, i = 0..3, e = 0..1);
+// radd[2 i + e] = 31 - (8 i + 2 j4 + e)
+template <int P>
+__device__ __forceinline__ uint32_t l2_frag_rowmax(const uint32_t (&v)[16], uint32_t mul, const uint32_t (&radd)[8]) {
+  const uint32_t k0 = imad_r(v[0 + 2 * P], mul, radd[0]), k1 = imad_r(v[1 + 2 * P], mul, radd[1]);
+  const uint32_t k2 = imad_r(v[4 + 2 * P], mul, radd[2]), k3 = imad_r(v[5 + 2 * P], mul, radd[3]);
+  const uint32_t k4 = imad_r(v[8 + 2 * P], mul, radd[4]), k5 = imad_r(v[9 + 2 * P], mul, radd[5]);
+  const uint32_t k6 = imad_r(v[12 + 2 * P], mul, radd[6]), k7 = imad_r(v[13 + 2 * P], mul, radd[7]);
+  return max(umax3(umax3(k0, k1, k2), umax3(k3, k4, k5), k6), k7);
+}
+
+// Column half of the fragment epilogue: cmax[c] = best key of column 8 (c >> 1) + 2 j4 + (c & 1)
+// among the thread's 8 rows.  A three-stage transposing butterfly over g8 leaves ONE column per
+// thread; one 128-byte store per warp.
+__device__ __forceinline__ void l2_frag_colstore(const L2Ws& w, const L2Item& it, const uint32_t (&cmax)[8],
+                                                 int quarter, int cq, int g8, int j4, int t, int nblk,
+                                                 int nrbp) {
+  const bool b0 = (g8 & 1) != 0, b1 = (g8 & 2) != 0, b2 = (g8 & 4) != 0;
+  uint32_t c1[4], c2[2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {          // exchange over e
+    const uint32_t send = b0 ? cmax[2 * i] : cmax[2 * i + 1], keep = b0 ? cmax[2 * i + 1] : cmax[2 * i];
+    c1[i] = max(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+  }
+#pragma unroll
+  for (int x = 0; x < 2; ++x) {          // exchange over the low bit of i
+    const uint32_t send = b1 ? c1[2 * x] : c1[2 * x + 1], keep = b1 ? c1[2 * x + 1] : c1[2 * x];
+    c2[x] = max(keep, __shfl_xor_sync(0xffffffffu, send, 8));
+  }
+  const uint32_t send = b2 ? c2[0] : c2[1], keep = b2 ? c2[1] : c2[0];
+  const uint32_t cm = max(keep, __shfl_xor_sync(0xffffffffu, send, 16));
+  const int col = 8 * (2 * ((g8 >> 2) & 1) + ((g8 >> 1) & 1)) + 2 * j4 + (g8 & 1);
+  const size_t ncol = (size_t)nblk * L2_BLK;
+  w.colpart[(((size_t)it.pair * nrbp + it.rbp) * 4 + quarter) * ncol + (size_t)(it.t_lo + t) * L2_BLK +
+            cq * 32 + col] = cm;
+}
+
+// Row butterfly of one row block: rmax[h * 2 + p] -> the best key of ONE row per thread
+__device__ __forceinline__ uint32_t l2_frag_rowbest(const uint32_t (&rmax)[4], bool jb0, bool jb1) {
+  uint32_t r1[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const uint32_t send = jb0 ? rmax[2 * h] : rmax[2 * h + 1], keep = jb0 ? rmax[2 * h + 1] : rmax[2 * h];
+    r1[h] = max(keep, __shfl_xor_sync(0xffffffffu, send, 1));
+  }
+  const uint32_t send = jb1 ? r1[0] : r1[1], keep = jb1 ? r1[1] : r1[0];
+  return max(keep, __shfl_xor_sync(0xffffffffu, send, 2));
+}
+
+// Key construction of one 16-lane half of a row block (the IMAD half of the epilogue): r0 / r1 =
+// best row key among the thread's 8 columns of rows g8 / g8 + 8, cmax[c] folds the two rows in
+// (column keys: bits * 256 + cadd(row); mul2 = 0 switches a row block off)
+template <bool ADDM, bool FIRST>
+__device__ __forceinline__ void l2_frag_keys(uint32_t (&v)[16], uint32_t cadd_p0, uint32_t cadd_p1, uint32_t mul,
+                                             uint32_t mul2, const uint32_t (&radd)[8], uint32_t& r0,
+                                             uint32_t& r1, uint32_t (&cmax)[8]) {
+  if (ADDM) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = __float_as_uint(__fadd_rn(__uint_as_float(v[k]), L2_MAGIC));
+  }
+  r0 = l2_frag_rowmax<0>(v, mul, radd);
+  r1 = l2_frag_rowmax<1>(v, mul, radd);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const uint32_t k0 = imad_r(v[4 * (c >> 1) + (c & 1)], mul2, cadd_p0);
+    const uint32_t k1 = imad_r(v[4 * (c >> 1) + 2 + (c & 1)], mul2, cadd_p1);
+    cmax[c] = FIRST ? max(k0, k1) : umax3(cmax[c], k0, k1);
+  }
+}
+
+// One B tile of the single-pass mutual mode with fragment-shaped TMEM loads (16x256b.x4: a thread
+// holds rows {g8, g8 + 8} x columns {8i + 2 j4 + e} of a 16-lane half; two halves, two row blocks
+// -> 8 rows x 8 columns per thread).  Rows: max over the thread's 8 columns (4 min/max ops), then a
+// two-stage transposing butterfly over j4 leaves ONE row per row block in every thread.  Columns:
+// max over the thread's 8 rows, then a three-stage butterfly over g8 leaves ONE column per thread.
+// Software-pipelined so that the select/shuffle work (ALU pipe) has key construction (IMAD, FMA
+// pipe) or a TMEM load to run beside: one 16-register load is in flight while the previous one is
+// turned into keys, the column butterfly of tile t - 1 runs under the first load of tile t, the
+// row butterfly of block 0 beside the keys of block 1.
+template <bool ADDM>
+__device__ __forceinline__ void l2_frag_tile(L2Smem& S, const L2Ws& w, const L2Item& it, L2Top (&st)[L2_RBK],
+                                             const uint32_t (&cadd8)[8], const uint32_t (&radd)[8],
+                                             uint32_t (&cpend)[8], uint32_t tmem, int as, int quarter, int cq,
+                                             int g8, int j4, int lane, int t, int tcol, uint32_t mul,
+                                             uint32_t mul2, int nblk, int nrbp, int dbg) {
+  const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16) + as * (L2_RBK * L2_BLK) + cq * 32;
+  const bool two = it.nrb == 2;
+  const uint32_t mul2b = two ? mul2 : 0u;  // a missing second row block never wins a column
+  const bool jb0 = (j4 & 1) != 0, jb1 = (j4 & 2) != 0;
+  uint32_t va[16], vb[16];                 // [4 i + 2 p + e] of one 16-lane half
+  uint32_t ra[4], rb4[4];
+#ifdef L2_FRAG_TIMING                     // timing experiments only: the branches split the schedule
+  const bool noload = (dbg & 4) != 0, norank = (dbg & 2) != 0;
+#else
+  constexpr bool noload = false, norank = false;
+#endif
+  if (noload) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) va[k] = vb[k] = L2_MAGIC_BITS + (uint32_t)(k + lane);
+  }
+  if (!noload) tc::ld_16x256b_x4_issue(tbase, va);                                  // block 0, lanes 0..15
+  if (t > 0 && !norank) l2_frag_colstore(w, it, cpend, quarter, cq, g8, j4, t - 1, nblk, nrbp);
+  if (!noload) { tc::ld_wait16(va); tc::ld_16x256b_x4_issue(tbase + (16u << 16), vb); }   // block 0, 16..31
+  if (!norank) l2_frag_keys<ADDM, true>(va, cadd8[0], cadd8[1], mul, mul2, radd, ra[0], ra[1], cpend);
+  if (!noload) { tc::ld_wait16(vb); tc::ld_16x256b_x4_issue(tbase + L2_BLK, va); }        // block 1, 0..15
+  if (!norank) l2_frag_keys<ADDM, false>(vb, cadd8[2], cadd8[3], mul, mul2, radd, ra[2], ra[3], cpend);
+  if (!noload) { tc::ld_wait16(va); tc::ld_16x256b_x4_issue(tbase + L2_BLK + (16u << 16), vb); }
+  if (!norank) {
+    l2_fold_tile<false>(st[0], l2_frag_rowbest(ra, jb0, jb1), 0u, tcol);
+    l2_frag_keys<ADDM, false>(va, cadd8[4], cadd8[5], mul, mul2b, radd, rb4[0], rb4[1], cpend);
+  }
+  if (!noload) tc::ld_wait16(vb);
+  tc::fence_before_sync();
+  __syncwarp();
+  if (lane == 0) tc::mbar_arrive(&S.tmem_empty[as]);   // the accumulators are in registers
+  if (norank) return;
+  l2_frag_keys<ADDM, false>(vb, cadd8[6], cadd8[7], mul, mul2b, radd, rb4[2], rb4[3], cpend);
+  const uint32_t best1 = l2_frag_rowbest(rb4, jb0, jb1);
+  if (two) l2_fold_tile<false>(st[1], best1, 0u, tcol);
+  if (t == it.ntile - 1) l2_frag_colstore(w, it, cpend, quarter, cq, g8, j4, t, nblk, nrbp);
+}
+
 // MODE: TOP1 = nearest neighbour of every row (cross-check from two directions, fallback for
 // inexact data); TOP2 = two nearest (knn + ratio); TOP1_COLMAX = nearest neighbour of every row
 // AND of every column from the same accumulator (cross-check in ONE pass, exact data only).
@@ -396,7 +525,8 @@ __global__ void __launch_bounds__(L2_THREADS, 1)
 l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ pairs, int nblk,
                   int n_splits, int ndir, int n_items, int run_if, L2Ws w) {
   constexpr bool TOP2 = (MODE == L2_MODE_TOP2);
-  constexpr bool COLMAX = (MODE == L2_MODE_TOP1_COLMAX);
+  constexpr bool FRAG = (MODE == L2_MODE_TOP1_COLMAX_FRAG);   // fragment-shaped TMEM loads
+  constexpr bool COLMAX = (MODE == L2_MODE_TOP1_COLMAX) || FRAG;
   if (run_if >= 0 && (w.flags[0] != 0) != (run_if != 0)) return;
   extern __shared__ uint8_t smem_raw[];
   L2Smem& S = *reinterpret_cast<L2Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -477,10 +607,16 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
   } else {
     // ===== epilogue warps 0..15: thread = TMEM lane = query row, warp/4 = 32-column quarter ====
     const int quarter = warp & 3, cq = warp >> 2;
-    const int rl = quarter * 32 + lane;
+    // FRAG: tcgen05.ld 16x256b hands a thread 2 rows x 8 columns of every 16-lane half; after the
+    // row butterfly thread (g8, j4) owns row 16 (j4 >> 1) + 8 (j4 & 1) + g8 of its warp's 32
+    const int g8 = lane >> 2, j4 = lane & 3;
+    const int rl = FRAG ? quarter * 32 + 16 * (j4 >> 1) + 8 * (j4 & 1) + g8 : quarter * 32 + lane;
     const uint32_t mul = 128u + (uint32_t)(n_items < 0);   // = 128, opaque to the compiler
     const uint32_t mul2 = 256u + (uint32_t)(n_items < 0);  // = 256 (column keys)
     const float inv_s2 = 1.f / (l2_scale(w.flags) * l2_scale(w.flags));
+    uint32_t radd[8];                      // FRAG: 31 - column of the thread's 8 fragment columns
+#pragma unroll
+    for (int k = 0; k < 8; ++k) radd[k] = 31u - (uint32_t)(8 * (k >> 1) + 2 * j4 + (k & 1));
     uint32_t g = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       const L2Item it = l2_item(item, nkp, pairs, nblk, nrbp, n_splits, ndir);
@@ -489,7 +625,9 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
 #pragma unroll
       for (int rb = 0; rb < L2_RBK; ++rb) { st[rb].k1 = st[rb].k2 = 0u; st[rb].t1 = st[rb].t2 = -1; }
       uint32_t cadd[L2_RBK] = {0u, 0u};
-      if (COLMAX) {
+      uint32_t cpend[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // FRAG: column keys of the previous tile
+      uint32_t cadd8[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // FRAG: the 8 rows this thread sees, slot = rb * 4 + h * 2 + p
+      if (COLMAX && !FRAG) {
         const float s2 = l2_scale(w.flags) * l2_scale(w.flags);
 #pragma unroll
         for (int rb = 0; rb < L2_RBK; ++rb) {
@@ -500,13 +638,36 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
           cadd[rb] = (255u - (uint32_t)(rb * L2_BLK + rl)) - ((na + L2_COL_OFFSET) << 8);
         }
       }
+      if constexpr (FRAG) {
+        // the 8 norm loads are unconditional (clamped index) so that they are all in flight at once
+        const float s2 = l2_scale(w.flags) * l2_scale(w.flags);
+        float nv[8];
+#pragma unroll
+        for (int sl = 0; sl < 8; ++sl) {
+          const int rb = sl >> 2, rloc = quarter * 32 + 16 * ((sl >> 1) & 1) + 8 * (sl & 1) + g8;
+          const int row = min((it.rbp * L2_RBK + rb) * L2_BLK + rloc, nblk * L2_BLK - 1);
+          nv[sl] = w.norms[(size_t)it.fq * nblk * L2_BLK + row];
+        }
+#pragma unroll
+        for (int sl = 0; sl < 8; ++sl) {
+          const int rb = sl >> 2, rloc = quarter * 32 + 16 * ((sl >> 1) & 1) + 8 * (sl & 1) + g8;
+          const int row = (it.rbp * L2_RBK + rb) * L2_BLK + rloc;
+          const uint32_t na = (rb < it.nrb && row < it.nq) ? (uint32_t)__float2int_rn(s2 * nv[sl]) : L2_PAD_NORM;
+          cadd8[sl] = (255u - (uint32_t)(rb * L2_BLK + rloc)) - ((na + L2_COL_OFFSET) << 8);
+        }
+      }
       for (int t = 0; t < it.ntile; ++t, ++g) {
         const int as = g & 1;
         mbar_wait(&S.tmem_full[as], (g >> 1) & 1);
         tc::fence_after_sync();
         const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + as * (L2_RBK * L2_BLK) + cq * 32;
-        uint32_t v0[32], v1[32];
         const int tcol = (it.t_lo + t) * 4 + cq;   // chunk number
+        if constexpr (FRAG) {
+          l2_frag_tile<ADDM>(S, w, it, st, cadd8, radd, cpend, tmem, as, quarter, cq, g8, j4, lane, t, tcol, mul, mul2,
+                             nblk, nrbp, dbg);
+          continue;
+        }
+        uint32_t v0[32], v1[32];
         if (dbg & 4) {
 #pragma unroll
           for (int c = 0; c < 32; ++c) v0[c] = v1[c] = L2_MAGIC_BITS;
@@ -786,20 +947,23 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   l2_norm_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
   l2_tile_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
   typedef void (*L2Kernel)(const int32_t*, const int32_t*, int, int, int, int, int, L2Ws);
-  static const L2Kernel kernels[6] = {
+  static const L2Kernel kernels[8] = {
       l2_top2_tc_kernel<L2_MODE_TOP1, false>, l2_top2_tc_kernel<L2_MODE_TOP2, false>,
-      l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, false>, l2_top2_tc_kernel<L2_MODE_TOP1, true>,
-      l2_top2_tc_kernel<L2_MODE_TOP2, true>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, true>};
+      l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, false>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX_FRAG, false>,
+      l2_top2_tc_kernel<L2_MODE_TOP1, true>, l2_top2_tc_kernel<L2_MODE_TOP2, true>,
+      l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, true>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX_FRAG, true>};
   static bool attr_set = false;
   const int smem = (int)sizeof(L2Smem) + 1024;
   if (!attr_set) {
-    for (int k = 0; k < 6; ++k)
+    for (int k = 0; k < 8; ++k)
       if (cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
           cudaSuccess)
         return check_launch("vo_match_l2_batch(smem attribute)");
     attr_set = true;
   }
-  const int addm = (g_l2_debug_host & 8) ? 3 : 0;
+  const int addm = (g_l2_debug_host & 8) ? 4 : 0;
+  // experimental: fragment-shaped TMEM loads (fewer instructions, measured 3 % slower: profiles/r1_summary.md)
+  const bool frag_layout = (g_l2_debug_host & 64) != 0;
   const bool two_pass_only = (g_l2_debug_host & 16) != 0;   // diagnostics: old mutual path
   {
     ProfScope prof(2, st);
@@ -818,7 +982,7 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
       // exact (integer) data: rows and columns ranked from ONE accumulator pass; anything else:
       // both directions + fp32 rerank.  The prep kernels decide on the device (flags[0]); the
       // launch that does not apply exits at once.
-      launch(L2_MODE_TOP1_COLMAX, 1, 0);
+      launch(frag_layout ? L2_MODE_TOP1_COLMAX_FRAG : L2_MODE_TOP1_COLMAX, 1, 0);
       launch(L2_MODE_TOP1, 2, 1);
     }
   }
