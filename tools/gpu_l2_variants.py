@@ -18,7 +18,7 @@ for N, B in [(2000, 200), (5000, 16)]:
     def run():
         _lib.check(lib.vo_match_l2_batch(_lib.ptr(desc), _lib.ptr(nkp), None, N, 128, F, _lib.ptr(pairs), B, 0, 0.0,
             _lib.ptr(q), _lib.ptr(t), _lib.ptr(dist), None, None, None, _lib.ptr(n_out), _lib.ptr(ws), wsb, _lib.cur_stream()))
-    for flags in (0, 1, 2, 3, 6, 7, 8, 64):   # 64 = fragment-layout epilogue (experimental)
+    for flags in (0, 1, 2, 3, 4, 5, 6, 7, 8, 64):   # 64 = fragment-layout epilogue (experimental)
         raw.vo_debug_l2(flags)
         for _ in range(2): run()
         torch.cuda.synchronize(); lib.vo_profile_enable(1)

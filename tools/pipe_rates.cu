@@ -25,6 +25,26 @@ __global__ void __launch_bounds__(1024) body(uint32_t* out, int iters, uint32_t 
       if (OP == 9) asm volatile("{.reg .pred p; setp.ne.u32 p, %2, 0; selp.b32 %0, %0, %1, p;}" : "+r"(a[k]) : "r"(b), "r"(c & 1));
       if (OP == 10) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b));
       if (OP == 11) { a[k] = __viaddmax_u32(a[k], b, c); asm volatile("" : "+r"(a[k])); }
+      // source-operand count: two register sources vs three
+      if (OP == 12) asm volatile("xor.b32 %0, %0, %1;" : "+r"(a[k]) : "r"(b));
+      if (OP == 13) asm volatile("mad.lo.u32 %0, %0, %1, 12345;" : "+r"(a[k]) : "r"(b));
+      if (OP == 14) asm volatile("mad.lo.u32 %0, %0, 129, %1;" : "+r"(a[k]) : "r"(c));
+      if (OP == 15) asm volatile("{.reg .pred p; setp.ne.u32 p, %1, 0; selp.b32 %0, %0, %1, p;}" : "+r"(a[k]) : "r"(b));
+      if (OP == 16) asm volatile("lop3.b32 %0, %0, %1, 0x0f0f0f0f, 0x96;" : "+r"(a[k]) : "r"(b));
+      if (OP == 17) {   // 1:1 mix of IMAD (3 sources) and a 2-source max
+        if (k & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[k]) : "r"(b), "r"(c));
+        else asm volatile("max.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b));
+      }
+      if (OP == 18) {   // 1:1 mix of IMAD and VIMNMX3 (both 3 sources)
+        if (k & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[k]) : "r"(b), "r"(c));
+        else { a[k] = __vimax3_u32(a[k], b, c); asm volatile("" : "+r"(a[k])); }
+      }
+      if (OP == 19) {   // 1:1 mix of IMAD with an immediate addend and a 2-source max
+        if (k & 1) asm volatile("mad.lo.u32 %0, %0, %1, 12345;" : "+r"(a[k]) : "r"(b));
+        else asm volatile("max.u32 %0, %0, %1;" : "+r"(a[k]) : "r"(b));
+      }
+      if (OP == 20) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+r"(a[k]) : "r"(b), "r"(c));
+      if (OP == 21) asm volatile("mad.lo.u32 %0, %0, %1, %0;" : "+r"(a[k]) : "r"(b));   // 3 sources, two of them the same register
     }
   }
   uint32_t s = 0;
@@ -71,5 +91,15 @@ int main() {
   run<6>("POPC", d, sms, ghz);
   run<7>("SHFL.BFLY", d, sms, ghz);
   run<8>("CREDUX.MAX", d, sms, ghz);
+  run<12>("XOR 2src", d, sms, ghz);
+  run<16>("LOP3 2src+imm", d, sms, ghz);
+  run<13>("IMAD r,r,imm", d, sms, ghz);
+  run<14>("IMAD r,imm,r", d, sms, ghz);
+  run<21>("IMAD r,r,same", d, sms, ghz);
+  run<20>("FFMA 3src", d, sms, ghz);
+  run<15>("SETP+SEL", d, sms, ghz);
+  run<17>("IMAD3+MAX2 mix", d, sms, ghz);
+  run<18>("IMAD3+MAX3 mix", d, sms, ghz);
+  run<19>("IMADimm+MAX2", d, sms, ghz);
   return 0;
 }
