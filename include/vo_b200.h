@@ -225,6 +225,36 @@ int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams, double* po
                      double* log_chi2, double* log_lambda, int32_t* log_trials, int* n_iterations,
                      double* chi2_initial, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- N4: ORB feature extraction (the detector handed to FrameGenerator, reference
+ * src/frame_generator.py:25 `detector.detectAndCompute(frame.image, None)`, src/visual_slam.py:16
+ * `cv2.ORB_create()`, src/image_and_keypoints.py:8) ----
+ * = cv2.ORB_create(nfeatures, scale_factor, nlevels, edge_threshold, 0, 2, HARRIS_SCORE, 31,
+ *   fast_threshold).detectAndCompute(gray, None) for a batch of equally sized 8-bit gray frames.
+ * images uint8 [n_frames, height, width] (width, height <= 4095);
+ * kp     float32 [n_frames, cap_out, 6] = (pt.x, pt.y, size, angle, response, octave);
+ * desc   uint8 [n_frames, cap_out, 32];  n_out int32 [n_frames];
+ * status int32 [n_frames]: 1 = more than cap_out key points survived (ties at a cut; rows beyond
+ *        cap_out dropped) - cap_out >= nfeatures + slack is the caller's choice.
+ * Key points are ordered by (octave, y, x); cv2 returns the same SET per octave in the order
+ * std::nth_element leaves.  vo_orb_level_info writes the pyramid geometry to HOST arrays
+ * [nlevels] (any may be NULL). */
+size_t vo_orb_workspace_bytes(int n_frames, int width, int height, int nfeatures,
+                              float scale_factor, int nlevels, int cap_out);
+int vo_orb_level_info(int width, int height, int nfeatures, float scale_factor, int nlevels,
+                      int32_t* w_h, int32_t* h_h, int32_t* nfeat_h, float* scale_h);
+int vo_orb_detect_batch(const uint8_t* images, int n_frames, int width, int height, int nfeatures,
+                        float scale_factor, int nlevels, int edge_threshold, int fast_threshold,
+                        int cap_out, float* kp, uint8_t* desc, int32_t* n_out, int32_t* status,
+                        void* ws, size_t ws_bytes, void* stream);
+/* FAST stage alone on level 0 (parity hook): scores uint8 [n_frames,height,width] = response + 1
+ * of cv2.FastFeatureDetector(threshold, nonmaxSuppression) before suppression (0 = no corner);
+ * corners uint32 [n_frames, (width/2+1)*(height/2+1)] = y << 20 | x << 8 | (response + 1) of the
+ * corners that survive suppression and the border filter, unordered; n_corners int32 [n_frames];
+ * hist int32 [n_frames,256] histogram of their scores. */
+int vo_orb_fast_score_map(const uint8_t* images, int n_frames, int width, int height,
+                          int fast_threshold, int edge_threshold, uint8_t* scores,
+                          uint32_t* corners, int32_t* n_corners, int32_t* hist, void* stream);
+
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).

@@ -73,6 +73,10 @@ SIGNATURES = {
     "vo_bundle_adjust_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_bundle_adjust": (_i, [_p, _p, _i, _p, _i, _p, _p, _p, _i, _d, _d, _d, _d, _i, _p, _p, _p, _p,
                               _p, _p, _sz, _p]),
+    "vo_orb_workspace_bytes": (_sz, [_i, _i, _i, _i, _f, _i, _i]),
+    "vo_orb_level_info": (_i, [_i, _i, _i, _f, _i, _p, _p, _p, _p]),
+    "vo_orb_detect_batch": (_i, [_p, _i, _i, _i, _i, _f, _i, _i, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
+    "vo_orb_fast_score_map": (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "vo_map_prune_workspace_bytes": (_sz, [_i]),
     "vo_map_prune_observations": (_i, [_p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
 }

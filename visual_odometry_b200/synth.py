@@ -157,3 +157,27 @@ def make_sequence(n_frames, n_kp, seed, inlier_ratio=0.7, noise_px=0.5, descript
 def make_pair(n_kp, seed, **kw):
     """One frame pair (config C1): a 2-frame sequence."""
     return make_sequence(2, n_kp, seed, **kw)
+
+
+def textured_image(height, width, seed, n_shapes=None):
+    """Synthetic gray image with corners for the ORB front end (N4): random filled rectangles and
+    discs on a mid-gray ground, 3x3 box smoothing, Gaussian pixel noise.  numpy only, so the GPU
+    box regenerates exactly the image the golden fixtures were made from."""
+    rng = np.random.default_rng(seed)
+    img = np.full((height, width), 110.0, np.float32)
+    n_shapes = n_shapes if n_shapes is not None else height * width // 1200
+    yy, xx = np.mgrid[0:64, 0:64]
+    for _ in range(n_shapes):
+        x, y = int(rng.integers(0, width)), int(rng.integers(0, height))
+        w, h = int(rng.integers(6, 60)), int(rng.integers(6, 60))
+        c = float(rng.integers(20, 236))
+        x1, y1 = min(x + w, width), min(y + h, height)
+        if rng.random() < 0.5:
+            img[y:y1, x:x1] = c
+        else:
+            m = ((xx[:y1 - y, :x1 - x] - w / 2) ** 2 / (w / 2) ** 2 + (yy[:y1 - y, :x1 - x] - h / 2) ** 2 / (h / 2) ** 2) <= 1
+            img[y:y1, x:x1][m] = c
+    p = np.pad(img, 1, mode="edge")
+    img = sum(p[dy:dy + height, dx:dx + width] for dy in range(3) for dx in range(3)) / 9.0
+    img = img + rng.normal(0, 2.5, img.shape).astype(np.float32)
+    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
