@@ -37,7 +37,7 @@ constexpr int ORB_BR = 20;                      // radius of the blurred patch (
 constexpr int ORB_SR = ORB_BR + 3;              // radius of the source patch
 constexpr int ORB_SW = 2 * ORB_SR + 1;          // 47
 constexpr int ORB_BW = 2 * ORB_BR + 1;          // 41
-constexpr int FAST_TW = 64, FAST_TH = 16;       // NMS tile; scores for a 66x18 ring, source 72x24
+constexpr int FAST_TW = 126, FAST_TH = 30;      // NMS tile; scores for a 128x32 ring, source 134x38
 
 struct OrbLevel {
   int w, h;             // level size
@@ -115,91 +115,136 @@ __device__ __forceinline__ const uint8_t* orb_level_ptr(const OrbGeom& g, int l,
 
 // ------------------------------------------------------------------ FAST-9/16 + NMS
 // Circle of radius 3, clockwise from (0, 3); (dx, dy)
-__device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch, int thr) {
+__device__ __forceinline__ void fast_circle(const uint8_t* c, int pitch, int (&d)[16]) {
   const int v = c[0];
-  int d[16];
   d[0] = v - c[3 * pitch];          d[1] = v - c[3 * pitch + 1];   d[2] = v - c[2 * pitch + 2];
   d[3] = v - c[pitch + 3];          d[4] = v - c[3];               d[5] = v - c[-pitch + 3];
   d[6] = v - c[-2 * pitch + 2];     d[7] = v - c[-3 * pitch + 1];  d[8] = v - c[-3 * pitch];
   d[9] = v - c[-3 * pitch - 1];     d[10] = v - c[-2 * pitch - 2]; d[11] = v - c[-pitch - 3];
   d[12] = v - c[-3];                d[13] = v - c[pitch - 3];      d[14] = v - c[2 * pitch - 2];
   d[15] = v - c[3 * pitch - 1];
+}
+// corner at threshold t: 9 contiguous circle pixels all darker than v - t or all brighter than v + t
+__device__ __forceinline__ bool fast_corner(const int (&d)[16], int t) {
+  uint32_t mb = 0, md = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    mb |= (uint32_t)(d[k] > t) << k;
+    md |= (uint32_t)(d[k] < -t) << k;
+  }
   // a circular run of >= 9 set bits in a 16-bit mask
   auto run9 = [](uint32_t m) {
     const uint32_t x = m | (m << 16);
     const uint32_t r2 = x & (x >> 1), r4 = r2 & (r2 >> 2), r8 = r4 & (r4 >> 4);
     return (r8 & (x >> 8) & 0xffffu) != 0u;
   };
-  // corner at threshold t: 9 contiguous circle pixels all darker than v - t or brighter than v + t
-  auto corner = [&](int t) {
-    uint32_t mb = 0, md = 0;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      mb |= (uint32_t)(d[k] > t) << k;
-      md |= (uint32_t)(d[k] < -t) << k;
-    }
-    return run9(mb) || run9(md);
-  };
-  if (!corner(thr)) return 0;
-  // score + 1 = max over the 16 arcs of min |d| = the largest t + 1 at which it still is a corner
-  // (the test is monotone in t): bisection over [thr, 255]
+  return run9(mb) || run9(md);
+}
+// score + 1 = max over the 16 arcs of min |d| = the largest t + 1 at which the pixel still is a
+// corner (the test is monotone in t): bisection over [thr, 255].  (A direct min / max tree over
+// the arcs compiled to code that returned wrong values on the B200 although its PTX read
+// correctly; the run test is what the detection itself uses, so score and detection cannot
+// disagree.)
+__device__ __forceinline__ int fast_raw_score(const int (&d)[16], int thr) {
   int lo_t = thr, hi_t = 255;
   while (hi_t - lo_t > 1) {
     const int mid = (lo_t + hi_t) >> 1;
-    if (corner(mid)) lo_t = mid; else hi_t = mid;
+    if (fast_corner(d, mid)) lo_t = mid; else hi_t = mid;
   }
-  const int best = lo_t + 1;
-  return best;   // > thr for a corner; cv2's response is best - 1
+  return lo_t + 1;   // > thr for a corner; cv2's response is this - 1
 }
 
-// corner word: y << 20 | x << 8 | raw score (so unsigned order = (y, x) order)
+// corner word: y << 20 | x << 8 | raw score (so unsigned order = (y, x) order).
+// Tile = 126 x 30 pixels: the score ring (tile + 1) is 128 x 32 = 4 lane strides x 4 rows per
+// warp, the source tile (ring + 3) 134 x 38 bytes.  Loops are (row per warp, column per lane):
+// no index divisions, bounds tests hoisted per row.
 __global__ void __launch_bounds__(256)
 orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint8_t* __restrict__ pyr,
                 uint32_t* __restrict__ list1, int32_t* __restrict__ cnt1, int32_t* __restrict__ hist,
                 uint8_t* __restrict__ score_map) {
-  constexpr int SP = FAST_TW + 8, SH = FAST_TH + 8;   // source tile 72 x 24
-  constexpr int CP = FAST_TW + 2, CH = FAST_TH + 2;   // score tile 66 x 18
+  constexpr int SP = FAST_TW + 8 + 2, SH = FAST_TH + 8;   // source tile 134 (+2 pad) x 38
+  constexpr int CP = FAST_TW + 2, CH = FAST_TH + 2;       // score ring 128 x 32
   __shared__ uint8_t s_src[SH][SP];
-  __shared__ uint8_t s_sc[CH][CP + 2];
-  __shared__ uint32_t s_out[FAST_TW * FAST_TH / 4 + 32];
-  __shared__ int s_n, s_base;
+  __shared__ uint8_t s_sc[CH][CP + 4];
+  __shared__ uint16_t s_cand[CH * CP];
+  __shared__ uint32_t s_out[(FAST_TW / 2 + 1) * (FAST_TH / 2 + 1)];
+  __shared__ int s_n, s_base, s_nc;
   const OrbLevel L = g.lv[l];
   const int f = blockIdx.z;
   const uint8_t* img = orb_level_ptr(g, l, f, images, pyr);
   const int tx0 = blockIdx.x * FAST_TW, ty0 = blockIdx.y * FAST_TH;
-  if (threadIdx.x == 0) s_n = 0;
-  for (int i = threadIdx.x; i < SH * SP; i += 256) {
-    const int sy = i / SP, sx = i - sy * SP;
-    const int y = ty0 - 4 + sy, x = tx0 - 4 + sx;
-    s_src[sy][sx] = (x >= 0 && x < L.w && y >= 0 && y < L.h) ? __ldg(img + (size_t)y * L.w + x) : 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { s_n = 0; s_nc = 0; }
+  for (int sy = warp; sy < SH; sy += 8) {
+    const int y = ty0 - 4 + sy;
+    const bool yok = y >= 0 && y < L.h;
+    const uint8_t* row = img + (size_t)(yok ? y : 0) * L.w;
+#pragma unroll
+    for (int sx = lane; sx < FAST_TW + 8; sx += 32) {
+      const int x = tx0 - 4 + sx;
+      s_src[sy][sx] = (yok && x >= 0 && x < L.w) ? __ldg(row + x) : (uint8_t)0;
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < CH * CP; i += 256) {
+  // pass 1: corner test over the ring (uniform work); the few corners go to a list
+  const int t = g.fast_thr;
+  const uint32_t t2 = 2u * (uint32_t)t;
+  for (int cy = warp; cy < CH; cy += 8) {
+    const int y = ty0 - 1 + cy;
+    const bool yok = y >= 3 && y < L.h - 3;
+#pragma unroll
+    for (int cx = lane; cx < CP; cx += 32) {
+      const int x = tx0 - 1 + cx;
+      s_sc[cy][cx] = 0;
+      if (!(yok && x >= 3 && x < L.w - 3)) continue;
+      // any 9 contiguous circle pixels contain one pixel of each opposite pair: flat regions
+      // (whole warps) leave after 5 loads.  |d| > t  <=>  (unsigned)(d + t) > 2 t
+      const uint8_t* c = &s_src[cy + 3][cx + 3];
+      const int v = c[0] + t;
+      const bool a0 = (uint32_t)(v - c[3 * SP]) > t2, a8 = (uint32_t)(v - c[-3 * SP]) > t2;
+      const bool a4 = (uint32_t)(v - c[3]) > t2, a12 = (uint32_t)(v - c[-3]) > t2;
+      if (!((a0 || a8) && (a4 || a12))) continue;
+      int d[16];
+      fast_circle(c, SP, d);
+      if (fast_corner(d, t)) s_cand[atomicAdd(&s_nc, 1)] = (uint16_t)(cy * CP + cx);
+    }
+  }
+  __syncthreads();
+  // pass 2: scores of the corners only (about 1.5 % of the pixels), all lanes busy
+  for (int k = threadIdx.x; k < s_nc; k += 256) {
+    const int i = s_cand[k];
     const int cy = i / CP, cx = i - cy * CP;
-    const int y = ty0 - 1 + cy, x = tx0 - 1 + cx;
-    int raw = 0;
-    if (x >= 3 && x < L.w - 3 && y >= 3 && y < L.h - 3)
-      raw = fast_raw_score(&s_src[cy + 3][cx + 3], SP, g.fast_thr);
-    s_sc[cy][cx] = (uint8_t)raw;
-    // test hook (vo_orb_fast_score_map): cv2's response is raw - 1, 0 = not a corner
-    if (score_map && cy >= 1 && cy <= FAST_TH && cx >= 1 && cx <= FAST_TW && x < L.w && y < L.h)
-      score_map[((size_t)f * L.h + y) * L.w + x] = (uint8_t)raw;
+    int d[16];
+    fast_circle(&s_src[cy + 3][cx + 3], SP, d);
+    s_sc[cy][cx] = (uint8_t)fast_raw_score(d, t);
   }
   __syncthreads();
+  // test hook (vo_orb_fast_score_map): cv2's response is raw - 1, 0 = not a corner
+  if (score_map) {
+    for (int py = warp; py < FAST_TH; py += 8)
+      for (int px = lane; px < FAST_TW; px += 32)
+        if (tx0 + px < L.w && ty0 + py < L.h)
+          score_map[((size_t)f * L.h + ty0 + py) * L.w + tx0 + px] = s_sc[py + 1][px + 1];
+  }
+  // pass 3: strict 3x3 maxima inside the border
   const bool border_ok = !(g.edge > 0 && (L.h <= 2 * g.edge || L.w <= 2 * g.edge));
-  for (int i = threadIdx.x; i < FAST_TW * FAST_TH; i += 256) {
-    const int py = i / FAST_TW, px = i - py * FAST_TW;
-    const int y = ty0 + py, x = tx0 + px;
-    const int s = s_sc[py + 1][px + 1];
-    if (s == 0 || !border_ok) continue;
-    if (x < g.edge || x >= L.w - g.edge || y < g.edge || y >= L.h - g.edge) continue;
-    const bool is_max = s > s_sc[py][px] && s > s_sc[py][px + 1] && s > s_sc[py][px + 2] &&
-                        s > s_sc[py + 1][px] && s > s_sc[py + 1][px + 2] && s > s_sc[py + 2][px] &&
-                        s > s_sc[py + 2][px + 1] && s > s_sc[py + 2][px + 2];
-    if (!is_max) continue;
-    const int k = atomicAdd(&s_n, 1);
-    s_out[k] = ((uint32_t)y << 20) | ((uint32_t)x << 8) | (uint32_t)s;
-    atomicAdd(&hist[((size_t)f * g.nlevels + l) * 256 + s], 1);
+  for (int py = warp; py < FAST_TH; py += 8) {
+    const int y = ty0 + py;
+    if (!border_ok || y < g.edge || y >= L.h - g.edge) continue;
+#pragma unroll
+    for (int px = lane; px < FAST_TW; px += 32) {
+      const int x = tx0 + px;
+      const int s = s_sc[py + 1][px + 1];
+      if (s == 0) continue;
+      if (x < g.edge || x >= L.w - g.edge) continue;
+      const bool is_max = s > s_sc[py][px] && s > s_sc[py][px + 1] && s > s_sc[py][px + 2] &&
+                          s > s_sc[py + 1][px] && s > s_sc[py + 1][px + 2] && s > s_sc[py + 2][px] &&
+                          s > s_sc[py + 2][px + 1] && s > s_sc[py + 2][px + 2];
+      if (!is_max) continue;
+      const int k = atomicAdd(&s_n, 1);
+      s_out[k] = ((uint32_t)y << 20) | ((uint32_t)x << 8) | (uint32_t)s;
+      atomicAdd(&hist[((size_t)f * g.nlevels + l) * 256 + s], 1);
+    }
   }
   __syncthreads();
   if (s_n == 0) return;
