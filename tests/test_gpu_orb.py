@@ -113,3 +113,32 @@ def test_detect_and_compute_drop_in(cuda_dev):
     assert np.array_equal(mine, ref[o])
     assert np.array_equal(frame.descriptors, d[o])
     assert frame.features[3].feature_id == (0, 3)
+
+
+def test_images_to_matches_through_the_reference_surface(cuda_dev):
+    """Two overlapping views -> FrameGenerator(OrbDetector) -> ImagePair.match_features with the
+    B200 matcher: the same matches (as point pairs with distances) as cv2.ORB_create +
+    cv2.BFMatcher(NORM_HAMMING, crossCheck=True) on the same images (reference
+    src/visual_slam.py:16-18,294; src/image_pair.py:233-258).  Index-based tie-breaks can differ
+    because cv2 leaves an octave's key points in std::nth_element order."""
+    cv2 = pytest.importorskip("cv2")
+    from visual_odometry_b200.image_pair import ImagePair
+    from visual_odometry_b200.matcher import B200Matcher, NORM_HAMMING
+    big = synth.textured_image(700, 900, 70)
+    img1, img2 = np.ascontiguousarray(big[60:540, 80:720]), np.ascontiguousarray(big[71:551, 97:737])
+    K = np.array([[700.0, 0, 320], [0, 700.0, 240], [0, 0, 1]])
+    gen = FrameGenerator(OrbDetector(nfeatures=800))
+    f1, f2 = gen.make_frame(img1), gen.make_frame(img2)
+    pair = ImagePair(f1, f2, B200Matcher(NORM_HAMMING, crossCheck=True), K)
+    pair.match_features()
+    mine = {(m.keypoint1, m.keypoint2, float(m.distance)) for m in pair.filtered_matches}
+    orb = cv2.ORB_create(nfeatures=800)
+    k1, d1 = orb.detectAndCompute(img1, None)
+    k2, d2 = orb.detectAndCompute(img2, None)
+    ref = {(k1[m.queryIdx].pt, k2[m.trainIdx].pt, float(m.distance))
+           for m in cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True).match(d1, d2)}
+    assert len(ref) > 300
+    assert len(mine & ref) >= 0.995 * len(ref) and abs(len(mine) - len(ref)) <= 0.005 * len(ref) + 1
+    # most of them are the true shift (17, 11) of the second crop
+    shift = np.array([np.subtract(a, b) for a, b, _ in mine])
+    assert (np.abs(shift - [17, 11]).max(1) < 2.0).mean() > 0.5

@@ -166,15 +166,15 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
   constexpr int CP = FAST_TW + 2, CH = FAST_TH + 2;       // score ring 128 x 32
   __shared__ uint8_t s_src[SH][SP];
   __shared__ uint8_t s_sc[CH][CP + 4];
-  __shared__ uint16_t s_cand[CH * CP];
+  __shared__ uint16_t s_cand[CH * CP], s_corner[CH * CP];
   __shared__ uint32_t s_out[(FAST_TW / 2 + 1) * (FAST_TH / 2 + 1)];
-  __shared__ int s_n, s_base, s_nc;
+  __shared__ int s_n, s_base, s_nc, s_nk;
   const OrbLevel L = g.lv[l];
   const int f = blockIdx.z;
   const uint8_t* img = orb_level_ptr(g, l, f, images, pyr);
   const int tx0 = blockIdx.x * FAST_TW, ty0 = blockIdx.y * FAST_TH;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) { s_n = 0; s_nc = 0; }
+  if (threadIdx.x == 0) { s_n = 0; s_nc = 0; s_nk = 0; }
   for (int sy = warp; sy < SH; sy += 8) {
     const int y = ty0 - 4 + sy;
     const bool yok = y >= 0 && y < L.h;
@@ -186,9 +186,10 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
     }
   }
   __syncthreads();
-  // pass 1: corner test over the ring (uniform work); the few corners go to a list
+  // pass 1a: cheap necessary condition over the ring; survivors go to a list so that the full
+  // test below runs with all lanes busy.  Nine contiguous circle pixels contain four cyclically
+  // consecutive ones of the eight even-numbered pixels: test that on |d| > t masks of each sign.
   const int t = g.fast_thr;
-  const uint32_t t2 = 2u * (uint32_t)t;
   for (int cy = warp; cy < CH; cy += 8) {
     const int y = ty0 - 1 + cy;
     const bool yok = y >= 3 && y < L.h - 3;
@@ -197,22 +198,41 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
       const int x = tx0 - 1 + cx;
       s_sc[cy][cx] = 0;
       if (!(yok && x >= 3 && x < L.w - 3)) continue;
-      // any 9 contiguous circle pixels contain one pixel of each opposite pair: flat regions
-      // (whole warps) leave after 5 loads.  |d| > t  <=>  (unsigned)(d + t) > 2 t
       const uint8_t* c = &s_src[cy + 3][cx + 3];
-      const int v = c[0] + t;
-      const bool a0 = (uint32_t)(v - c[3 * SP]) > t2, a8 = (uint32_t)(v - c[-3 * SP]) > t2;
-      const bool a4 = (uint32_t)(v - c[3]) > t2, a12 = (uint32_t)(v - c[-3]) > t2;
-      if (!((a0 || a8) && (a4 || a12))) continue;
-      int d[16];
-      fast_circle(c, SP, d);
-      if (fast_corner(d, t)) s_cand[atomicAdd(&s_nc, 1)] = (uint16_t)(cy * CP + cx);
+      const int hi = c[0] + t, lo = c[0] - t;
+      // opposite pairs first: flat regions (whole warps) leave after 5 loads
+      const int p0 = c[3 * SP], p8 = c[-3 * SP], p4 = c[3], p12 = c[-3];
+      const bool v_any = p0 > hi || p0 < lo || p8 > hi || p8 < lo;
+      const bool h_any = p4 > hi || p4 < lo || p12 > hi || p12 < lo;
+      if (!(v_any && h_any)) continue;
+      const int p2 = c[2 * SP + 2], p6 = c[-2 * SP + 2], p10 = c[-2 * SP - 2], p14 = c[2 * SP - 2];
+      const uint32_t mb = (uint32_t)(p0 < lo) | (uint32_t)(p2 < lo) << 1 | (uint32_t)(p4 < lo) << 2 |
+                          (uint32_t)(p6 < lo) << 3 | (uint32_t)(p8 < lo) << 4 | (uint32_t)(p10 < lo) << 5 |
+                          (uint32_t)(p12 < lo) << 6 | (uint32_t)(p14 < lo) << 7;
+      const uint32_t md = (uint32_t)(p0 > hi) | (uint32_t)(p2 > hi) << 1 | (uint32_t)(p4 > hi) << 2 |
+                          (uint32_t)(p6 > hi) << 3 | (uint32_t)(p8 > hi) << 4 | (uint32_t)(p10 > hi) << 5 |
+                          (uint32_t)(p12 > hi) << 6 | (uint32_t)(p14 > hi) << 7;
+      auto run4 = [](uint32_t m) {
+        const uint32_t x8 = m | (m << 8);
+        const uint32_t r2 = x8 & (x8 >> 1);
+        return (r2 & (r2 >> 2) & 0xffu) != 0u;
+      };
+      if (run4(mb) || run4(md)) s_cand[atomicAdd(&s_nc, 1)] = (uint16_t)(cy * CP + cx);
     }
   }
   __syncthreads();
-  // pass 2: scores of the corners only (about 1.5 % of the pixels), all lanes busy
+  // pass 1b: the full run-of-9 test on the listed pixels; corners go to a second list
   for (int k = threadIdx.x; k < s_nc; k += 256) {
     const int i = s_cand[k];
+    const int cy = i / CP, cx = i - cy * CP;
+    int d[16];
+    fast_circle(&s_src[cy + 3][cx + 3], SP, d);
+    if (fast_corner(d, t)) s_corner[atomicAdd(&s_nk, 1)] = (uint16_t)i;
+  }
+  __syncthreads();
+  // pass 2: scores of the corners only (about 1.5 % of the pixels)
+  for (int k = threadIdx.x; k < s_nk; k += 256) {
+    const int i = s_corner[k];
     const int cy = i / CP, cx = i - cy * CP;
     int d[16];
     fast_circle(&s_src[cy + 3][cx + 3], SP, d);
@@ -420,7 +440,8 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
                     float* __restrict__ kp, const int32_t* __restrict__ kp_level_xy,
                     const int32_t* __restrict__ n_out, uint8_t* __restrict__ desc) {
   __shared__ uint8_t s_src[ORB_SW][ORB_SW + 1];
-  __shared__ float s_row[ORB_SW][ORB_BW];
+  __shared__ float s_srcf[ORB_SW][ORB_SW + 2];
+  __shared__ float s_row[ORB_SW][ORB_BW + 2];
   __shared__ uint8_t s_blur[ORB_BW][ORB_BW + 3];
   __shared__ float s_ab[2];
   const int f = blockIdx.y, i = blockIdx.x;
@@ -430,10 +451,18 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
   const OrbLevel L = g.lv[l];
   const int x0 = kp_level_xy[((size_t)f * g.cap_out + i) * 2], y0 = kp_level_xy[((size_t)f * g.cap_out + i) * 2 + 1];
   const uint8_t* img = orb_level_ptr(g, l, f, images, pyr);
-  for (int t = threadIdx.x; t < ORB_SW * ORB_SW; t += 256) {
-    const int sy = t / ORB_SW, sx = t - sy * ORB_SW;
-    const int y = orb_reflect101(y0 - ORB_SR + sy, L.h), x = orb_reflect101(x0 - ORB_SR + sx, L.w);
-    s_src[sy][sx] = __ldg(img + (size_t)y * L.w + x);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool inside = x0 >= ORB_SR && x0 + ORB_SR < L.w && y0 >= ORB_SR && y0 + ORB_SR < L.h;
+  for (int sy = warp; sy < ORB_SW; sy += 8) {
+    const int y = inside ? y0 - ORB_SR + sy : orb_reflect101(y0 - ORB_SR + sy, L.h);
+    const uint8_t* row = img + (size_t)y * L.w;
+#pragma unroll
+    for (int sx = lane; sx < ORB_SW; sx += 32) {
+      const int x = inside ? x0 - ORB_SR + sx : orb_reflect101(x0 - ORB_SR + sx, L.w);
+      const uint8_t p = __ldg(row + x);
+      s_src[sy][sx] = p;
+      s_srcf[sy][sx] = (float)p;
+    }
   }
   __syncthreads();
   // --- orientation: warp 0, lane = row of the disc (31 rows)
@@ -461,25 +490,38 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
       s_ab[1] = (float)sin((double)rad);
     }
   }
-  // --- blur, row pass: k0 p0, then fused multiply-adds in tap order
-  for (int t = threadIdx.x; t < ORB_SW * ORB_BW; t += 256) {
-    const int sy = t / ORB_BW, bx = t - sy * ORB_BW;
-    const uint8_t* p = &s_src[sy][bx];            // taps bx .. bx+6 (centre bx+3)
-    float h = __fmul_rn(c_orb_taps[0], (float)p[0]);
+  // --- blur, row pass: k0 p0, then fused multiply-adds in tap order.  A thread owns 11
+  // consecutive outputs of one row (47 rows x 4 runs = 188 tasks): 17 loads feed 77 multiply-adds
+  if (threadIdx.x < ORB_SW * 4) {
+    const int sy = threadIdx.x >> 2, b0 = (threadIdx.x & 3) * 11;
+    float p[17];
 #pragma unroll
-    for (int k = 1; k < 7; ++k) h = __fmaf_rn((float)p[k], c_orb_taps[k], h);
-    s_row[sy][bx] = h;
+    for (int k = 0; k < 17; ++k) p[k] = (b0 + k < ORB_SW) ? s_srcf[sy][b0 + k] : 0.f;
+#pragma unroll
+    for (int o = 0; o < 11; ++o) {
+      float h = __fmul_rn(c_orb_taps[0], p[o]);
+#pragma unroll
+      for (int k = 1; k < 7; ++k) h = __fmaf_rn(p[o + k], c_orb_taps[k], h);
+      if (b0 + o < ORB_BW) s_row[sy][b0 + o] = h;
+    }
   }
   __syncthreads();
-  // --- column pass, symmetric form, round half to even, saturate
-  for (int t = threadIdx.x; t < ORB_BW * ORB_BW; t += 256) {
-    const int by = t / ORB_BW, bx = t - by * ORB_BW;
-    float v = __fmul_rn(c_orb_taps[3], s_row[by + 3][bx]);
+  // --- column pass, symmetric form, round half to even, saturate.  A thread owns 7 consecutive
+  // rows of one column (41 columns x 6 runs = 246 tasks)
+  if (threadIdx.x < ORB_BW * 6) {
+    const int run = threadIdx.x / ORB_BW, bx = threadIdx.x - run * ORB_BW, r0 = run * 7;
+    float hcol[13];
 #pragma unroll
-    for (int k = 1; k <= 3; ++k)
-      v = __fmaf_rn(__fadd_rn(s_row[by + 3 + k][bx], s_row[by + 3 - k][bx]), c_orb_taps[3 + k], v);
-    const int q = __float2int_rn(v);
-    s_blur[by][bx] = (uint8_t)min(max(q, 0), 255);
+    for (int k = 0; k < 13; ++k) hcol[k] = (r0 + k < ORB_SW) ? s_row[r0 + k][bx] : 0.f;
+#pragma unroll
+    for (int o = 0; o < 7; ++o) {
+      float v = __fmul_rn(c_orb_taps[3], hcol[o + 3]);
+#pragma unroll
+      for (int k = 1; k <= 3; ++k)
+        v = __fmaf_rn(__fadd_rn(hcol[o + 3 + k], hcol[o + 3 - k]), c_orb_taps[3 + k], v);
+      const int q = __float2int_rn(v);
+      if (r0 + o < ORB_BW) s_blur[r0 + o][bx] = (uint8_t)min(max(q, 0), 255);
+    }
   }
   __syncthreads();
   // --- 256 comparisons
