@@ -142,3 +142,68 @@ def test_images_to_matches_through_the_reference_surface(cuda_dev):
     # most of them are the true shift (17, 11) of the second crop
     shift = np.array([np.subtract(a, b) for a, b, _ in mine])
     assert (np.abs(shift - [17, 11]).max(1) < 2.0).mean() > 0.5
+
+
+def _render_two_plane_sequence(n_frames, W=640, H=480):
+    """A far textured plane (Z = 14) with two nearer ones (Z = 8, Z = 5) in front of parts of it, seen by a
+    camera that translates and yaws a little per frame; views rendered with cv2.warpPerspective.
+    -> (images u8 [F,H,W], K, list of (R_k, C_k))."""
+    import cv2
+    K = np.array([[700.0, 0, W / 2], [0, 700.0, H / 2], [0, 0, 1]])
+    far, mid, near = (synth.textured_image(1600, 2200, 81), synth.textured_image(520, 520, 82),
+                      synth.textured_image(400, 400, 83))
+    planes = [(far, 0.014, 1100, 800, 14.0, 0.0, 0.0), (mid, 0.007, 260, 260, 8.0, -1.6, 0.4),
+              (near, 0.005, 200, 200, 5.0, 1.3, -0.5)]
+    images, cams = [], []
+    for k in range(n_frames):
+        yaw = 0.012 * k
+        R = np.array([[np.cos(yaw), 0, np.sin(yaw)], [0, 1, 0], [-np.sin(yaw), 0, np.cos(yaw)]])
+        C = np.array([0.35 * k, 0.05 * k, 0.08 * k])
+        t = -R @ C
+        img = None
+        for tex, s, cx, cy, Z0, ox, oy in planes:
+            M = np.array([[s, 0, -cx * s + ox], [0, s, -cy * s + oy], [0, 0, Z0]])
+            Hm = K @ (R @ M + np.outer(t, [0, 0, 1.0]))
+            layer = cv2.warpPerspective(tex, Hm, (W, H), flags=cv2.INTER_LINEAR)
+            cover = cv2.warpPerspective(np.full_like(tex, 255), Hm, (W, H), flags=cv2.INTER_NEAREST) > 0
+            img = layer if img is None else np.where(cover, layer, img)
+        images.append(img)
+        cams.append((R, C))
+    return np.stack(images), K, cams
+
+
+def test_image_sequence_to_poses_on_the_device(cuda_dev):
+    """Images -> ORB extraction -> Hamming matching -> E-RANSAC -> recoverPose without leaving the
+    device (PairPipeline.run_images); the relative poses follow the ground truth of the rendered
+    sequence, and so does cv2's own chain on the same images."""
+    cv2 = pytest.importorskip("cv2")
+    from visual_odometry_b200.pipeline import PairPipeline
+    images, K, cams = _render_two_plane_sequence(5)
+    pipe = PairPipeline(1500, 4, 5, K=K, device="cuda:0")
+    b = pipe.run_images(images, OrbDetector(nfeatures=1200))
+    torch.cuda.synchronize()
+    assert b == 4
+    Rg, tg = pipe.R[:b].cpu().numpy().reshape(b, 3, 3), pipe.t[:b].cpu().numpy().reshape(b, 3)
+    n_inl = pipe.n_inl[:b].cpu().numpy()
+    orb, bf = cv2.ORB_create(nfeatures=1200), cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)
+    for k in range(b):
+        (R1, C1), (R2, C2) = cams[k], cams[k + 1]
+        R_true = R2 @ R1.T
+        t_true = R2 @ (C1 - C2)
+        t_true /= np.linalg.norm(t_true)
+        ang = np.degrees(np.arccos(np.clip((np.trace(Rg[k].T @ R_true) - 1) / 2, -1, 1)))
+        tdir = np.degrees(np.arccos(np.clip(tg[k] @ t_true, -1, 1)))
+        assert n_inl[k] > 150, (k, n_inl[k])
+        # (1 px RANSAC without a refit on ORB's integer pyramid coordinates: cv2's own chain is
+        # within 1-3 degrees / 3-12 degrees of the truth on this scene)
+        assert ang < 4.0 and tdir < 20.0, (k, ang, tdir)
+        # cv2's own chain on the same two images lands on the same motion
+        k1, d1 = orb.detectAndCompute(images[k], None)
+        k2, d2 = orb.detectAndCompute(images[k + 1], None)
+        m = bf.match(d1, d2)
+        assert abs(len(m) - int(pipe.n_match[k].item())) <= 0.01 * len(m) + 2
+        p1 = np.float64([k1[x.queryIdx].pt for x in m]); p2 = np.float64([k2[x.trainIdx].pt for x in m])
+        E, mask = cv2.findEssentialMat(p1, p2, K, cv2.FM_RANSAC, 0.99, 1)
+        _, Rc, tc, _ = cv2.recoverPose(E, p1[mask.ravel() == 1], p2[mask.ravel() == 1], K)
+        ang_c = np.degrees(np.arccos(np.clip((np.trace(Rg[k].T @ Rc) - 1) / 2, -1, 1)))
+        assert ang_c < 5.0, (k, ang_c)

@@ -103,6 +103,34 @@ class PairPipeline:
         if self.do_chain if chain is None else chain:
             _lib.check(lib.vo_chain_poses(g(self.R), g(self.t), a + B, None, g(self.poses), st))
 
+    # ------------------------------------------------------------------ images in (N4 front end)
+    def run_images(self, images, detector, pairs=None):
+        """Frames as IMAGES: ORB extraction (orb.OrbDetector.detect_batch, csrc/orb.cu) writes
+        descriptors and key points straight into this pipeline's frame arrays on the device, then
+        the hot path runs on `pairs` (default: consecutive frames).  What the reference does per
+        frame in FrameGenerator.make_frame + match_current_and_previous_frame
+        (src/frame_generator.py:10-38, src/visual_slam.py:286-307), for a whole sequence without a
+        host round trip.  Returns the number of pairs; results are in the attributes."""
+        if self.descriptor != "orb":
+            raise ValueError("run_images: the GPU front end extracts ORB features")
+        out = detector.detect_batch(images, cap=self.n_cap)
+        f = int(out["n"].shape[0])
+        if f > self.F:
+            raise ValueError("run_images: more frames than max_frames")
+        self.desc[:f].copy_(out["desc"])
+        self.kp[:f].copy_(out["kp"][:, :, :2])
+        self.nkp[:f].copy_(out["n"])
+        if pairs is None:
+            pairs = np.stack([np.arange(f - 1), np.arange(1, f)], 1)
+        pairs = torch.as_tensor(np.ascontiguousarray(pairs, np.int32))
+        b = int(pairs.shape[0])
+        self.pairs[:b].copy_(pairs)
+        self.run_device(b)
+        if int(out["status"].max().item()) != 0:
+            raise _lib.VoError(_lib.VO_ERR_WORKSPACE,
+                               "run_images: more than n_cap key points survived in some frame")
+        return b
+
     def launches_per_run(self, n_pairs=None):
         """Number of libvo_b200 kernels one run_device issues (memsets excluded); mirrors the
         round schedule of vo_essential_ransac_batch (csrc/ransac.cu)."""
