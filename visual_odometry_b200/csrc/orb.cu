@@ -24,7 +24,7 @@
 //                      never reach HBM): packed corners (y | x | score) + score histogram
 //   orb_cut1_kernel    histogram -> score cut, compaction of the survivors
 //   orb_harris_kernel  one warp per candidate
-//   orb_cut2_kernel    Harris cut and (y, x) ranking by counting, key-point records
+//   orb_keep / orb_place  Harris cut and (y, x) ranking by counting, key-point records
 //   orb_describe_kernel  one 256-thread block per key point: 47x47 source patch in shared memory
 //                      -> orientation, blurred 41x41 patch, 256 comparisons, 8 ballots
 #include "common.cuh"
@@ -33,6 +33,7 @@ namespace vo {
 
 constexpr int ORB_MAX_LEVELS = 16;
 constexpr int ORB_HALF_PATCH = 15;
+constexpr int ORB_STAGE = 4096;                 // candidates of one level staged in shared memory
 constexpr int ORB_BR = 20;                      // radius of the blurred patch (pattern reach 18.4)
 constexpr int ORB_SR = ORB_BR + 3;              // radius of the source patch
 constexpr int ORB_SW = 2 * ORB_SR + 1;          // 47
@@ -41,6 +42,7 @@ constexpr int FAST_TW = 126, FAST_TH = 30;      // NMS tile; scores for a 128x32
 
 struct OrbLevel {
   int w, h;             // level size
+  int pitch;            // bytes per row: width for the caller's base level, 16-byte multiple above
   int nfeat;            // features wanted on this level
   int cap;              // capacity of its corner lists
   float scale;          // layerScale
@@ -86,25 +88,34 @@ __global__ void orb_coef_kernel(OrbGeom g, int2* __restrict__ coef) {
   }
 }
 
-__global__ void __launch_bounds__(256)
+// four consecutive output pixels per thread, one aligned 32-bit store (the row pitch of levels >= 1
+// is a multiple of 16; the padding columns receive the clamped edge taps and are never read)
+__global__ void __launch_bounds__(128)
 orb_resize_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, uint8_t* __restrict__ pyr,
                   const int2* __restrict__ coef) {
   const OrbLevel L = g.lv[l], P = g.lv[l - 1];
   const int f = blockIdx.z, y = blockIdx.y;
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= L.w) return;
+  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (x4 >= L.w) return;
   const uint8_t* src = (l == 1) ? images + (size_t)f * g.width * g.height
                                 : pyr + (size_t)f * g.pyr_stride + P.pix_off;
   uint8_t* dst = pyr + (size_t)f * g.pyr_stride + L.pix_off;
-  const int2 cx = coef[L.coef_off + x], cy = coef[L.coef_off + L.w + y];
-  const int x0 = cx.x, x1 = min(cx.x + 1, P.w - 1), y0 = cy.x, y1 = min(cy.x + 1, P.h - 1);
-  const int ax1 = cx.y, ax0 = 256 - cx.y, ay1 = cy.y, ay0 = 256 - cy.y;
-  const uint8_t* r0 = src + (size_t)y0 * P.w;
-  const uint8_t* r1 = src + (size_t)y1 * P.w;
-  const int h0 = (int)__ldg(r0 + x0) * ax0 + (int)__ldg(r0 + x1) * ax1;
-  const int h1 = (int)__ldg(r1 + x0) * ax0 + (int)__ldg(r1 + x1) * ax1;
-  const uint32_t v = (uint32_t)h0 * (uint32_t)ay0 + (uint32_t)h1 * (uint32_t)ay1;
-  dst[(size_t)y * L.w + x] = (uint8_t)((v + (1u << 15)) >> 16);
+  const int2 cy = coef[L.coef_off + L.w + y];
+  const int y0 = cy.x, y1 = min(cy.x + 1, P.h - 1);
+  const uint32_t ay1 = cy.y, ay0 = 256 - cy.y;
+  const uint8_t* r0 = src + (size_t)y0 * P.pitch;
+  const uint8_t* r1 = src + (size_t)y1 * P.pitch;
+  uint32_t out = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int2 cx = coef[L.coef_off + min(x4 + k, L.w - 1)];
+    const int x0 = cx.x, x1 = min(cx.x + 1, P.w - 1);
+    const uint32_t ax1 = cx.y, ax0 = 256 - cx.y;
+    const uint32_t h0 = __ldg(r0 + x0) * ax0 + __ldg(r0 + x1) * ax1;
+    const uint32_t h1 = __ldg(r1 + x0) * ax0 + __ldg(r1 + x1) * ax1;
+    out |= (((h0 * ay0 + h1 * ay1) + (1u << 15)) >> 16) << (8 * k);
+  }
+  *reinterpret_cast<uint32_t*>(dst + (size_t)y * L.pitch + x4) = out;
 }
 
 __device__ __forceinline__ const uint8_t* orb_level_ptr(const OrbGeom& g, int l, int f,
@@ -162,9 +173,9 @@ __global__ void __launch_bounds__(256)
 orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint8_t* __restrict__ pyr,
                 uint32_t* __restrict__ list1, int32_t* __restrict__ cnt1, int32_t* __restrict__ hist,
                 uint8_t* __restrict__ score_map) {
-  constexpr int SP = FAST_TW + 8 + 2, SH = FAST_TH + 8;   // source tile 134 (+2 pad) x 38
+  constexpr int SP = FAST_TW + 8 + 6, SH = FAST_TH + 8;   // source tile 134 (+ alignment shift, pad) x 38
   constexpr int CP = FAST_TW + 2, CH = FAST_TH + 2;       // score ring 128 x 32
-  __shared__ uint8_t s_src[SH][SP];
+  __shared__ __align__(16) uint8_t s_src[SH][SP];
   __shared__ uint8_t s_sc[CH][CP + 4];
   __shared__ uint16_t s_cand[CH * CP], s_corner[CH * CP];
   __shared__ uint32_t s_out[(FAST_TW / 2 + 1) * (FAST_TH / 2 + 1)];
@@ -175,14 +186,32 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
   const int tx0 = blockIdx.x * FAST_TW, ty0 = blockIdx.y * FAST_TH;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) { s_n = 0; s_nc = 0; s_nk = 0; }
-  for (int sy = warp; sy < SH; sy += 8) {
-    const int y = ty0 - 4 + sy;
-    const bool yok = y >= 0 && y < L.h;
-    const uint8_t* row = img + (size_t)(yok ? y : 0) * L.w;
+  // source tile: aligned 32-bit loads when rows start on word boundaries (every level the library
+  // allocates; the caller's base level when its width is a multiple of 4), the tile then sits
+  // `al` bytes to the right in shared memory; byte loads otherwise
+  const bool words = (L.pitch & 3) == 0 && ((uintptr_t)img & 3) == 0;
+  const int al = words ? ((tx0 - 4) & 3) : 0;
+  if (words) {
+    constexpr int NW = SP / 4;                               // 35 words per row
+    const int gx = tx0 - 4 - al;                             // multiple of 4 (may be -4)
+    for (int i = threadIdx.x; i < SH * NW; i += 256) {
+      const int sy = i / NW, wi = i - sy * NW;
+      const int y = ty0 - 4 + sy, x = gx + 4 * wi;
+      uint32_t v = 0;
+      if (y >= 0 && y < L.h && x >= 0 && x < L.pitch)
+        v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)y * L.pitch + x));
+      *reinterpret_cast<uint32_t*>(&s_src[sy][4 * wi]) = v;
+    }
+  } else {
+    for (int sy = warp; sy < SH; sy += 8) {
+      const int y = ty0 - 4 + sy;
+      const bool yok = y >= 0 && y < L.h;
+      const uint8_t* row = img + (size_t)(yok ? y : 0) * L.pitch;
 #pragma unroll
-    for (int sx = lane; sx < FAST_TW + 8; sx += 32) {
-      const int x = tx0 - 4 + sx;
-      s_src[sy][sx] = (yok && x >= 0 && x < L.w) ? __ldg(row + x) : (uint8_t)0;
+      for (int sx = lane; sx < FAST_TW + 8; sx += 32) {
+        const int x = tx0 - 4 + sx;
+        s_src[sy][sx] = (yok && x >= 0 && x < L.w) ? __ldg(row + x) : (uint8_t)0;
+      }
     }
   }
   __syncthreads();
@@ -198,7 +227,7 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
       const int x = tx0 - 1 + cx;
       s_sc[cy][cx] = 0;
       if (!(yok && x >= 3 && x < L.w - 3)) continue;
-      const uint8_t* c = &s_src[cy + 3][cx + 3];
+      const uint8_t* c = &s_src[cy + 3][cx + 3 + al];
       const int hi = c[0] + t, lo = c[0] - t;
       // opposite pairs first: flat regions (whole warps) leave after 5 loads
       const int p0 = c[3 * SP], p8 = c[-3 * SP], p4 = c[3], p12 = c[-3];
@@ -226,7 +255,7 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
     const int i = s_cand[k];
     const int cy = i / CP, cx = i - cy * CP;
     int d[16];
-    fast_circle(&s_src[cy + 3][cx + 3], SP, d);
+    fast_circle(&s_src[cy + 3][cx + 3 + al], SP, d);
     if (fast_corner(d, t)) s_corner[atomicAdd(&s_nk, 1)] = (uint16_t)i;
   }
   __syncthreads();
@@ -235,7 +264,7 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
     const int i = s_corner[k];
     const int cy = i / CP, cx = i - cy * CP;
     int d[16];
-    fast_circle(&s_src[cy + 3][cx + 3], SP, d);
+    fast_circle(&s_src[cy + 3][cx + 3 + al], SP, d);
     s_sc[cy][cx] = (uint8_t)fast_raw_score(d, t);
   }
   __syncthreads();
@@ -334,7 +363,7 @@ orb_harris_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t* 
       // clamped reads: only reached when edgeThreshold < 4 (cv2 reads its reflected border there)
       auto px = [&](int dx, int dy) {
         const int X = min(max(xx + dx, 0), L.w - 1), Y = min(max(yy + dy, 0), L.h - 1);
-        return (int)__ldg(img + (size_t)Y * L.w + X);
+        return (int)__ldg(img + (size_t)Y * L.pitch + X);
       };
       const int ix = (px(1, 0) - px(-1, 0)) * 2 + (px(1, -1) - px(-1, -1)) + (px(1, 1) - px(-1, 1));
       const int iy = (px(0, 1) - px(0, -1)) * 2 + (px(-1, 1) - px(-1, -1)) + (px(1, 1) - px(1, -1));
@@ -354,62 +383,113 @@ orb_harris_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t* 
 }
 
 // ------------------------------------------------------------------ second cut + ordering
-// One block per frame walks the levels: retainBest(n) on the Harris response (kept: fewer than n
-// candidates are strictly better), rank of a survivor = number of survivors with a smaller
-// (y, x) word.  Record: x, y (scaled), size, angle (filled later), response, octave.
-__global__ void __launch_bounds__(1024)
-orb_cut2_kernel(OrbGeom g, const uint32_t* __restrict__ list2, const int32_t* __restrict__ cnt2,
-                const float* __restrict__ resp, uint32_t* __restrict__ keepflag,
-                float* __restrict__ kp, int32_t* __restrict__ kp_level_xy, int32_t* __restrict__ n_out,
-                int32_t* __restrict__ status) {
+// One block per (level, frame).  keep: retainBest(n) on the Harris response (kept: fewer than n
+// candidates are strictly better; ties at the cut survive, as in OpenCV).  place: rank of a
+// survivor = number of survivors of its level with a smaller (y, x) word, after the survivors of
+// the lower levels.  Record: x, y (scaled), size, angle (filled later), response, octave.
+__global__ void __launch_bounds__(256)
+orb_keep_kernel(OrbGeom g, const int32_t* __restrict__ cnt2, const float* __restrict__ resp,
+                uint32_t* __restrict__ keepflag, int32_t* __restrict__ cnt3) {
   __shared__ int s_kept;
-  const int f = blockIdx.x;
-  int base = 0;
-  for (int l = 0; l < g.nlevels; ++l) {
-    const OrbLevel L = g.lv[l];
-    const int m = cnt2[f * g.nlevels + l];
-    const uint32_t* cand = list2 + (size_t)f * g.list_stride + L.list_off;
-    const float* r = resp + (size_t)f * g.list_stride + L.list_off;
-    uint32_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
-    if (threadIdx.x == 0) s_kept = 0;
-    __syncthreads();
-    for (int i = threadIdx.x; i < m; i += 1024) {
-      int better = 0;
-      if (m > L.nfeat) {
-        const float ri = r[i];
-        for (int j = 0; j < m; ++j) better += (r[j] > ri);
-      }
-      const bool k = better < L.nfeat;
-      keep[i] = k;
-      if (k) atomicAdd(&s_kept, 1);
+  const int l = blockIdx.x, f = blockIdx.y;
+  const OrbLevel L = g.lv[l];
+  const int m = cnt2[f * g.nlevels + l];
+  const float* r = resp + (size_t)f * g.list_stride + L.list_off;
+  uint32_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
+  __shared__ float s_r[ORB_STAGE];
+  if (threadIdx.x == 0) s_kept = 0;
+  const bool staged = m <= ORB_STAGE;
+  if (staged)
+    for (int i = threadIdx.x; i < m; i += 256) s_r[i] = r[i];
+  __syncthreads();
+  const float* rr = staged ? s_r : r;     // every lane reads the same j: shared-memory broadcast
+  int mine = 0;
+  for (int i = threadIdx.x; i < m; i += 256) {
+    int better = 0;
+    if (m > L.nfeat) {
+      const float ri = rr[i];
+      int j = 0;
+      for (; j + 4 <= m; j += 4)
+        better += (rr[j] > ri) + (rr[j + 1] > ri) + (rr[j + 2] > ri) + (rr[j + 3] > ri);
+      for (; j < m; ++j) better += (rr[j] > ri);
     }
-    __syncthreads();
-    const int kept = s_kept;
-    for (int i = threadIdx.x; i < m; i += 1024) {
-      if (!keep[i]) continue;
-      const uint32_t ci = cand[i] >> 8;
-      int rank = 0;
-      for (int j = 0; j < m; ++j) rank += (keep[j] && (cand[j] >> 8) < ci);
-      const int o = base + rank;
-      if (o < g.cap_out) {
-        const int x = ci & 0xfff, y = ci >> 12;
-        float* rec = kp + ((size_t)f * g.cap_out + o) * 6;
-        rec[0] = __fmul_rn((float)x, L.scale);
-        rec[1] = __fmul_rn((float)y, L.scale);
-        rec[2] = __fmul_rn(31.f, L.scale);
-        rec[3] = -1.f;
-        rec[4] = r[i];
-        rec[5] = (float)l;
-        int32_t* q = kp_level_xy + ((size_t)f * g.cap_out + o) * 2;
-        q[0] = x; q[1] = y;
-      }
-    }
-    base += kept;
-    __syncthreads();
+    const bool k = better < L.nfeat;
+    keep[i] = k;
+    mine += k;
   }
-  if (threadIdx.x == 0) {
-    n_out[f] = min(base, g.cap_out);
-    status[f] = base > g.cap_out ? 1 : 0;
+  if (mine) atomicAdd(&s_kept, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) cnt3[f * g.nlevels + l] = s_kept;
+}
+
+__global__ void __launch_bounds__(256)
+orb_place_kernel(OrbGeom g, const uint32_t* __restrict__ list2, const int32_t* __restrict__ cnt2,
+                 const float* __restrict__ resp, const uint32_t* __restrict__ keepflag,
+                 const int32_t* __restrict__ cnt3, float* __restrict__ kp,
+                 int32_t* __restrict__ kp_level_xy, int32_t* __restrict__ n_out,
+                 int32_t* __restrict__ status) {
+  const int l = blockIdx.x, f = blockIdx.y;
+  const OrbLevel L = g.lv[l];
+  int base = 0, total = 0;
+  for (int k = 0; k < g.nlevels; ++k) {
+    const int c = cnt3[f * g.nlevels + k];
+    if (k < l) base += c;
+    total += c;
+  }
+  if (l == 0 && threadIdx.x == 0) {
+    n_out[f] = min(total, g.cap_out);
+    status[f] = total > g.cap_out ? 1 : 0;
+  }
+  const int m = cnt2[f * g.nlevels + l];
+  const uint32_t* cand = list2 + (size_t)f * g.list_stride + L.list_off;
+  const float* r = resp + (size_t)f * g.list_stride + L.list_off;
+  const uint32_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
+  __shared__ uint32_t s_w[ORB_STAGE];
+  __shared__ uint16_t s_i[ORB_STAGE];
+  __shared__ int s_nk;
+  const int kept = cnt3[f * g.nlevels + l];
+  const bool staged = kept <= ORB_STAGE && m <= 65535;
+  if (threadIdx.x == 0) s_nk = 0;
+  __syncthreads();
+  if (staged) {
+    for (int i = threadIdx.x; i < m; i += 256)
+      if (keep[i]) {
+        const int k = atomicAdd(&s_nk, 1);
+        s_w[k] = cand[i] >> 8;
+        s_i[k] = (uint16_t)i;
+      }
+  }
+  __syncthreads();
+  const int n_items = staged ? kept : m;
+  for (int k = threadIdx.x; k < n_items; k += 256) {
+    int i, rank = 0;
+    uint32_t ci;
+    if (staged) {
+      i = s_i[k];
+      ci = s_w[k];
+      int j = 0;
+      for (; j + 4 <= kept; j += 4)
+        rank += (s_w[j] < ci) + (s_w[j + 1] < ci) + (s_w[j + 2] < ci) + (s_w[j + 3] < ci);
+      for (; j < kept; ++j) rank += (s_w[j] < ci);
+    } else {
+      i = k;
+      if (!keep[i]) continue;
+      ci = cand[i] >> 8;
+      for (int j = 0; j < m; ++j) rank += (keep[j] && (cand[j] >> 8) < ci);
+    }
+    const int o = base + rank;
+    if (o < g.cap_out) {
+      const int x = ci & 0xfff, y = ci >> 12;
+      float* rec = kp + ((size_t)f * g.cap_out + o) * 6;
+      rec[0] = __fmul_rn((float)x, L.scale);
+      rec[1] = __fmul_rn((float)y, L.scale);
+      rec[2] = __fmul_rn(31.f, L.scale);
+      rec[3] = -1.f;
+      rec[4] = r[i];
+      rec[5] = (float)l;
+      int32_t* q = kp_level_xy + ((size_t)f * g.cap_out + o) * 2;
+      q[0] = x; q[1] = y;
+    }
   }
 }
 
@@ -455,7 +535,7 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
   const bool inside = x0 >= ORB_SR && x0 + ORB_SR < L.w && y0 >= ORB_SR && y0 + ORB_SR < L.h;
   for (int sy = warp; sy < ORB_SW; sy += 8) {
     const int y = inside ? y0 - ORB_SR + sy : orb_reflect101(y0 - ORB_SR + sy, L.h);
-    const uint8_t* row = img + (size_t)y * L.w;
+    const uint8_t* row = img + (size_t)y * L.pitch;
 #pragma unroll
     for (int sx = lane; sx < ORB_SW; sx += 32) {
       const int x = inside ? x0 - ORB_SR + sx : orb_reflect101(x0 - ORB_SR + sx, L.w);
@@ -545,7 +625,7 @@ struct OrbWs {
   uint8_t* pyr;
   uint32_t *list1, *list2, *keep;
   float* resp;
-  int32_t *cnt1, *cnt2, *hist, *level_xy;
+  int32_t *cnt1, *cnt2, *cnt3, *hist, *level_xy;
   size_t bytes;
 };
 
@@ -577,7 +657,8 @@ static bool orb_geometry(OrbGeom& g, int n_frames, int width, int height, int nf
     }
     L.cap = (L.w / 2 + 1) * (L.h / 2 + 1);   // strict 3x3 maxima: at most one per 2x2 cell
     L.pix_off = pix;
-    if (l > 0) pix += ((size_t)L.w * L.h + 255) & ~(size_t)255;
+    L.pitch = l == 0 ? width : (L.w + 15) & ~15;
+    if (l > 0) pix += ((size_t)L.pitch * L.h + 255) & ~(size_t)255;
     L.list_off = list;
     list += ((size_t)L.cap + 63) & ~(size_t)63;
     L.coef_off = coef;
@@ -606,9 +687,10 @@ static OrbWs orb_carve(void* base, const OrbGeom& g) {
   w.keep = (uint32_t*)take(F * g.list_stride * 4);
   w.resp = (float*)take(F * g.list_stride * 4);
   // counters and histogram are contiguous: one memset
-  w.cnt1 = (int32_t*)take(F * g.nlevels * (2 + 256) * sizeof(int32_t));
+  w.cnt1 = (int32_t*)take(F * g.nlevels * (3 + 256) * sizeof(int32_t));
   w.cnt2 = w.cnt1 + F * g.nlevels;
-  w.hist = w.cnt2 + F * g.nlevels;
+  w.cnt3 = w.cnt2 + F * g.nlevels;
+  w.hist = w.cnt3 + F * g.nlevels;
   w.level_xy = (int32_t*)take(F * (size_t)(g.cap_out > 0 ? g.cap_out : 0) * 2 * sizeof(int32_t));
   w.bytes = off;
   return w;
@@ -660,18 +742,19 @@ extern "C" int vo_orb_detect_batch(const uint8_t* images, int n_frames, int widt
   VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_orb_detect_batch: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   const int F = n_frames;
-  cudaMemsetAsync(w.cnt1, 0, (size_t)F * nlevels * (2 + 256) * sizeof(int32_t), st);
+  cudaMemsetAsync(w.cnt1, 0, (size_t)F * nlevels * (3 + 256) * sizeof(int32_t), st);
   if (nlevels > 1) orb_coef_kernel<<<dim3(8, nlevels - 1), 256, 0, st>>>(g, w.coef);
   for (int l = 0; l < nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
     if (l > 0)
-      orb_resize_kernel<<<dim3((L.w + 255) / 256, L.h, F), 256, 0, st>>>(g, l, images, w.pyr, w.coef);
+      orb_resize_kernel<<<dim3((L.w + 511) / 512, L.h, F), 128, 0, st>>>(g, l, images, w.pyr, w.coef);
     orb_fast_kernel<<<dim3((L.w + FAST_TW - 1) / FAST_TW, (L.h + FAST_TH - 1) / FAST_TH, F), 256, 0, st>>>(
         g, l, images, w.pyr, w.list1, w.cnt1, w.hist, nullptr);
   }
   orb_cut1_kernel<<<dim3(nlevels, F), 256, 0, st>>>(g, w.list1, w.cnt1, w.hist, w.list2, w.cnt2);
   orb_harris_kernel<<<dim3(64, nlevels, F), 256, 0, st>>>(g, images, w.pyr, w.list2, w.cnt2, w.resp);
-  orb_cut2_kernel<<<F, 1024, 0, st>>>(g, w.list2, w.cnt2, w.resp, w.keep, kp, w.level_xy, n_out, status);
+  orb_keep_kernel<<<dim3(nlevels, F), 256, 0, st>>>(g, w.cnt2, w.resp, w.keep, w.cnt3);
+  orb_place_kernel<<<dim3(nlevels, F), 256, 0, st>>>(g, w.list2, w.cnt2, w.resp, w.keep, w.cnt3, kp, w.level_xy, n_out, status);
   orb_describe_kernel<<<dim3(cap_out, F), 256, 0, st>>>(g, images, w.pyr, kp, w.level_xy, n_out, desc);
   return check_launch("vo_orb_detect_batch");
 }
