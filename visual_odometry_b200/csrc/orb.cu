@@ -194,13 +194,21 @@ orb_fast_kernel(OrbGeom g, int l, const uint8_t* __restrict__ images, const uint
   if (words) {
     constexpr int NW = SP / 4;                               // 35 words per row
     const int gx = tx0 - 4 - al;                             // multiple of 4 (may be -4)
-    for (int i = threadIdx.x; i < SH * NW; i += 256) {
+    constexpr int NIT = (SH * NW + 255) / 256;               // 6: all loads in flight, then the stores
+    uint32_t v[NIT];
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int i = threadIdx.x + 256 * k;
       const int sy = i / NW, wi = i - sy * NW;
       const int y = ty0 - 4 + sy, x = gx + 4 * wi;
-      uint32_t v = 0;
-      if (y >= 0 && y < L.h && x >= 0 && x < L.pitch)
-        v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)y * L.pitch + x));
-      *reinterpret_cast<uint32_t*>(&s_src[sy][4 * wi]) = v;
+      v[k] = 0;
+      if (i < SH * NW && y >= 0 && y < L.h && x >= 0 && x < L.pitch)
+        v[k] = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)y * L.pitch + x));
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; ++k) {
+      const int i = threadIdx.x + 256 * k;
+      if (i < SH * NW) reinterpret_cast<uint32_t*>(&s_src[0][0])[i] = v[k];
     }
   } else {
     for (int sy = warp; sy < SH; sy += 8) {
