@@ -207,3 +207,32 @@ def test_image_sequence_to_poses_on_the_device(cuda_dev):
         _, Rc, tc, _ = cv2.recoverPose(E, p1[mask.ravel() == 1], p2[mask.ravel() == 1], K)
         ang_c = np.degrees(np.arccos(np.clip((np.trace(Rg[k].T @ Rc) - 1) / 2, -1, 1)))
         assert ang_c < 5.0, (k, ang_c)
+
+
+@pytest.mark.parametrize("kind,h,w,nf,nl,thr", [("noise", 480, 640, 500, 8, 20), ("noise", 300, 401, 3000, 5, 40),
+                                                ("texture", 1080, 1920, 500, 8, 20), ("texture", 2160, 3840, 5000, 8, 20),
+                                                ("texture", 333, 517, 1000, 8, 7), ("blocks", 256, 256, 200, 4, 20)])
+def test_equals_live_cv2(cuda_dev, kind, h, w, nf, nl, thr):
+    """Against cv2 itself on the box (not a stored golden): noise images have tens of thousands of
+    FAST corners and heavy score ties at the first cut, the block image has exactly repeated
+    structure (tied Harris responses), 4K is the largest size the packed corner words hold."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(h * w + nf)
+    if kind == "noise":
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    elif kind == "blocks":
+        img = np.kron(rng.integers(0, 2, (h // 32, w // 32)) * 120 + 60, np.ones((32, 32))).astype(np.uint8)
+        img[:, w // 2:] = img[:, :w // 2]          # exact repetition -> tied responses
+    else:
+        img = synth.textured_image(h, w, h + w)
+    kps, d = cv2.ORB_create(nfeatures=nf, nlevels=nl, fastThreshold=thr).detectAndCompute(img, None)
+    ref = np.array([(k.pt[0], k.pt[1], k.size, k.angle, k.response, k.octave) for k in kps],
+                   np.float32).reshape(-1, 6)
+    d = np.zeros((0, 32), np.uint8) if d is None else d
+    o = np.lexsort((ref[:, 0], ref[:, 1], ref[:, 5]))
+    res, status = run(OrbDetector(nfeatures=nf, nlevels=nl, fastThreshold=thr), img[None], cap=len(ref) + 64)
+    assert status[0] == 0
+    kp, desc = res[0]
+    assert kp.shape == ref.shape
+    assert np.array_equal(kp, ref[o])
+    assert np.array_equal(desc, d[o])
