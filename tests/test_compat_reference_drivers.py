@@ -44,6 +44,16 @@ def test_reference_visual_slam_runs_on_compat_modules(compat_path):
     assert np.allclose([slam.camera_matrix[0, 0], slam.camera_matrix[0, 2], slam.camera_matrix[1, 2]],
                        [802.832, 565.427, 240.124], atol=1e-3)
     assert vs.cv2 is initials.cv2 and hasattr(vs.cv2, "solvePnPRansac")
+    # the matcher VisualSlam.__init__ builds (src/visual_slam.py:19) is the B200 one, and so is the
+    # ORB detector of the commented-out line 16 / of ImageAndKeypoints; SIFT stays cv2's
+    from visual_odometry_b200.matcher import B200Matcher, NORM_L2
+    from visual_odometry_b200.orb import OrbDetector
+    assert isinstance(slam.bf, B200Matcher) and slam.bf.normType == NORM_L2 and slam.bf.crossCheck
+    det = vs.cv2.ORB_create(nfeatures=700)
+    assert isinstance(det, OrbDetector) and det.nfeatures == 700 and det.nlevels == 8
+    with pytest.raises(NotImplementedError):
+        vs.cv2.ORB_create(WTA_K=3)
+    assert type(slam.detector).__module__.startswith("cv2")
     # namedtuples keep the reference's field order
     assert initials.Match._fields == ('featureid1', 'featureid2', 'keypoint1', 'keypoint2',
                                       'descriptor1', 'descriptor2', 'distance', 'color')

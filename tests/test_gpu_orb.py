@@ -236,3 +236,26 @@ def test_equals_live_cv2(cuda_dev, kind, h, w, nf, nl, thr):
     assert kp.shape == ref.shape
     assert np.array_equal(kp, ref[o])
     assert np.array_equal(desc, d[o])
+
+
+def test_legacy_two_image_demo_from_files(cuda_dev, tmp_path):
+    """TriangulatePointsFromTwoImages.run (reference src/triangulate_points_from_images.py:17-41,
+    what main_triangulate.py calls) on two image FILES: cv2.imread -> ImageAndKeypoints("ORB")
+    (GPU detector through the cv2 shim) -> legacy ImagePair("ORB").standard_pipeline -> the
+    match visualisation written to disk."""
+    cv2 = pytest.importorskip("cv2")
+    from visual_odometry_b200.legacy import TriangulatePointsFromTwoImages
+    from visual_odometry_b200.orb import OrbDetector as _Det
+    images, K, cams = _render_two_plane_sequence(2)
+    f1, f2, out = str(tmp_path / "a.png"), str(tmp_path / "b.png"), str(tmp_path / "m.png")
+    cv2.imwrite(f1, cv2.cvtColor(images[0], cv2.COLOR_GRAY2BGR))
+    cv2.imwrite(f2, cv2.cvtColor(images[1], cv2.COLOR_GRAY2BGR))
+    tp = TriangulatePointsFromTwoImages()
+    tp.run(f1, f2, output=out)
+    pair = tp.pair
+    assert isinstance(pair.image1.detector, _Det)
+    assert len(pair.image1.keypoints) == 500 and pair.image1.descriptors.shape == (500, 32)
+    assert pair.R.shape == (3, 3) and abs(np.linalg.det(pair.R) - 1) < 1e-9
+    assert abs(np.linalg.norm(pair.t) - 1) < 1e-9
+    assert pair.points3d_reconstr.shape[0] == 4 and pair.points3d_reconstr.shape[1] > 50
+    assert os.path.getsize(out) > 10000

@@ -2,7 +2,9 @@
 
 src/visual_slam.py calls cv2.solvePnPRansac (:231) and cv2.Rodrigues (:243) directly, so the only
 way to move them to the GPU with that file unchanged is to rebind the name `cv2`.
-Everything not overridden forwards to the real OpenCV module (image I/O, resize, drawing).
+The matcher and the ORB detector the reference constructs through that name come from this
+package too (B200Matcher, OrbDetector); SIFT extraction is not implemented on the GPU and stays
+cv2's.  Everything not overridden forwards to the real OpenCV module (image I/O, resize, drawing).
 """
 import numpy as np
 
@@ -24,6 +26,24 @@ class _Cv2Namespace:
     def Rodrigues(self, src, *a, **k):
         from . import pnp
         return pnp.rodrigues(src)
+
+    # ---- GPU overrides (K1 / K6 matcher, N4 detector): the objects the reference builds in
+    # VisualSlam.__init__ (src/visual_slam.py:16-19) and ImageAndKeypoints (src/image_and_keypoints.py:8-13)
+    def BFMatcher(self, normType=None, crossCheck=False):
+        from . import matcher
+        normType = _real.NORM_L2 if normType is None else normType
+        if normType not in (_real.NORM_HAMMING, _real.NORM_L2):
+            raise NotImplementedError("B200 path: BFMatcher supports NORM_HAMMING and NORM_L2 only")
+        return matcher.B200Matcher(matcher.NORM_HAMMING if normType == _real.NORM_HAMMING
+                                   else matcher.NORM_L2, crossCheck=crossCheck)
+
+    def ORB_create(self, nfeatures=500, scaleFactor=1.2, nlevels=8, edgeThreshold=31, firstLevel=0,
+                   WTA_K=2, scoreType=0, patchSize=31, fastThreshold=20):
+        if firstLevel != 0 or WTA_K != 2 or scoreType != _real.ORB_HARRIS_SCORE or patchSize != 31:
+            raise NotImplementedError("B200 path: ORB with firstLevel 0, WTA_K 2, HARRIS_SCORE, "
+                                      "patchSize 31 only")
+        from . import orb
+        return orb.OrbDetector(nfeatures, scaleFactor, nlevels, edgeThreshold, fastThreshold)
 
     # ---- headless GUI ----
     def imshow(self, *a, **k):
