@@ -553,11 +553,12 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
     }
   }
   __syncthreads();
-  // --- orientation: warp 0, lane = row of the disc (31 rows)
-  if (threadIdx.x < 32) {
+  // --- orientation: warp 7 (idle during the row pass below, which occupies threads 0..187),
+  // lane = row of the disc (31 rows)
+  if (warp == 7) {
     int m01 = 0, m10 = 0;
-    if (threadIdx.x < 2 * ORB_HALF_PATCH + 1) {
-      const int v = (int)threadIdx.x - ORB_HALF_PATCH;
+    if (lane < 2 * ORB_HALF_PATCH + 1) {
+      const int v = lane - ORB_HALF_PATCH;
       const int d = c_orb_umax[abs(v)];
       int sum = 0;
       for (int u = -d; u <= d; ++u) {
@@ -569,7 +570,7 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
     }
     m01 = __reduce_add_sync(0xffffffffu, m01);
     m10 = __reduce_add_sync(0xffffffffu, m10);
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
       const float a = orb_fast_atan2((float)m01, (float)m10);
       rec[3] = a;
       // angle *= (float)(CV_PI / 180.f); a = (float)cos(angle), b = (float)sin(angle)  (orb.cpp)
