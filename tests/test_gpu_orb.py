@@ -259,3 +259,19 @@ def test_legacy_two_image_demo_from_files(cuda_dev, tmp_path):
     assert abs(np.linalg.norm(pair.t) - 1) < 1e-9
     assert pair.points3d_reconstr.shape[0] == 4 and pair.points3d_reconstr.shape[1] > 50
     assert os.path.getsize(out) > 10000
+
+
+def test_slam_loop_from_images(cuda_dev):
+    """DeviceSlam.run_images: rendered frames -> ORB extraction -> hot path -> map stage (PnP,
+    map growth, bundle adjustment, pruning) without descriptors or key points touching the host."""
+    pytest.importorskip("cv2")
+    from visual_odometry_b200.slam import DeviceSlam
+    images, K, cams = _render_two_plane_sequence(6)
+    slam = DeviceSlam(K, 1500, 6, descriptor="orb", ba_iterations=10)
+    log = slam.run_images(images, OrbDetector(nfeatures=1200))
+    assert len(log) == 5
+    assert log[0]["n_points"] > 100 and log[0]["n_obs"] >= 2 * log[0]["n_points"] - 5
+    ok = [e["pnp_ok"] for e in log[1:]]
+    assert sum(bool(x) for x in ok) >= 3, log
+    assert log[-1]["n_points"] > log[0]["n_points"] // 2
+    assert len(log[-1]["cameras"]) >= 4

@@ -44,6 +44,13 @@ class DeviceSlam:
         self.pipe.run_host(desc, kp, nkp, pairs)
         return [self.step(b) for b in range(F - 1)]
 
+    def run_images(self, images, detector):
+        """The same loop fed with IMAGES (uint8 [F,H,W] or BGR [F,H,W,3]): ORB extraction on the
+        device (orb.OrbDetector, reference src/frame_generator.py:25) writes straight into the
+        pipeline's frame arrays, then the hot path and the per-frame map stage as in `run`."""
+        b = self.pipe.run_images(images, detector)
+        return [self.step(k) for k in range(b)]
+
     # ------------------------------------------------------------------ streaming
     def add_frame(self, desc, kp):
         """VisualSlam.add_to_list_of_frames + match_current_and_previous_frame for ONE new frame
