@@ -742,8 +742,8 @@ extern "C" int vo_orb_detect_batch(const uint8_t* images, int n_frames, int widt
                           edge_threshold, fast_threshold, cap_out),
              VO_ERR_INVALID_ARG,
              "vo_orb_detect_batch: bad geometry (1 <= nlevels <= 16, size <= 4095, scale > 1)");
-  VO_REQUIRE(edge_threshold >= 0 && cap_out >= 1, VO_ERR_INVALID_ARG,
-             "vo_orb_detect_batch: edge_threshold >= 0 and cap_out >= 1 required");
+  VO_REQUIRE(edge_threshold >= 0 && cap_out >= 1 && n_frames <= 65535, VO_ERR_INVALID_ARG,
+             "vo_orb_detect_batch: edge_threshold >= 0, cap_out >= 1 and at most 65535 frames per call");
   if (n_frames == 0) return VO_OK;
   VO_REQUIRE(images && kp && desc && n_out && status && ws, VO_ERR_INVALID_ARG,
              "vo_orb_detect_batch: null pointer");
