@@ -116,3 +116,20 @@ def test_detector_equals_live_cv2():
 def test_level_budget():
     assert cv_orb.features_per_level(500, 8) == [109, 90, 75, 63, 52, 44, 36, 31]
     assert sum(cv_orb.features_per_level(2000, 8)) == 2000
+
+
+def test_library_level_geometry_equals_oracle_without_a_device():
+    """vo_orb_level_info is host-side logic of the C-ABI (pyramid sizes, per-level feature budget,
+    float32 layer scales as cv2 computes them): checked here without a GPU."""
+    from visual_odometry_b200.orb import OrbDetector
+    for (h, w, nf, nl) in ((1080, 1920, 2000, 8), (480, 640, 500, 8), (97, 131, 50, 3), (2160, 3840, 5000, 12)):
+        info = OrbDetector(nfeatures=nf, nlevels=nl, device="cpu").level_info(w, h)
+        assert list(zip(info["w"], info["h"])) == cv_orb.level_sizes((h, w), nl)
+        assert info["nfeatures"] == cv_orb.features_per_level(nf, nl)
+        assert np.array_equal(np.array(info["scale"], np.float32), cv_orb.level_scales(nl))
+    from visual_odometry_b200 import _lib
+    lib = _lib.load()
+    assert lib.vo_orb_workspace_bytes(4, 1920, 1080, 2000, 1.2, 8, 2256) > 4 * 1920 * 1080
+    assert lib.vo_orb_workspace_bytes(1, 5000, 100, 10, 1.2, 8, 100) == 0      # wider than 4095
+    rc = lib.vo_orb_detect_batch(None, 1, 640, 480, 500, 1.2, 8, 31, 20, 600, None, None, None, None, None, 0, None)
+    assert rc == _lib.VO_ERR_INVALID_ARG and b"null" in lib.vo_last_error_string()
