@@ -397,13 +397,13 @@ orb_harris_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t* 
 // the lower levels.  Record: x, y (scaled), size, angle (filled later), response, octave.
 __global__ void __launch_bounds__(256)
 orb_keep_kernel(OrbGeom g, const int32_t* __restrict__ cnt2, const float* __restrict__ resp,
-                uint32_t* __restrict__ keepflag, int32_t* __restrict__ cnt3) {
+                uint8_t* __restrict__ keepflag, int32_t* __restrict__ cnt3) {
   __shared__ int s_kept;
   const int l = blockIdx.x, f = blockIdx.y;
   const OrbLevel L = g.lv[l];
   const int m = cnt2[f * g.nlevels + l];
   const float* r = resp + (size_t)f * g.list_stride + L.list_off;
-  uint32_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
+  uint8_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
   __shared__ float s_r[ORB_STAGE];
   if (threadIdx.x == 0) s_kept = 0;
   const bool staged = m <= ORB_STAGE;
@@ -432,7 +432,7 @@ orb_keep_kernel(OrbGeom g, const int32_t* __restrict__ cnt2, const float* __rest
 
 __global__ void __launch_bounds__(256)
 orb_place_kernel(OrbGeom g, const uint32_t* __restrict__ list2, const int32_t* __restrict__ cnt2,
-                 const float* __restrict__ resp, const uint32_t* __restrict__ keepflag,
+                 const float* __restrict__ resp, const uint8_t* __restrict__ keepflag,
                  const int32_t* __restrict__ cnt3, float* __restrict__ kp,
                  int32_t* __restrict__ kp_level_xy, int32_t* __restrict__ n_out,
                  int32_t* __restrict__ status) {
@@ -451,7 +451,7 @@ orb_place_kernel(OrbGeom g, const uint32_t* __restrict__ list2, const int32_t* _
   const int m = cnt2[f * g.nlevels + l];
   const uint32_t* cand = list2 + (size_t)f * g.list_stride + L.list_off;
   const float* r = resp + (size_t)f * g.list_stride + L.list_off;
-  const uint32_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
+  const uint8_t* keep = keepflag + (size_t)f * g.list_stride + L.list_off;
   __shared__ uint32_t s_w[ORB_STAGE];
   __shared__ uint16_t s_i[ORB_STAGE];
   __shared__ int s_nk;
@@ -632,7 +632,8 @@ orb_describe_kernel(OrbGeom g, const uint8_t* __restrict__ images, const uint8_t
 struct OrbWs {
   int2* coef;
   uint8_t* pyr;
-  uint32_t *list1, *list2, *keep;
+  uint32_t *list1, *list2;
+  uint8_t* keep;
   float* resp;
   int32_t *cnt1, *cnt2, *cnt3, *hist, *level_xy;
   size_t bytes;
@@ -693,8 +694,9 @@ static OrbWs orb_carve(void* base, const OrbGeom& g) {
   w.pyr = (uint8_t*)take(F * g.pyr_stride + 16);
   w.list1 = (uint32_t*)take(F * g.list_stride * 4);
   w.list2 = (uint32_t*)take(F * g.list_stride * 4);
-  w.keep = (uint32_t*)take(F * g.list_stride * 4);
-  w.resp = (float*)take(F * g.list_stride * 4);
+  w.keep = (uint8_t*)take(F * g.list_stride);
+  // the Harris responses reuse the memory of the first corner list, which is dead after cut1
+  w.resp = (float*)w.list1;
   // counters and histogram are contiguous: one memset
   w.cnt1 = (int32_t*)take(F * g.nlevels * (3 + 256) * sizeof(int32_t));
   w.cnt2 = w.cnt1 + F * g.nlevels;
