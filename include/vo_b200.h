@@ -46,12 +46,17 @@ const char* vo_last_error_string(void);
  *         t2/dist2 second neighbour (mode KNN2_RATIO; may be NULL);
  *         pts float64 [n_pairs, n_cap, 4] = (x1,y1,x2,y2) of each match (image_pair.py:294-299);
  *         n_out int32 [n_pairs] number of matches, rows sorted by queryIdx.
+ * Two kernels behind one entry, identical results (bit-exact): small batches run the popc kernel
+ * (csrc/hamming.cu); large ones expand every frame 0..n_frames-1 once into int8 operand tiles
+ * and rank both directions with tcgen05 kind::i8 MMAs (csrc/hamming_tc.cuh).  n_frames = 0
+ * (frame count unknown) keeps the popc kernel.  vo_debug_hamming(1 | 2) forces one of the two.
  */
-size_t vo_match_workspace_bytes(int n_pairs, int n_cap);
+size_t vo_match_workspace_bytes(int n_frames, int n_pairs, int n_cap);
 int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
-                           const int32_t* pairs, int n_pairs, int mode, double ratio,
+                           int n_frames, const int32_t* pairs, int n_pairs, int mode, double ratio,
                            int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                            double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+int vo_debug_hamming(int flags);
 /* single pair convenience: d1 [n1,32], d2 [n2,32]; outputs sized n1 */
 int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode, double ratio,
                      int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,

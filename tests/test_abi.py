@@ -31,14 +31,14 @@ def test_loader_binds_and_reports_version():
     assert lib.vo_version() >= 100
     assert isinstance(lib.vo_last_error_string(), bytes)
     # pure host-side size queries work without a device
-    assert lib.vo_match_workspace_bytes(3, 100) >= 3 * 100 * 33 * 4
+    assert lib.vo_match_workspace_bytes(0, 3, 100) >= 3 * 100 * 33 * 4
     assert lib.vo_essential_workspace_bytes(2, 100, 1000) > 0
     assert lib.vo_pose_workspace_bytes(2, 100) >= 200
 
 
 def test_invalid_arguments_fail_loudly_without_a_device():
     lib = _lib.load()
-    rc = lib.vo_match_hamming_batch(None, None, None, 10, None, 1, 0, 0.0, None, None, None, None,
+    rc = lib.vo_match_hamming_batch(None, None, None, 10, 2, None, 1, 0, 0.0, None, None, None, None,
                                     None, None, None, None, 0, None)
     assert rc == _lib.VO_ERR_INVALID_ARG
     assert b"null" in lib.vo_last_error_string()

@@ -83,3 +83,36 @@ def test_install_can_patch_the_reference_map(compat_path):
     assert ref_map.Map.calculate_reprojection_error is map_ops.calculate_reprojection_error
     m = ref_map.Map()                         # the rest of the class is the reference's own
     assert m.increment_id() == 0 and m.increment_id() == 1
+
+
+def test_reference_run_loop_returns_when_headless(compat_path, tmp_path, monkeypatch):
+    """The reference's UNMODIFIED VisualSlam.run() (src/visual_slam.py:338-374) ends in
+    `while True: k = cv2.waitKey(100); if k == ord('q'): break`.  With the headless cv2 namespace
+    it must come back: every frame is read and processed, then the idle loop is released."""
+    import time
+    import cv2 as real_cv2
+    vs = importlib.import_module("visual_slam")
+    rng = np.random.default_rng(0)
+    for k in range(3):
+        real_cv2.imwrite(str(tmp_path / f"f{k:02d}.jpg"), rng.integers(0, 255, (48, 64, 3), dtype=np.uint8))
+    slam = vs.VisualSlam(str(tmp_path))
+    slam.set_camera_matrix()
+    seen = []
+
+    def fake_process_frame(img):            # stands for make_frame + match_current_and_previous_frame
+        seen.append(img.shape)
+        if len(seen) > 1:
+            vs.cv2.imshow("matches", img)   # visual_slam.py:304
+            vs.cv2.waitKey(100)             # visual_slam.py:312
+        return img
+
+    monkeypatch.setattr(slam, "process_frame", fake_process_frame)
+    monkeypatch.setattr(slam.map, "show_map_statistics", lambda: None)
+    monkeypatch.setenv("VO_B200_HEADLESS_QUIT", "5")
+    t0 = time.perf_counter()
+    slam.run()
+    assert len(seen) == 3 and time.perf_counter() - t0 < 5.0
+    # a frame loop with more frames than the idle limit is not cut short: imread / imshow reset it
+    for _ in range(12):
+        vs.cv2.imread(str(tmp_path / "f00.jpg"))
+        assert vs.cv2.waitKey(400000) == -1

@@ -34,9 +34,10 @@ _sz = C.c_size_t
 SIGNATURES = {
     "vo_version": (_i, []),
     "vo_last_error_string": (C.c_char_p, []),
-    "vo_match_workspace_bytes": (_sz, [_i, _i]),
-    "vo_match_hamming_batch": (_i, [_p, _p, _p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,
-                                    _p, _sz, _p]),
+    "vo_match_workspace_bytes": (_sz, [_i, _i, _i]),
+    "vo_match_hamming_batch": (_i, [_p, _p, _p, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p,
+                                    _p, _p, _sz, _p]),
+    "vo_debug_hamming": (_i, [_i]),
     "vo_match_hamming": (_i, [_p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_match_l2_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_match_l2_batch": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p,

@@ -13,6 +13,7 @@
 // per-thread min over RQ -> REDUX warp min -> shared atomicMin -> one global atomicMin per tile
 // column, so forward NN, second NN and backward NN all come out of ONE pass (cv2 does two).
 #include "common.cuh"
+#include "hamming_tc.cuh"
 
 namespace vo {
 
@@ -287,9 +288,46 @@ match_compact_kernel(const uint32_t* __restrict__ rowbest, const uint32_t* __res
 
 using namespace vo;
 
-extern "C" size_t vo_match_workspace_bytes(int n_pairs, int n_cap) {
+static size_t popc_workspace_bytes(int n_pairs, int n_cap) {
   // rowbest for up to 16 splits + colmin
   return (size_t)n_pairs * n_cap * (16 * 2 + 1) * sizeof(uint32_t);
+}
+
+// bits 0..1: 0 = choose by batch size, 1 = always the popc kernel, 2 = always the tensor-core
+// kernel (needs n_frames > 0); bits 2..: htc::g_debug (timing experiments)
+static int g_hamming_debug = 0;
+extern "C" int vo_debug_hamming(int flags) {
+  g_hamming_debug = flags;
+  const int kd = flags >> 2;
+  return cudaMemcpyToSymbol(htc::g_debug, &kd, sizeof(int)) == cudaSuccess ? VO_OK : VO_ERR_CUDA;
+}
+
+static int device_sms() {
+  static int sms[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!sms[dev] &&
+      (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] <= 0))
+    sms[dev] = 148;
+  return sms[dev];
+}
+
+// The tensor-core path pays a per-frame operand expansion and works in (pair, direction, 256-row
+// block) items of ~10 us each: worth it once the items give every SM something to do.
+static bool use_tensor_path(int n_frames, int n_pairs, int n_cap, int mode) {
+  const int path = g_hamming_debug & 3;
+  if (n_frames <= 0 || path == 1) return false;
+  if (path == 2) return true;
+  const long items = (long)n_pairs * (mode == VO_MATCH_MUTUAL ? 2 : 1) * ((n_cap + htc::ROWS - 1) / htc::ROWS);
+  return n_cap >= 512 && items >= device_sms() / 2;
+}
+
+extern "C" size_t vo_match_workspace_bytes(int n_frames, int n_pairs, int n_cap) {
+  if (n_pairs <= 0 || n_cap <= 0) return 0;
+  const size_t a = popc_workspace_bytes(n_pairs, n_cap);
+  const size_t b = n_frames > 0 ? htc::carve(nullptr, n_frames, n_pairs, n_cap).bytes : 0;
+  return a > b ? a : b;
 }
 
 // Train-range splits serve two purposes: filling the SMs when there are few (pair, query tile)
@@ -368,20 +406,68 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
   return check_launch("vo_match_hamming");
 }
 
+// tensor-core path: expand every frame once, both directions as MMA passes, the same compaction
+static int launch_hamming_tc(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
+                             int n_frames, const int32_t* pairs, int n_pairs, int mode, double ratio,
+                             int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
+                             double* pts, int32_t* n_out, void* ws, cudaStream_t st) {
+  const int ntile = (n_cap + htc::ROWS - 1) / htc::ROWS;
+  const htc::Ws w = htc::carve(ws, n_frames, n_pairs, n_cap);
+  const int smem = (int)sizeof(htc::Smem) + 1024;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!attr_set[dev]) {
+    if (cudaFuncSetAttribute(htc::match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(htc::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+      return check_launch("vo_match_hamming_batch(smem attribute)");
+    attr_set[dev] = true;
+  }
+  {
+    ProfScope prof(4, st);
+    htc::expand_kernel<<<dim3(ntile, n_frames), htc::ROWS, 0, st>>>(desc, nkp, n_cap, ntile, w.tiles);
+  }
+  const int ndir = mode == VO_MATCH_MUTUAL ? 2 : 1;
+  const long n_items = (long)n_pairs * ndir * ntile;
+  const int grid = (int)(n_items < device_sms() ? n_items : device_sms());
+  {
+    ProfScope prof(0, st);
+    if (mode == VO_MATCH_MUTUAL)
+      htc::match_kernel<false><<<grid, htc::THREADS, smem, st>>>(w.tiles, nkp, pairs, n_cap, ntile, ndir,
+                                                                n_items, w.rowbest, w.colmin);
+    else
+      htc::match_kernel<true><<<grid, htc::THREADS, smem, st>>>(w.tiles, nkp, pairs, n_cap, ntile, ndir,
+                                                               n_items, w.rowbest, w.colmin);
+  }
+  for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
+    const int np = n_pairs - p0 < 65535 ? n_pairs - p0 : 65535;
+    const size_t ob = (size_t)p0 * n_cap;
+    match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
+        w.rowbest + ob * 2, w.colmin + ob, nkp, kp, n_cap, pairs + 2 * p0, 0, 0, 1, mode, ratio, q + ob,
+        t + ob, dist + ob, t2 ? t2 + ob : nullptr, dist2 ? dist2 + ob : nullptr,
+        pts ? pts + ob * 4 : nullptr, n_out + p0);
+  }
+  return check_launch("vo_match_hamming_batch(tensor)");
+}
+
 extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp,
-                                      int n_cap, const int32_t* pairs, int n_pairs, int mode,
-                                      double ratio, int32_t* q, int32_t* t, float* dist,
+                                      int n_cap, int n_frames, const int32_t* pairs, int n_pairs,
+                                      int mode, double ratio, int32_t* q, int32_t* t, float* dist,
                                       int32_t* t2, float* dist2, double* pts, int32_t* n_out,
                                       void* ws, size_t ws_bytes, void* stream) {
   VO_REQUIRE(desc && nkp && pairs && q && t && dist && n_out && ws, VO_ERR_INVALID_ARG,
              "vo_match_hamming_batch: null pointer");
-  VO_REQUIRE(n_cap > 0 && n_cap <= 65535 && n_pairs >= 0, VO_ERR_INVALID_ARG,
+  VO_REQUIRE(n_cap > 0 && n_cap <= 65535 && n_pairs >= 0 && n_frames >= 0, VO_ERR_INVALID_ARG,
              "vo_match_hamming_batch: n_cap must be in 1..65535 (got %d)", n_cap);
   VO_REQUIRE(mode == VO_MATCH_MUTUAL || mode == VO_MATCH_KNN2_RATIO, VO_ERR_INVALID_ARG,
              "vo_match_hamming_batch: bad mode %d", mode);
-  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(n_pairs, n_cap), VO_ERR_WORKSPACE,
+  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(n_frames, n_pairs, n_cap), VO_ERR_WORKSPACE,
              "vo_match_hamming_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
+  if (use_tensor_path(n_frames, n_pairs, n_cap, mode))
+    return launch_hamming_tc(desc, nkp, kp, n_cap, n_frames, pairs, n_pairs, mode, ratio, q, t, dist,
+                             t2, dist2, pts, n_out, ws, (cudaStream_t)stream);
   return launch_hamming(desc, nullptr, 0, 0, nkp, kp, n_cap, pairs, n_pairs, mode, ratio, q, t,
                         dist, t2, dist2, pts, n_out, ws, (cudaStream_t)stream);
 }
@@ -401,7 +487,7 @@ extern "C" int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, in
     return check_launch("vo_match_hamming");
   }
   VO_REQUIRE(d1 && d2, VO_ERR_INVALID_ARG, "vo_match_hamming: null descriptors");
-  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(1, n_cap), VO_ERR_WORKSPACE,
+  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(0, 1, n_cap), VO_ERR_WORKSPACE,
              "vo_match_hamming: workspace too small");
   return launch_hamming(d1, d2, n1, n2, nullptr, nullptr, n_cap, nullptr, 1, mode, ratio, q, t,
                         dist, t2, dist2, nullptr, n_out, ws, (cudaStream_t)stream);

@@ -46,11 +46,31 @@ class _Cv2Namespace:
         return orb.OrbDetector(nfeatures, scaleFactor, nlevels, edgeThreshold, fastThreshold)
 
     # ---- headless GUI ----
+    def imread(self, *a, **k):
+        self._idle_polls = 0           # a frame loop is alive (see waitKey)
+        return _real.imread(*a, **k)
+
     def imshow(self, *a, **k):
+        self._idle_polls = 0
         return _real.imshow(*a, **k) if self._gui else None
 
-    def waitKey(self, *a, **k):
-        return _real.waitKey(*a, **k) if self._gui else -1
+    def waitKey(self, delay=0, *a, **k):
+        """Headless: there is no window and no key will ever arrive.  Sleep like cv2 would (capped
+        at 10 ms so frame loops are not slowed) and, after `VO_B200_HEADLESS_QUIT` (default 20)
+        consecutive polls with no imshow in between, answer ord('q'): the reference's
+        `VisualSlam.run` ends with `while True: k = cv2.waitKey(100); if k == ord('q'): break`
+        (src/visual_slam.py:344-349), which would otherwise spin forever."""
+        if self._gui:
+            return _real.waitKey(delay, *a, **k)
+        import os
+        import time
+        time.sleep(min(max(int(delay), 0), 10) * 1e-3)
+        self._idle_polls = getattr(self, "_idle_polls", 0) + 1
+        limit = int(os.environ.get("VO_B200_HEADLESS_QUIT", "20"))
+        if limit > 0 and self._idle_polls >= limit:
+            self._idle_polls = 0
+            return ord("q")
+        return -1
 
     def destroyAllWindows(self, *a, **k):
         return _real.destroyAllWindows(*a, **k) if self._gui else None

@@ -32,8 +32,10 @@ class DMatch:
 
 
 # Device copies of descriptor arrays, keyed by the identity of the host array (a Frame's
-# descriptors are matched twice: as frame2 of one pair, then as frame1 of the next).  Entries die
-# with their array (weakref callback); arrays are treated as immutable once matched.
+# descriptors are matched twice: as frame2 of one pair, then as frame1 of the next).  Only arrays
+# the caller has made READ-ONLY (`a.flags.writeable = False`) are cached: a writable array may be
+# refilled in place between two calls (a video loop reusing one buffer) and cv2.BFMatcher would
+# see the new contents, so it is uploaded on every call.  Entries die with their array.
 _DEV_CACHE = {}
 
 
@@ -41,12 +43,13 @@ def _dev(a, dtype):
     if isinstance(a, torch.Tensor):
         return a.to(device="cuda", dtype=dtype).contiguous()
     key = id(a)
-    hit = _DEV_CACHE.get(key)
+    cacheable = isinstance(a, np.ndarray) and not a.flags.writeable
+    hit = _DEV_CACHE.get(key) if cacheable else None
     if hit is not None and hit[0]() is a and hit[1].dtype == dtype:
         return hit[1]
     t = torch.from_numpy(np.ascontiguousarray(a, dtype={torch.uint8: np.uint8,
                                                         torch.float32: np.float32}[dtype])).cuda()
-    if isinstance(a, np.ndarray):
+    if cacheable:
         try:
             _DEV_CACHE[key] = (weakref.ref(a, lambda _r, k=key: _DEV_CACHE.pop(k, None)), t)
         except TypeError:
@@ -86,7 +89,7 @@ class B200Matcher:
         dist = torch.empty(max(n1, 1), dtype=torch.float32, device=dev)
         dist2 = torch.empty_like(dist)
         n_out = torch.zeros(1, dtype=torch.int32, device=dev)
-        wsb = self.lib.vo_match_workspace_bytes(1, cap)
+        wsb = self.lib.vo_match_workspace_bytes(0, 1, cap)
         ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
         _lib.check(self.lib.vo_match_hamming(
             _lib.ptr(d1), n1, _lib.ptr(d2), n2, mode, float(ratio), _lib.ptr(q), _lib.ptr(t),

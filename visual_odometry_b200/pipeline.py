@@ -57,7 +57,7 @@ class PairPipeline:
         self.poses = e(P + 1, 4, 4, dt=F64)
         # workspaces
         if descriptor == "orb":
-            self.ws_match = e(max(self.lib.vo_match_workspace_bytes(P, N), 256), dt=U8)
+            self.ws_match = e(max(self.lib.vo_match_workspace_bytes(F, P, N), 256), dt=U8)
         else:
             self.ws_match = e(max(self.lib.vo_match_l2_workspace_bytes(F, P, N), 256), dt=U8)
         self.ws_ess = e(max(self.lib.vo_essential_workspace_bytes(P, N, self.max_iters), 256), dt=U8)
@@ -81,7 +81,7 @@ class PairPipeline:
             return
         if self.descriptor == "orb":
             _lib.check(lib.vo_match_hamming_batch(
-                g(self.desc), g(self.nkp), g(self.kp), N, p(self.pairs), B, self.match_mode,
+                g(self.desc), g(self.nkp), g(self.kp), N, self.F, p(self.pairs), B, self.match_mode,
                 self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None, p(self.pts),
                 p(self.n_match), g(self.ws_match), self.ws_match.numel(), st))
         else:
