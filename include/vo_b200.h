@@ -125,13 +125,33 @@ int vo_triangulate_pairs(const double* R, const double* t, const double* pts, co
  * rel_k = [R_k | t_k] of pair k-1. poses float64 [n_pairs+1,16]. */
 int vo_chain_poses(const double* R, const double* t, int n_pairs, const double* P0,
                    double* poses, void* stream);
+/* multi-GPU form of the same chaining (the one collective is an all-gather of the
+ * per-pair [R|t]): vo_pack_poses writes rt float64 [n_pairs,12] = (R row-major, t) rows straight
+ * into the all-gather send buffer; vo_chain_poses_packed chains the gathered rows. */
+int vo_pack_poses(const double* R, const double* t, int n_pairs, double* rt, void* stream);
+int vo_chain_poses_packed(const double* rt, int n_pairs, const double* P0, double* poses,
+                          void* stream);
 
 /* ---- K7: PnP-RANSAC (cv2.solvePnPRansac defaults, visual_slam.py:231-235) ----
- * X [n,3], x [n,2]; out rvec[3], tvec[3], inliers int32 [n], n_inl, ok (device ints). */
+ * X [n,3], x [n,2]; out rvec[3], tvec[3], inliers int32 [n], n_inl, ok (device ints).
+ * n >= 6: RANSAC over 5-point EPnP samples + iterative refit on the inliers; n == 5: EPnP on all
+ * points, n == 4: P3P (three points + the fourth to choose) - OpenCV's solvepnp.cpp takes the
+ * plain-solvePnP route when npoints == model_points: no RANSAC, no refit, every point an inlier. */
 size_t vo_pnp_workspace_bytes(int n, int iters);
 int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int iters,
                   double reproj_px, double conf, double* rvec, double* tvec, int32_t* inliers,
                   int32_t* n_inl, int32_t* ok, void* ws, size_t ws_bytes, void* stream);
+/* batched (BASELINE config C5: "PnP-RANSAC of new frames against the map"): frame f owns rows
+ * offsets[f] .. offsets[f+1]-1 of X [n_total,3] / x [n_total,2] (CSR; offsets int32 [n_frames+1]
+ * on the device).  One launch group for all frames, no host synchronisation.
+ * out: rvec, tvec float64 [n_frames,3]; inliers int32 [n_total]: frame f's inlier indices
+ * (frame-local, ascending) start at inliers[offsets[f]]; n_inl, ok int32 [n_frames]
+ * (ok = 0: fewer than 4 points or no model). */
+size_t vo_pnp_batch_workspace_bytes(long n_total, int n_frames, int iters);
+int vo_pnp_ransac_batch(const double* X, const double* x, const int32_t* offsets, long n_total,
+                        int n_frames, const double* K, int iters, double reproj_px, double conf,
+                        double* rvec, double* tvec, int32_t* inliers, int32_t* n_inl, int32_t* ok,
+                        void* ws, size_t ws_bytes, void* stream);
 
 /* ---- N2: reprojection errors of all map observations (Map.calculate_reprojection_error,
  * Map.remove_observations_with_reprojection_errors_above_threshold; reference src/map.py:46-97,
@@ -263,7 +283,12 @@ int vo_orb_fast_score_map(const uint8_t* images, int n_frames, int width, int he
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).
- * kernel_id: 0 = hamming_top2_kernel (K1), 1 = ransac_score_kernel (K2), 2 = l2 tensor-core GEMM. */
+ * kernel_id: 0 = the Hamming N1 x N2 pass (K1 popc kernel or K1t tcgen05 kernel), 1 = ransac_score_kernel
+ * (K2), 2 = l2 tensor-core GEMM (K6), 3 = ransac_solve_kernel (K3), 4 = K1t operand expansion,
+ * 5 = recover_pose_kernel (K5), 6 = triangulate_pairs_kernel (K4), 7 = chain_kernel,
+ * 8 = match_compact_kernel, 9 = RANSAC control kernels (init / sample / scan / mask).
+ * on: 0 = off, 1 = ids 0..4 only (two event records per scope: cheap enough for a timed region),
+ * 2 = every scope. */
 int vo_profile_enable(int on);
 int vo_profile_read(int kernel_id, double* total_ms, int* launches);
 int vo_measure_popc_peak(double* popc32_per_s, void* stream);

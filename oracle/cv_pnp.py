@@ -194,6 +194,89 @@ def refine_pose(X, x, K, rvec, tvec, iters=30):
     return p[:3].copy(), p[3:].copy()
 
 
+def p3p_solutions(X3, y3):
+    """All real solutions (R, t) of the perspective-three-point problem: X3 [3,3] object points,
+    y3 [3,3] unit bearing vectors of their images.  Grunert's quartic in v = s3 / s1 (Haralick et
+    al. 1994, eq. 6-9; OpenCV's calib3d/src/p3p.cpp solves the same system after Gao et al., any
+    exact P3P has the same solution set), roots by numpy, depths polished by Newton on the three
+    cosine-law equations, pose from the two point triads."""
+    X3, y3 = np.asarray(X3, np.float64), np.asarray(y3, np.float64)
+    a2 = ((X3[1] - X3[2]) ** 2).sum()
+    b2 = ((X3[0] - X3[2]) ** 2).sum()
+    c2 = ((X3[0] - X3[1]) ** 2).sum()
+    ca, cb, cg = y3[1] @ y3[2], y3[0] @ y3[2], y3[0] @ y3[1]
+    if min(a2, b2, c2) <= 0:
+        return []
+    q = (a2 - c2) / b2
+    p_ = (a2 + c2) / b2
+    A4 = (q - 1) ** 2 - 4 * c2 / b2 * ca * ca
+    A3 = 4 * (q * (1 - q) * cb - (1 - p_) * ca * cg + 2 * c2 / b2 * ca * ca * cb)
+    A2 = 2 * (q * q - 1 + 2 * q * q * cb * cb + 2 * (b2 - c2) / b2 * ca * ca
+              - 4 * p_ * ca * cb * cg + 2 * (b2 - a2) / b2 * cg * cg)
+    A1 = 4 * (-q * (1 + q) * cb + 2 * a2 / b2 * cg * cg * cb - (1 - p_) * ca * cg)
+    A0 = (1 + q) ** 2 - 4 * a2 / b2 * cg * cg
+    sols = []
+    for v in np.roots([A4, A3, A2, A1, A0]):
+        if abs(v.imag) > 1e-7 * max(1.0, abs(v.real)) or v.real <= 0:
+            continue
+        v = v.real
+        den = 2 * (cg - v * ca)
+        if abs(den) < 1e-14:
+            continue
+        u = ((q - 1) * v * v - 2 * q * cb * v + 1 + q) / den
+        d1 = 1 + v * v - 2 * v * cb
+        if u <= 0 or d1 <= 0:
+            continue
+        s = np.array([1.0, u, v]) * np.sqrt(b2 / d1)
+        for _ in range(10):                        # Newton polish on the cosine-law system
+            f = np.array([s[1] ** 2 + s[2] ** 2 - 2 * s[1] * s[2] * ca - a2,
+                          s[0] ** 2 + s[2] ** 2 - 2 * s[0] * s[2] * cb - b2,
+                          s[0] ** 2 + s[1] ** 2 - 2 * s[0] * s[1] * cg - c2])
+            J = np.array([[0, 2 * s[1] - 2 * s[2] * ca, 2 * s[2] - 2 * s[1] * ca],
+                          [2 * s[0] - 2 * s[2] * cb, 0, 2 * s[2] - 2 * s[0] * cb],
+                          [2 * s[0] - 2 * s[1] * cg, 2 * s[1] - 2 * s[0] * cg, 0]])
+            try:
+                s = s - np.linalg.solve(J, f)
+            except np.linalg.LinAlgError:
+                break
+        if np.any(s <= 0) or np.abs(f).max() > 1e-6 * max(a2, b2, c2):
+            continue
+        C = y3 * s[:, None]                        # the three points in the camera frame
+
+        def frame(P):
+            e1 = P[1] - P[0]
+            e1 = e1 / np.linalg.norm(e1)
+            e3 = np.cross(e1, P[2] - P[0])
+            e3 = e3 / np.linalg.norm(e3)
+            return np.stack([e1, np.cross(e3, e1), e3], 1)
+        R = frame(C) @ frame(X3).T
+        t = C[0] - R @ X3[0]
+        if not any(np.abs(R - R0).max() < 1e-9 and np.abs(t - t0).max() < 1e-9 for R0, t0 in sols):
+            sols.append((R, t))
+    return sols
+
+
+def solve_p3p_4points(X, x, K):
+    """cv2.solvePnP(..., SOLVEPNP_P3P) on exactly 4 points = what solvePnPRansac does when
+    npoints == 4 (solvepnp.cpp: model_points == npoints -> solvePnP with the RANSAC kernel
+    method): P3P on the first three points, the solution with the smallest squared reprojection
+    error of the fourth wins."""
+    Ki = np.linalg.inv(K)
+    y = (Ki @ np.c_[x, np.ones(len(x))].T).T
+    y3 = y[:3] / np.linalg.norm(y[:3], axis=1, keepdims=True)
+    best, best_e = None, np.inf
+    for R, t in p3p_solutions(X[:3], y3):
+        pc = R @ X[3] + t
+        if pc[2] == 0:
+            continue
+        pr = (K @ (pc / pc[2]))[:2]
+        e = ((pr - x[3]) ** 2).sum()
+        if e < best_e:
+            best, best_e = (R, t), e
+    return best
+
+
+
 def solve_pnp_ransac(X, x, K, iterations=100, reproj_error=8.0, confidence=0.99,
                      return_model=False):
     """cv2.solvePnPRansac(X, x, K, zeros) with default arguments.
@@ -203,6 +286,18 @@ def solve_pnp_ransac(X, x, K, iterations=100, reproj_error=8.0, confidence=0.99,
     n = len(X)
     if n < 4:
         raise ValueError("solvePnPRansac needs >= 4 points")
+    if n == 4 or n == 5:
+        # solvepnp.cpp: model_points == npoints -> plain solvePnP with the RANSAC kernel method
+        # (P3P for 4 points, EPnP for 5), no RANSAC, no iterative refit, every point an inlier
+        try:
+            sol = solve_p3p_4points(X, x, K) if n == 4 else epnp(X, x, K)
+        except np.linalg.LinAlgError:
+            sol = None
+        if sol is None:
+            return False, np.zeros((3, 1)), np.zeros((3, 1)), np.zeros((0, 1), np.int32)
+        out = (True, R_to_rodrigues(sol[0]).reshape(3, 1), np.asarray(sol[1], np.float64).reshape(3, 1),
+               np.arange(n, dtype=np.int32).reshape(-1, 1))
+        return out + ((out[1].ravel(), out[2].ravel()),) if return_model else out
     rng = CvRNG()
     thr = np.float32(reproj_error * reproj_error)
     niters = iterations

@@ -37,3 +37,27 @@ def cuda_dev():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+def record_parity(test, **fields):
+    """Per-test parity counts (mask mismatches, pose deviation on mismatching pairs, ...) merged
+    into one JSON (default gpurun_out/parity.json; copied to profiles/parity_rNN.json): what the
+    parity tests MEASURED, next to what they assert."""
+    import json
+    path = os.environ.get("VO_PARITY_JSON", os.path.join(ROOT, "gpurun_out", "parity.json"))
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        data = json.load(open(path)) if os.path.exists(path) else {}
+        clean = {}
+        for k, v in fields.items():
+            if isinstance(v, (np.integer,)):
+                v = int(v)
+            elif isinstance(v, (np.floating,)):
+                v = float(v)
+            elif isinstance(v, np.ndarray):
+                v = v.tolist()
+            clean[k] = v
+        data[test] = clean
+        json.dump(data, open(path, "w"), indent=1, sort_keys=True)
+    except OSError:
+        pass

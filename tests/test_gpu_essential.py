@@ -10,7 +10,7 @@ from oracle import reference_path as RP
 from visual_odometry_b200 import geometry as G
 from visual_odometry_b200 import image_pair as IP
 from visual_odometry_b200.synth import make_sequence
-from conftest import load_golden, GOLDEN_CASES
+from conftest import record_parity, load_golden, GOLDEN_CASES
 
 pytestmark = pytest.mark.gpu
 
@@ -55,6 +55,8 @@ def test_fivept_matches_cv2_minimal_solver(cuda_dev):
                     for j in range(ncv))
             n_total += 1
             n_close += d < 1e-6
+    record_parity("fivept_vs_cv2_minimal_solver", samples=S, solution_count_mismatches=count_mismatch,
+                  solutions_compared=n_total, solutions_within_1e_6=n_close)
     assert count_mismatch <= 1            # same number of real solutions as OpenCV
     assert n_close >= 0.97 * n_total      # and the same matrices (cv2's own roots are ~1e-6 off
     #                                       on ill-conditioned samples; ours satisfy the constraints)
@@ -106,12 +108,20 @@ def test_batch_vs_cv2_sequence(cuda_dev):
     out = G.find_essential_batch(torch.from_numpy(pts).cuda(), torch.from_numpy(m).cuda(),
                                  torch.from_numpy(K).cuda())
     E, M = out["E"].cpu().numpy(), out["mask"].cpu().numpy()
-    same = 0
+    same, diff_bits, e_dev = 0, [], 0.0
     for b in range(B):
         Ecv, mcv = ref[b]
-        same += np.array_equal(M[b, :m[b]], mcv.ravel())
+        eq = np.array_equal(M[b, :m[b]], mcv.ravel())
+        same += eq
+        if eq:    # same consensus set: E itself agrees up to sign and root-finder accuracy
+            e_dev = max(e_dev, min(np.abs(E[b] - Ecv).max(), np.abs(E[b] + Ecv).max()))
+        else:
+            diff_bits.append(int((M[b, :m[b]] != mcv.ravel()).sum()))
         assert np.all(M[b, m[b]:] == 0)
+    record_parity("essential_batch_vs_cv2_sequence", pairs=B, masks_identical=same,
+                  mismatching_mask_bits=diff_bits, max_abs_E_dev_on_identical=e_dev)
     assert same >= B - 1                      # identical masks to cv2 end to end
+    assert e_dev < 1e-5
     assert np.array_equal(out["n_inl"].cpu().numpy(), M.sum(1))
     assert np.all(out["status"].cpu().numpy() == 0)
 

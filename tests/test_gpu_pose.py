@@ -15,7 +15,7 @@ from visual_odometry_b200.frame import FrameGenerator, SyntheticDetector
 from visual_odometry_b200.matcher import B200Matcher, NORM_HAMMING, NORM_L2
 from visual_odometry_b200.pipeline import PairPipeline
 from visual_odometry_b200.synth import make_sequence
-from conftest import load_golden, GOLDEN_CASES
+from conftest import load_golden, GOLDEN_CASES, record_parity
 
 pytestmark = pytest.mark.gpu
 
@@ -92,10 +92,17 @@ def test_pipeline_sequence_vs_reference_path_and_ground_truth(cuda_dev):
     pipe = PairPipeline(N, F - 1, K=seq.K)
     out = pipe.run_host(seq.desc, seq.kp, seq.nkp, seq.consecutive_pairs())
     Rs, ts = [], []
-    exact = 0
+    exact, off_pairs = 0, []
     for b in range(F - 1):
         ref = RP.pair_cv2(seq.desc[b], seq.kp[b], seq.desc[b + 1], seq.kp[b + 1], seq.K)
         assert out["n_match"][b] == len(ref["q"])
+        n = int(out["n_match"][b])
+        if not np.array_equal(pipe.mask[b, :n].cpu().numpy(), ref["mask"].ravel()):
+            # a different consensus set (an inlier-count tie between two hypotheses, or a
+            # correspondence on the threshold): how far the pose then is from cv2's
+            off_pairs.append({"pair": b, "inliers": [int(out["n_inl"][b]), int(ref["mask"].sum())],
+                              "rot_rad_vs_cv2": float(rot_angle(out["R"][b], ref["R"])),
+                              "t_abs_vs_cv2": float(np.abs(out["t"][b] - ref["tvec"].ravel()).max())})
         if out["n_inl"][b] == int(ref["mask"].sum()):
             exact += 1
             assert rot_angle(out["R"][b], ref["R"]) < ROT_TOL
@@ -107,6 +114,8 @@ def test_pipeline_sequence_vs_reference_path_and_ground_truth(cuda_dev):
         Rg, tg = seq.relative_pose(b, b + 1)
         assert rot_angle(out["R"][b], Rg) < 0.02          # and close to ground truth
         Rs.append(ref["R"]); ts.append(ref["tvec"])
+    record_parity("pipeline_sequence_vs_reference_path", pairs=F - 1, inlier_counts_equal=exact,
+                  pairs_with_different_mask=off_pairs)
     assert exact >= F - 2
     if exact == F - 1:
         assert np.abs(out["poses"] - RP.chain_poses(Rs, ts)).max() < 1e-3
@@ -144,7 +153,7 @@ def test_full_size_c4_batch_vs_reference_path(cuda_dev):
     pipe = PairPipeline(N, F - 1, K=seq.K)
     out = pipe.run_host(seq.desc, seq.kp, seq.nkp, seq.consecutive_pairs())
     assert np.all(out["status"] == 0) and np.all(out["n_match"] > 0.6 * N)
-    exact = 0
+    exact, off_pairs = 0, []
     for b in (0, 11, 23):
         ref = RP.pair_cv2(seq.desc[b], seq.kp[b], seq.desc[b + 1], seq.kp[b + 1], seq.K,
                           cv2.NORM_HAMMING)
@@ -157,4 +166,10 @@ def test_full_size_c4_batch_vs_reference_path(cuda_dev):
             exact += 1
             assert rot_angle(out["R"][b], ref["R"]) < 1e-4
             assert np.abs(out["t"][b] - ref["tvec"].ravel()).max() < 1e-4
+        else:
+            off_pairs.append({"pair": b, "mask_bits": int((pipe.mask[b, :n].cpu().numpy() != ref["mask"].ravel()).sum()),
+                              "rot_rad_vs_cv2": float(rot_angle(out["R"][b], ref["R"])),
+                              "t_abs_vs_cv2": float(np.abs(out["t"][b] - ref["tvec"].ravel()).max())})
+    record_parity("c4_batch_vs_reference_path", pairs_checked=3, masks_identical=exact,
+                  pairs_with_different_mask=off_pairs)
     assert exact >= 2

@@ -50,3 +50,38 @@ def test_pnp_ransac_equals_cv2(seed):
     # model, not under the returned (refit) pose: check the documented behaviour holds here
     err = np.linalg.norm(P.project(X.astype(np.float32).astype(np.float64), r, t, K) - x, axis=1)
     assert abs(int((err <= 8).sum()) - len(inl)) <= 3
+
+
+def test_four_and_five_points_take_the_plain_solvepnp_route():
+    """npoints == 4 -> P3P (+ fourth point), npoints == 5 -> EPnP once; every point an inlier, no
+    refit (solvepnp.cpp: model_points == npoints).  P3P is pinned to 1e-4.  Five-point EPnP is NOT
+    reproducible between two correct implementations (10 x 12 system, two-dimensional null space
+    whose basis is decided by rounding, DESIGN.md section 2: the Gauss-Newton stage can settle in
+    different minima), so there the check is the quality of the fit, not the pose."""
+    rng = np.random.default_rng(3)
+    n_cmp = 0
+    for trial in range(40):
+        X = np.c_[rng.uniform(-5, 5, 4), rng.uniform(-3, 3, 4), rng.uniform(8, 20, 4)]
+        rv, tv = rng.normal(0, 0.1, 3), rng.normal(0, 0.5, 3)
+        x = cv2.projectPoints(X, rv, tv, K, None)[0].reshape(-1, 2) + rng.normal(0, 0.3, (4, 2))
+        ok, r, t, inl = cv2.solvePnPRansac(X, x, K, np.zeros(4))
+        ok2, r2, t2, inl2 = P.solve_pnp_ransac(X, x, K)
+        if not (ok and np.all(np.isfinite(t))):
+            assert not ok2
+            continue
+        assert ok2 and np.array_equal(inl, inl2)
+        R1, R2 = cv2.Rodrigues(r)[0], cv2.Rodrigues(r2)[0]
+        assert np.arccos(np.clip((np.trace(R1.T @ R2) - 1) / 2, -1, 1)) < 1e-4
+        assert np.abs(t - t2).max() < 1e-4
+        n_cmp += 1
+    assert n_cmp >= 35
+    for trial in range(10):
+        X = np.c_[rng.uniform(-5, 5, 5), rng.uniform(-3, 3, 5), rng.uniform(8, 20, 5)]
+        rv, tv = rng.normal(0, 0.1, 3), rng.normal(0, 0.5, 3)
+        x = cv2.projectPoints(X, rv, tv, K, None)[0].reshape(-1, 2) + rng.normal(0, 0.3, (5, 2))
+        ok, r, t, inl = cv2.solvePnPRansac(X, x, K, np.zeros(4))
+        ok2, r2, t2, inl2 = P.solve_pnp_ransac(X, x, K)
+        assert ok and ok2 and np.array_equal(inl, inl2)
+        e1 = np.linalg.norm(cv2.projectPoints(X, r, t, K, None)[0].reshape(-1, 2) - x, axis=1).mean()
+        e2 = np.linalg.norm(cv2.projectPoints(X, r2, t2, K, None)[0].reshape(-1, 2) - x, axis=1).mean()
+        assert e2 < 2.0 * e1 + 0.5       # an equally good explanation of the five observations

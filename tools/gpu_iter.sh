@@ -1,8 +1,11 @@
 #!/bin/bash
-# one quick GPU-box call while iterating on K1t (tensor-core Hamming)
+# one GPU-box call while iterating: parity tests of the touched kernels, bench, launch list, K1t capture
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm --format=csv > gpurun_out/gpu.txt
-timeout 600 python -m pytest tests/test_gpu_match.py -x -q > gpurun_out/pytest_match.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_match.log
-timeout 300 python tools/gpu_check_hamming.py > gpurun_out/hamming_check.log 2>&1; echo "rc=$?" >> gpurun_out/hamming_check.log
-timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "rc=$?" >> gpurun_out/bench.err
-tail -5 gpurun_out/pytest_match.log; tail -20 gpurun_out/hamming_check.log; cat gpurun_out/bench.json | head -c 1500
+timeout 900 python -m pytest tests/test_gpu_match.py tests/test_gpu_pnp.py tests/test_gpu_pose.py tests/test_gpu_config_c5.py tests/test_gpu_essential.py tests/test_gpu_slam.py tests/test_gpu_device_map.py -x -q > gpurun_out/pytest_iter.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_iter.log
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "rc=$?" >> gpurun_out/bench.err
+if [ "$1" = "ncu" ]; then
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_bench_c2.csv python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_launch.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 3 -c 1 -o gpurun_out/k1t_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1t.log 2>&1
+fi
+tail -5 gpurun_out/pytest_iter.log; tail -3 gpurun_out/bench.err; head -c 6000 gpurun_out/bench.json

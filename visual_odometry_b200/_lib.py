@@ -53,11 +53,15 @@ SIGNATURES = {
     "vo_triangulate": (_i, [_p, _p, _p, _p, _i, _p, _i, _p]),
     "vo_triangulate_pairs": (_i, [_p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p]),
     "vo_chain_poses": (_i, [_p, _p, _i, _p, _p, _p]),
+    "vo_pack_poses": (_i, [_p, _p, _i, _p, _p]),
+    "vo_chain_poses_packed": (_i, [_p, _i, _p, _p, _p]),
     "vo_profile_enable": (_i, [_i]),
     "vo_profile_read": (_i, [_i, _p, _p]),
     "vo_measure_popc_peak": (_i, [_p, _p]),
     "vo_pnp_workspace_bytes": (_sz, [_i, _i]),
     "vo_pnp_ransac": (_i, [_p, _p, _i, _p, _i, _d, _d, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vo_pnp_batch_workspace_bytes": (_sz, [C.c_long, _i, _i]),
+    "vo_pnp_ransac_batch": (_i, [_p, _p, _p, C.c_long, _i, _p, _i, _d, _d, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_tracks_reset": (_i, [_p, _p, _p, C.c_long, _p]),
     "vo_tracks_update": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "vo_tracks_set_points": (_i, [_p, _p, _i, _p, _p]),

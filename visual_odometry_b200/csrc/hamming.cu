@@ -398,6 +398,7 @@ static int launch_hamming(const uint8_t* desc, const uint8_t* desc2, int n1d, in
                                                          splits, rb, cm);
     }
     const size_t ob = (size_t)p0 * n_cap;
+    ProfScope prof_c(8, st);
     match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
         rb, cm, nkp, kp, n_cap, pp, n1d, n2d, splits, mode, ratio, q + ob, t + ob, dist + ob,
         t2 ? t2 + ob : nullptr, dist2 ? dist2 + ob : nullptr, pts ? pts + ob * 4 : nullptr,
@@ -443,6 +444,7 @@ static int launch_hamming_tc(const uint8_t* desc, const int32_t* nkp, const floa
   for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
     const int np = n_pairs - p0 < 65535 ? n_pairs - p0 : 65535;
     const size_t ob = (size_t)p0 * n_cap;
+    ProfScope prof_c(8, st);
     match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
         w.rowbest + ob * 2, w.colmin + ob, nkp, kp, n_cap, pairs + 2 * p0, 0, 0, 1, mode, ratio, q + ob,
         t + ob, dist + ob, t2 ? t2 + ob : nullptr, dist2 ? dist2 + ob : nullptr,

@@ -81,6 +81,69 @@ __device__ __forceinline__ void null_vector4(double (&A)[4][4], double (&x)[4]) 
     x[k] = (bj == 0) ? V[k][0] : (bj == 1) ? V[k][1] : (bj == 2) ? V[k][2] : V[k][3];
 }
 
+// full-precision reciprocal: MUFU seed + two Newton steps
+__device__ __forceinline__ double rcp_full(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = r * (2.0 - x * r);
+  return fma(r, fma(-x, r, 1.0), r);
+}
+
+// The same vector ~8x cheaper: the smallest right singular vector of A is the eigenvector of the
+// smallest eigenvalue of B = A^T A, and for a DLT matrix that eigenvalue is separated from the
+// next by the square of (noise / parallax), so inverse iteration on an LDL^T factorisation of B
+// converges in 2-4 steps (error ratio lambda_4 / lambda_3 per step).  Accuracy: the factorisation
+// is backward stable for a symmetric positive definite B, the fixed point is the eigenvector of
+// B + dB with |dB| <= c eps |B|, i.e. within eps sigma_1^2 / (sigma_3^2 - sigma_4^2) of the true
+// one (~1e-13 for the geometries of this path; Jacobi on A itself: ~1e-15).  Points that have not
+// settled to 1e-14 after 16 steps (sigma_4 ~ sigma_3: no parallax at all) return false and take
+// the Jacobi route, whose answer they then share with OpenCV to rounding.
+__device__ __forceinline__ bool null_vector4_invit(const double (&A)[4][4], double (&x)[4]) {
+  double b[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = i; j < 4; ++j)
+      b[i][j] = fma(A[0][i], A[0][j], fma(A[1][i], A[1][j], fma(A[2][i], A[2][j], A[3][i] * A[3][j])));
+  const double tiny = 1e-300 + 1e-34 * (b[0][0] + b[1][1] + b[2][2] + b[3][3]);
+  // B = L D L^T
+  const double d0 = fmax(b[0][0], tiny), i0 = rcp_full(d0);
+  const double l10 = b[0][1] * i0, l20 = b[0][2] * i0, l30 = b[0][3] * i0;
+  const double d1 = fmax(fma(-l10, b[0][1], b[1][1]), tiny), i1 = rcp_full(d1);
+  const double t21 = fma(-l20, b[0][1], b[1][2]), t31 = fma(-l30, b[0][1], b[1][3]);
+  const double l21 = t21 * i1, l31 = t31 * i1;
+  const double d2 = fmax(fma(-l21, t21, fma(-l20, b[0][2], b[2][2])), tiny), i2 = rcp_full(d2);
+  const double t32 = fma(-l31, t21, fma(-l30, b[0][2], b[2][3]));
+  const double l32 = t32 * i2;
+  const double d3r = fma(-l32, t32, fma(-l31, t31, fma(-l30, b[0][3], b[3][3])));
+  const double d3 = fmax(d3r, tiny), i3 = rcp_full(d3);
+  double v0 = 0.5, v1 = 0.5, v2 = 0.5, v3 = 0.5;
+  bool settled = false;
+  for (int it = 0; it < 16; ++it) {
+    // solve L D L^T y = v
+    const double z0 = v0;
+    const double z1 = fma(-l10, z0, v1);
+    const double z2 = fma(-l21, z1, fma(-l20, z0, v2));
+    const double z3 = fma(-l32, z2, fma(-l31, z1, fma(-l30, z0, v3)));
+    double y3 = z3 * i3;
+    double y2 = fma(-l32, y3, z2 * i2);
+    double y1 = fma(-l31, y3, fma(-l21, y2, z1 * i1));
+    double y0 = fma(-l30, y3, fma(-l20, y2, fma(-l10, y1, z0 * i0)));
+    const double n2 = fma(y0, y0, fma(y1, y1, fma(y2, y2, y3 * y3)));
+    const double dot = fma(y0, v0, fma(y1, v1, fma(y2, v2, y3 * v3)));
+    const double inv = copysign(rsqrt(n2), dot);    // keep the sign of the previous iterate
+    y0 *= inv; y1 *= inv; y2 *= inv; y3 *= inv;
+    const double e0 = y0 - v0, e1 = y1 - v1, e2 = y2 - v2, e3 = y3 - v3;
+    const double dd = fma(e0, e0, fma(e1, e1, fma(e2, e2, e3 * e3)));
+    v0 = y0; v1 = y1; v2 = y2; v3 = y3;
+    if (settled) break;                 // one more step after the iterates agree to 1e-14
+    if (dd < 1e-28) settled = true;
+    if (!(n2 < 1e300)) break;           // overflow guard (exactly singular B): direction is exact
+  }
+  x[0] = v0; x[1] = v1; x[2] = v2; x[3] = v3;
+  return settled;
+}
+
 // cv::triangulatePoints for one point: rows x*P[2]-P[0], y*P[2]-P[1] for both cameras.
 __device__ __forceinline__ void dlt_point(const double* __restrict__ P1,
                                           const double* __restrict__ P2, double x1, double y1,
@@ -93,6 +156,7 @@ __device__ __forceinline__ void dlt_point(const double* __restrict__ P1,
     A[2][k] = x2 * P2[8 + k] - P2[k];
     A[3][k] = y2 * P2[8 + k] - P2[4 + k];
   }
+  if (null_vector4_invit(A, X)) return;
   null_vector4(A, X);
 }
 

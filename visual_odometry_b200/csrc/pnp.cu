@@ -20,18 +20,19 @@ namespace vo {
 constexpr int PNP_MAX_ITERS = 1024;
 
 struct PnpWs {
-  double* Xf;         // [n][3] float32-rounded object points
-  double* xf;         // [n][2] float32-rounded image points
-  double* models;     // [iters][12]  R (9) + t (3)
-  int32_t* samples;   // [iters][5]
-  int32_t* counts;    // [iters]
-  int32_t* valid;     // [iters]
-  int32_t* best;      // [4] best index, niters, max_good, n_inl
-  uint8_t* mask;      // [n]
+  double* Xf;         // [n_total][3] float32-rounded object points
+  double* xf;         // [n_total][2] float32-rounded image points
+  double* models;     // [F][iters][12]  R (9) + t (3)
+  int32_t* samples;   // [F][iters][5]
+  int32_t* counts;    // [F][iters]
+  int32_t* valid;     // [F][iters]
+  int32_t* best;      // [F][4] best index, niters, max_good, n_inl
+  uint8_t* mask;      // [n_total]
+  int iters;
   size_t bytes;
 };
 
-static PnpWs pnp_carve(void* base, int n, int iters) {
+static PnpWs pnp_carve(void* base, long n_total, int n_frames, int iters) {
   PnpWs w;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -39,17 +40,32 @@ static PnpWs pnp_carve(void* base, int n, int iters) {
     off += (bytes + 255) & ~(size_t)255;
     return p;
   };
-  w.Xf = (double*)take((size_t)n * 3 * sizeof(double));
-  w.xf = (double*)take((size_t)n * 2 * sizeof(double));
-  w.models = (double*)take((size_t)iters * 12 * sizeof(double));
-  w.samples = (int32_t*)take((size_t)iters * 5 * sizeof(int32_t));
-  w.counts = (int32_t*)take((size_t)iters * sizeof(int32_t));
-  w.valid = (int32_t*)take((size_t)iters * sizeof(int32_t));
-  w.best = (int32_t*)take(4 * sizeof(int32_t));
-  w.mask = (uint8_t*)take((size_t)n);
+  const size_t fi = (size_t)n_frames * iters;
+  w.Xf = (double*)take((size_t)n_total * 3 * sizeof(double));
+  w.xf = (double*)take((size_t)n_total * 2 * sizeof(double));
+  w.models = (double*)take(fi * 12 * sizeof(double));
+  w.samples = (int32_t*)take(fi * 5 * sizeof(int32_t));
+  w.counts = (int32_t*)take(fi * sizeof(int32_t));
+  w.valid = (int32_t*)take(fi * sizeof(int32_t));
+  w.best = (int32_t*)take((size_t)n_frames * 4 * sizeof(int32_t));
+  w.mask = (uint8_t*)take((size_t)n_total);
+  w.iters = iters;
   w.bytes = off;
   return w;
 }
+
+// frame f of a batch: observations [base, base + n) of the concatenated arrays.  off == nullptr:
+// a single problem of n_single observations.
+struct PnpFrame { int base, n; };
+__device__ __forceinline__ PnpFrame pnp_frame(const int32_t* __restrict__ off, int n_single, int f) {
+  PnpFrame fr;
+  fr.base = off ? off[f] : 0;
+  fr.n = off ? off[f + 1] - off[f] : n_single;
+  return fr;
+}
+// solvepnp.cpp: npoints == model_points -> one plain solvePnP call, no RANSAC: 4 points P3P,
+// 5 points EPnP; fewer than 4: error
+__device__ __forceinline__ bool pnp_is_ransac(int n) { return n >= 6; }
 
 // ------------------------------------------------------------------ small dense helpers (runtime sizes)
 // cyclic Jacobi eigen-decomposition of a symmetric n x n matrix (row-major, destroyed);
@@ -395,11 +411,157 @@ __device__ bool epnp5(Epnp5& E, const double* K, double* R, double* t, Jac12Smem
   return true;
 }
 
-// ------------------------------------------------------------------ kernels
-__global__ void pnp_prepare_kernel(const double* __restrict__ X, const double* __restrict__ x, int n,
-                                   PnpWs w) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+// ------------------------------------------------------------------ P3P (the npoints == 4 case)
+struct Cplx { double re, im; };
+__device__ __forceinline__ Cplx cmul(Cplx a, Cplx b) { return {a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }
+__device__ __forceinline__ Cplx cdiv(Cplx a, Cplx b) {
+  const double d = b.re * b.re + b.im * b.im;
+  return {(a.re * b.re + a.im * b.im) / d, (a.im * b.re - a.re * b.im) / d};
+}
+// the four roots of c[4] v^4 + ... + c[0] (c[4] != 0): Durand-Kerner from a circle of the Cauchy
+// bound radius
+__device__ void quartic_roots(const double* c, Cplx* z) {
+  double a[4], bound = 0.0;
+  for (int k = 0; k < 4; ++k) { a[k] = c[k] / c[4]; bound = fmax(bound, fabs(a[k])); }
+  bound += 1.0;
+  for (int k = 0; k < 4; ++k) {
+    const double ang = 0.4 + 1.5707963267948966 * k;
+    z[k] = {0.5 * bound * cos(ang), 0.5 * bound * sin(ang)};
+  }
+  for (int it = 0; it < 200; ++it) {
+    double moved = 0.0;
+    for (int k = 0; k < 4; ++k) {
+      Cplx pv = {1.0, 0.0};
+      for (int d = 3; d >= 0; --d) { pv = cmul(pv, z[k]); pv.re += a[d]; }
+      Cplx den = {1.0, 0.0};
+      for (int m = 0; m < 4; ++m)
+        if (m != k) den = cmul(den, Cplx{z[k].re - z[m].re, z[k].im - z[m].im});
+      if (den.re == 0.0 && den.im == 0.0) den.re = 1e-300;
+      const Cplx st = cdiv(pv, den);
+      z[k].re -= st.re; z[k].im -= st.im;
+      moved = fmax(moved, fabs(st.re) + fabs(st.im));
+    }
+    if (moved < 1e-15 * bound) break;
+  }
+}
+
+// rotation taking the triad of X to the triad of C (frames from P0->P1 and the plane normal)
+__device__ void triad_frame(const double (*P)[3], double* F /*3x3 columns e1,e2,e3*/) {
+  double e1[3], d2[3], e3[3], e2[3];
+  for (int k = 0; k < 3; ++k) { e1[k] = P[1][k] - P[0][k]; d2[k] = P[2][k] - P[0][k]; }
+  double n = rsqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
+  for (int k = 0; k < 3; ++k) e1[k] *= n;
+  e3[0] = e1[1] * d2[2] - e1[2] * d2[1]; e3[1] = e1[2] * d2[0] - e1[0] * d2[2]; e3[2] = e1[0] * d2[1] - e1[1] * d2[0];
+  n = rsqrt(e3[0] * e3[0] + e3[1] * e3[1] + e3[2] * e3[2]);
+  for (int k = 0; k < 3; ++k) e3[k] *= n;
+  e2[0] = e3[1] * e1[2] - e3[2] * e1[1]; e2[1] = e3[2] * e1[0] - e3[0] * e1[2]; e2[2] = e3[0] * e1[1] - e3[1] * e1[0];
+  for (int k = 0; k < 3; ++k) { F[3 * k] = e1[k]; F[3 * k + 1] = e2[k]; F[3 * k + 2] = e3[k]; }
+}
+
+// cv2.solvePnP(SOLVEPNP_P3P) on exactly four points: Grunert's quartic in v = s3 / s1 on the first
+// three (any exact P3P has the same solution set as OpenCV's p3p.cpp), depths polished by Newton
+// on the cosine-law system, pose from the two triads; the solution with the smallest squared
+// reprojection error of the FOURTH point wins.  false = no real solution with positive depths.
+__device__ bool pnp_p3p4(const double* __restrict__ Xf, const double* __restrict__ xf,
+                         const double* __restrict__ K, double* R, double* t) {
+  const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+  double y[3][3], X3[3][3];
+  for (int i = 0; i < 3; ++i) {
+    const double a = (xf[2 * i] - cx) / fx, b = (xf[2 * i + 1] - cy) / fy;
+    const double n = rsqrt(a * a + b * b + 1.0);
+    y[i][0] = a * n; y[i][1] = b * n; y[i][2] = n;
+    for (int k = 0; k < 3; ++k) X3[i][k] = Xf[3 * i + k];
+  }
+  auto d2 = [&](int i, int j) {
+    double s = 0.0;
+    for (int k = 0; k < 3; ++k) s += (X3[i][k] - X3[j][k]) * (X3[i][k] - X3[j][k]);
+    return s;
+  };
+  auto dt = [&](int i, int j) { return y[i][0] * y[j][0] + y[i][1] * y[j][1] + y[i][2] * y[j][2]; };
+  const double a2 = d2(1, 2), b2 = d2(0, 2), c2 = d2(0, 1);
+  const double ca = dt(1, 2), cb = dt(0, 2), cg = dt(0, 1);
+  if (!(a2 > 0.0) || !(b2 > 0.0) || !(c2 > 0.0)) return false;
+  const double q = (a2 - c2) / b2, pp = (a2 + c2) / b2;
+  double c[5];
+  c[4] = (q - 1) * (q - 1) - 4 * c2 / b2 * ca * ca;
+  c[3] = 4 * (q * (1 - q) * cb - (1 - pp) * ca * cg + 2 * c2 / b2 * ca * ca * cb);
+  c[2] = 2 * (q * q - 1 + 2 * q * q * cb * cb + 2 * (b2 - c2) / b2 * ca * ca - 4 * pp * ca * cb * cg +
+              2 * (b2 - a2) / b2 * cg * cg);
+  c[1] = 4 * (-q * (1 + q) * cb + 2 * a2 / b2 * cg * cg * cb - (1 - pp) * ca * cg);
+  c[0] = (1 + q) * (1 + q) - 4 * a2 / b2 * cg * cg;
+  const double cmax = fmax(fmax(fabs(c[0]), fabs(c[1])), fmax(fabs(c[2]), fmax(fabs(c[3]), fabs(c[4]))));
+  if (!(fabs(c[4]) > 1e-14 * cmax)) return false;
+  Cplx z[4];
+  quartic_roots(c, z);
+  bool have = false;
+  double best_e = 0.0;
+  for (int r = 0; r < 4; ++r) {
+    const double v = z[r].re;
+    if (fabs(z[r].im) > 1e-7 * fmax(1.0, fabs(v)) || !(v > 0.0)) continue;
+    const double den = 2 * (cg - v * ca);
+    if (fabs(den) < 1e-14) continue;
+    const double u = ((q - 1) * v * v - 2 * q * cb * v + 1 + q) / den;
+    const double d1 = 1 + v * v - 2 * v * cb;
+    if (!(u > 0.0) || !(d1 > 0.0)) continue;
+    double sd[3];
+    sd[0] = sqrt(b2 / d1); sd[1] = u * sd[0]; sd[2] = v * sd[0];
+    double f[3] = {0, 0, 0};
+    for (int it = 0; it < 10; ++it) {
+      f[0] = sd[1] * sd[1] + sd[2] * sd[2] - 2 * sd[1] * sd[2] * ca - a2;
+      f[1] = sd[0] * sd[0] + sd[2] * sd[2] - 2 * sd[0] * sd[2] * cb - b2;
+      f[2] = sd[0] * sd[0] + sd[1] * sd[1] - 2 * sd[0] * sd[1] * cg - c2;
+      const double J[9] = {0, 2 * sd[1] - 2 * sd[2] * ca, 2 * sd[2] - 2 * sd[1] * ca,
+                           2 * sd[0] - 2 * sd[2] * cb, 0, 2 * sd[2] - 2 * sd[0] * cb,
+                           2 * sd[0] - 2 * sd[1] * cg, 2 * sd[1] - 2 * sd[0] * cg, 0};
+      const double det = J[0] * (J[4] * J[8] - J[5] * J[7]) - J[1] * (J[3] * J[8] - J[5] * J[6]) +
+                         J[2] * (J[3] * J[7] - J[4] * J[6]);
+      if (fabs(det) < 1e-300) break;
+      // Cramer
+      const double dx = (f[0] * (J[4] * J[8] - J[5] * J[7]) - J[1] * (f[1] * J[8] - J[5] * f[2]) +
+                         J[2] * (f[1] * J[7] - J[4] * f[2])) / det;
+      const double dy = (J[0] * (f[1] * J[8] - J[5] * f[2]) - f[0] * (J[3] * J[8] - J[5] * J[6]) +
+                         J[2] * (J[3] * f[2] - f[1] * J[6])) / det;
+      const double dz = (J[0] * (J[4] * f[2] - f[1] * J[7]) - J[1] * (J[3] * f[2] - f[1] * J[6]) +
+                         f[0] * (J[3] * J[7] - J[4] * J[6])) / det;
+      sd[0] -= dx; sd[1] -= dy; sd[2] -= dz;
+    }
+    f[0] = sd[1] * sd[1] + sd[2] * sd[2] - 2 * sd[1] * sd[2] * ca - a2;
+    f[1] = sd[0] * sd[0] + sd[2] * sd[2] - 2 * sd[0] * sd[2] * cb - b2;
+    f[2] = sd[0] * sd[0] + sd[1] * sd[1] - 2 * sd[0] * sd[1] * cg - c2;
+    const double fmx = fmax(fabs(f[0]), fmax(fabs(f[1]), fabs(f[2])));
+    if (!(sd[0] > 0 && sd[1] > 0 && sd[2] > 0) || !(fmx <= 1e-6 * fmax(a2, fmax(b2, c2)))) continue;
+    double C[3][3], FC[9], FX[9], Rc[9], tc[3];
+    for (int i = 0; i < 3; ++i)
+      for (int k = 0; k < 3; ++k) C[i][k] = y[i][k] * sd[i];
+    triad_frame(C, FC);
+    triad_frame(X3, FX);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        Rc[3 * i + j] = FC[3 * i] * FX[3 * j] + FC[3 * i + 1] * FX[3 * j + 1] + FC[3 * i + 2] * FX[3 * j + 2];
+    for (int i = 0; i < 3; ++i)
+      tc[i] = C[0][i] - (Rc[3 * i] * X3[0][0] + Rc[3 * i + 1] * X3[0][1] + Rc[3 * i + 2] * X3[0][2]);
+    // fourth point
+    const double* X4 = Xf + 9;
+    const double px = Rc[0] * X4[0] + Rc[1] * X4[1] + Rc[2] * X4[2] + tc[0];
+    const double py = Rc[3] * X4[0] + Rc[4] * X4[1] + Rc[5] * X4[2] + tc[1];
+    const double pz = Rc[6] * X4[0] + Rc[7] * X4[1] + Rc[8] * X4[2] + tc[2];
+    if (pz == 0.0) continue;
+    const double eu = fx * px / pz + cx - xf[6], ev = fy * py / pz + cy - xf[7];
+    const double e = eu * eu + ev * ev;
+    if (!have || e < best_e) {
+      have = true; best_e = e;
+      for (int k = 0; k < 9; ++k) R[k] = Rc[k];
+      for (int k = 0; k < 3; ++k) t[k] = tc[k];
+    }
+  }
+  return have;
+}
+
+// ------------------------------------------------------------------ kernels (grid.y = frame)
+__global__ void pnp_prepare_kernel(const double* __restrict__ X, const double* __restrict__ x,
+                                   long n_total, PnpWs w) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_total) return;
   // solvePnPRansac converts its inputs to CV_32F before anything else
   for (int k = 0; k < 3; ++k) w.Xf[3 * i + k] = (double)__double2float_rn(X[3 * i + k]);
   for (int k = 0; k < 2; ++k) w.xf[2 * i + k] = (double)__double2float_rn(x[2 * i + k]);
@@ -410,46 +572,66 @@ __device__ __forceinline__ uint32_t pnp_rng_next(uint64_t& s) {
   return (uint32_t)s;
 }
 
-__global__ void pnp_sample_kernel(int n, int iters, PnpWs w) {
-  if (blockIdx.x || threadIdx.x) return;
+// one thread per frame replays cv::RNG(2^64-1) for its point count
+__global__ void pnp_sample_kernel(const int32_t* __restrict__ off, int n_single, int n_frames,
+                                  PnpWs w) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_frames) return;
+  const PnpFrame fr = pnp_frame(off, n_single, f);
+  if (!pnp_is_ransac(fr.n)) return;
+  const int iters = w.iters;
+  int32_t* out = w.samples + (size_t)f * iters * 5;
   uint64_t s = 0xffffffffffffffffull;
   for (int it = 0; it < iters; ++it) {
     int32_t idx[5];
     for (int i = 0; i < 5;) {
-      const int v = (int)(pnp_rng_next(s) % (uint32_t)n);
+      const int v = (int)(pnp_rng_next(s) % (uint32_t)fr.n);
       bool dup = false;
       for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
       idx[i] = v;
       if (!dup) ++i;
     }
-    for (int k = 0; k < 5; ++k) w.samples[5 * it + k] = idx[k];
+    for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
   }
 }
 
 // one WARP per RANSAC iteration: EPnP on its 5-point sample.  All lanes carry the hypothesis
 // (identical scalar work, same latency as one thread); the 12x12 eigen-decomposition, which is
 // ~90 % of the serial solve, is spread over the lanes in shared memory.
+// Frames with 4 or 5 observations have ONE hypothesis (iteration 0): P3P / EPnP on all points.
 constexpr int PNP_SOLVE_WARPS = 4;
 __global__ void __launch_bounds__(PNP_SOLVE_WARPS * 32)
-pnp_solve_kernel(const double* __restrict__ K, int iters, PnpWs w) {
+pnp_solve_kernel(const double* __restrict__ K, const int32_t* __restrict__ off, int n_single, PnpWs w) {
   __shared__ Jac12Smem sm[PNP_SOLVE_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int it = blockIdx.x * PNP_SOLVE_WARPS + warp;
+  const int it = blockIdx.x * PNP_SOLVE_WARPS + warp, f = blockIdx.y;
+  const int iters = w.iters;
   if (it >= iters) return;
-  Epnp5 E;
-  for (int p = 0; p < 5; ++p) {
-    const int i = w.samples[5 * it + p];
-    for (int k = 0; k < 3; ++k) E.X[p][k] = w.Xf[3 * i + k];
-    for (int k = 0; k < 2; ++k) E.u[p][k] = w.xf[2 * i + k];
+  const PnpFrame fr = pnp_frame(off, n_single, f);
+  const size_t hyp = (size_t)f * iters + it;
+  if (!pnp_is_ransac(fr.n) && (it > 0 || fr.n < 4)) {
+    if (lane == 0) w.valid[hyp] = 0;
+    return;
   }
   double Kl[9], R[9], t[3];
   for (int e = 0; e < 9; ++e) Kl[e] = K[e];
-  const bool ok = epnp5(E, Kl, R, t, sm[warp]);
+  bool ok;
+  if (fr.n == 4) {
+    ok = pnp_p3p4(w.Xf + 3 * (size_t)fr.base, w.xf + 2 * (size_t)fr.base, Kl, R, t);
+  } else {
+    Epnp5 E;
+    for (int p = 0; p < 5; ++p) {
+      const int i = fr.base + (fr.n == 5 ? p : w.samples[hyp * 5 + p]);
+      for (int k = 0; k < 3; ++k) E.X[p][k] = w.Xf[3 * (size_t)i + k];
+      for (int k = 0; k < 2; ++k) E.u[p][k] = w.xf[2 * (size_t)i + k];
+    }
+    ok = epnp5(E, Kl, R, t, sm[warp]);
+  }
   if (lane == 0) {
-    w.valid[it] = ok ? 1 : 0;
+    w.valid[hyp] = ok ? 1 : 0;
     if (ok) {
-      for (int e = 0; e < 9; ++e) w.models[12 * it + e] = R[e];
-      for (int e = 0; e < 3; ++e) w.models[12 * it + 9 + e] = t[e];
+      for (int e = 0; e < 9; ++e) w.models[12 * hyp + e] = R[e];
+      for (int e = 0; e < 3; ++e) w.models[12 * hyp + 9 + e] = t[e];
     }
   }
 }
@@ -472,17 +654,23 @@ __device__ __forceinline__ float pnp_error(const double* __restrict__ Rt, const 
 }
 
 __global__ void __launch_bounds__(256)
-pnp_score_kernel(const double* __restrict__ K, int n, int iters, float thr2, PnpWs w) {
-  const int it = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+pnp_score_kernel(const double* __restrict__ K, const int32_t* __restrict__ off, int n_single,
+                 float thr2, PnpWs w) {
+  const int it = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31, f = blockIdx.y;
+  const int iters = w.iters;
   if (it >= iters) return;
-  if (!w.valid[it]) { if (lane == 0) w.counts[it] = 0; return; }
+  const PnpFrame fr = pnp_frame(off, n_single, f);
+  const size_t hyp = (size_t)f * iters + it;
+  if (!pnp_is_ransac(fr.n) || !w.valid[hyp]) { if (lane == 0) w.counts[hyp] = 0; return; }
   double Rt[12], Kl[9];
-  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * it + e];
+  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * hyp + e];
   for (int e = 0; e < 9; ++e) Kl[e] = K[e];
+  const double* Xb = w.Xf + 3 * (size_t)fr.base;
+  const double* xb = w.xf + 2 * (size_t)fr.base;
   int cnt = 0;
-  for (int i = lane; i < n; i += 32) cnt += pnp_error(Rt, Kl, w.Xf + 3 * i, w.xf + 2 * i) <= thr2;
+  for (int i = lane; i < fr.n; i += 32) cnt += pnp_error(Rt, Kl, Xb + 3 * i, xb + 2 * i) <= thr2;
   for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-  if (lane == 0) w.counts[it] = cnt;
+  if (lane == 0) w.counts[hyp] = cnt;
 }
 
 __device__ int pnp_update_num_iters(double p, double ep, int model_points, int max_iters) {
@@ -496,49 +684,69 @@ __device__ int pnp_update_num_iters(double p, double ep, int model_points, int m
   return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
 }
 
-// ordered scan (OpenCV's sequential rule) + inlier mask of the winner + ascending index list
+// ordered scan (OpenCV's sequential rule) + inlier mask of the winner + ascending index list.
+// One block per frame; inliers of frame f are written at inliers[base ...] (frame-local indices).
 __global__ void __launch_bounds__(1024)
-pnp_select_kernel(const double* __restrict__ K, int n, int iters, double conf, float thr2, PnpWs w,
-                  int32_t* __restrict__ inliers, int32_t* __restrict__ n_inl, int32_t* __restrict__ ok) {
+pnp_select_kernel(const double* __restrict__ K, const int32_t* __restrict__ off, int n_single,
+                  double conf, float thr2, PnpWs w, int32_t* __restrict__ inliers,
+                  int32_t* __restrict__ n_inl, int32_t* __restrict__ ok) {
   __shared__ int s_best, s_base, warp_tot[32];
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, f = blockIdx.x;
+  const PnpFrame fr = pnp_frame(off, n_single, f);
+  const int n = fr.n, iters = w.iters;
+  const size_t h0 = (size_t)f * iters;
+  int32_t* best4 = w.best + 4 * f;
+  int32_t* inl = inliers + fr.base;
+  if (!pnp_is_ransac(n)) {
+    // 4 or 5 points: the single solvePnP model, every point reported as an inlier, no refit
+    const bool good = n >= 4 && w.valid[h0];
+    if (tid == 0) {
+      best4[0] = good ? 0 : -1; best4[1] = 0; best4[2] = good ? n : 0; best4[3] = -1;   // -1: skip the refit
+      n_inl[f] = good ? n : 0;
+      ok[f] = good ? 1 : 0;
+    }
+    if (good && tid < n) inl[tid] = tid;
+    return;
+  }
   if (tid == 0) {
     int niters = iters, maxgood = 0, best = -1;
     for (int it = 0; it < iters && it < niters; ++it) {
-      const int c = w.counts[it];
-      if (w.valid[it] && c > max(maxgood, 4)) {
+      const int c = w.counts[h0 + it];
+      if (w.valid[h0 + it] && c > max(maxgood, 4)) {
         maxgood = c; best = it;
         niters = pnp_update_num_iters(conf, (double)(n - c) / n, 5, niters);
       }
     }
     s_best = best; s_base = 0;
-    w.best[0] = best; w.best[1] = niters; w.best[2] = maxgood;
+    best4[0] = best; best4[1] = niters; best4[2] = maxgood;
   }
   __syncthreads();
   const int best = s_best;
   if (best < 0) {
-    if (tid == 0) { *n_inl = 0; *ok = 0; w.best[3] = 0; }
+    if (tid == 0) { n_inl[f] = 0; ok[f] = 0; best4[3] = 0; }
     return;
   }
   double Rt[12], Kl[9];
-  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * best + e];
+  for (int e = 0; e < 12; ++e) Rt[e] = w.models[12 * (h0 + best) + e];
   for (int e = 0; e < 9; ++e) Kl[e] = K[e];
+  const double* Xb = w.Xf + 3 * (size_t)fr.base;
+  const double* xb = w.xf + 2 * (size_t)fr.base;
   for (int i0 = 0; i0 < n; i0 += 1024) {
     const int i = i0 + tid;
-    const bool in = i < n && pnp_error(Rt, Kl, w.Xf + 3 * i, w.xf + 2 * i) <= thr2;
-    if (i < n) w.mask[i] = in;
+    const bool in = i < n && pnp_error(Rt, Kl, Xb + 3 * i, xb + 2 * i) <= thr2;
+    if (i < n) w.mask[fr.base + i] = in;
     const unsigned bal = __ballot_sync(0xffffffffu, in);
     if (lane == 0) warp_tot[wid] = __popc(bal);
     __syncthreads();
-    int off = s_base;
-    for (int k = 0; k < wid; ++k) off += warp_tot[k];
-    off += __popc(bal & ((1u << lane) - 1u));
-    if (in) inliers[off] = i;
+    int o = s_base;
+    for (int k = 0; k < wid; ++k) o += warp_tot[k];
+    o += __popc(bal & ((1u << lane) - 1u));
+    if (in) inl[o] = i;
     __syncthreads();
     if (tid == 0) { int tot = 0; for (int k = 0; k < 32; ++k) tot += warp_tot[k]; s_base += tot; }
     __syncthreads();
   }
-  if (tid == 0) { *n_inl = s_base; *ok = 1; w.best[3] = s_base; }
+  if (tid == 0) { n_inl[f] = s_base; ok[f] = 1; best4[3] = s_base; }
 }
 
 // ------------------------------------------------------------------ iterative refit (LM)
@@ -621,19 +829,38 @@ __device__ bool chol_solve6(const double* H, const double* g, double lambda, dou
 }
 
 __global__ void __launch_bounds__(REFINE_THREADS)
-pnp_refine_kernel(const double* __restrict__ K, PnpWs w, const int32_t* __restrict__ inliers,
-                  double* __restrict__ rvec, double* __restrict__ tvec) {
+pnp_refine_kernel(const double* __restrict__ K, const int32_t* __restrict__ off, int n_single, PnpWs w,
+                  const int32_t* __restrict__ inliers_all, double* __restrict__ rvec_all,
+                  double* __restrict__ tvec_all) {
   __shared__ double red[8 * 28];
   __shared__ double sR[9], st[3], cR[9], ct[3];
   __shared__ double s_cost, s_lambda;
   __shared__ int s_state;   // 0 continue, 1 converged/stop
-  const int best = w.best[0], ni = w.best[3];
-  if (best < 0) return;
+  const int f = blockIdx.x;
+  const PnpFrame fr = pnp_frame(off, n_single, f);
+  const int best = w.best[4 * f], ni = w.best[4 * f + 3];
+  double* rvec = rvec_all + 3 * f;
+  double* tvec = tvec_all + 3 * f;
   const int tid = threadIdx.x;
-  if (tid < 9) sR[tid] = w.models[12 * best + tid];
-  if (tid < 3) st[tid] = w.models[12 * best + 9 + tid];
+  if (best < 0) {
+    if (tid < 3) { rvec[tid] = 0.0; tvec[tid] = 0.0; }
+    return;
+  }
+  const int32_t* inliers = inliers_all + fr.base;
+  const size_t hyp = (size_t)f * w.iters + best;
+  if (tid < 9) sR[tid] = w.models[12 * hyp + tid];
+  if (tid < 3) st[tid] = w.models[12 * hyp + 9 + tid];
   if (tid == 0) { s_lambda = 1e-3; s_state = 0; s_cost = -1.0; }
   __syncthreads();
+  if (ni < 0) {   // 4 / 5 points: solvePnP's own answer, no iterative refit
+    if (tid == 0) {
+      log_so3(sR, rvec);
+      for (int k = 0; k < 3; ++k) tvec[k] = st[k];
+    }
+    return;
+  }
+  const double* Xb = w.Xf + 3 * (size_t)fr.base;
+  const double* xb = w.xf + 2 * (size_t)fr.base;
   const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
   for (int iter = 0; iter < 60; ++iter) {
     // normal equations at (sR, st)
@@ -641,12 +868,12 @@ pnp_refine_kernel(const double* __restrict__ K, PnpWs w, const int32_t* __restri
     for (int k = 0; k < 28; ++k) acc[k] = 0.0;
     for (int q = tid; q < ni; q += REFINE_THREADS) {
       const int i = inliers[q];
-      const double X = w.Xf[3 * i], Y = w.Xf[3 * i + 1], Z = w.Xf[3 * i + 2];
+      const double X = Xb[3 * i], Y = Xb[3 * i + 1], Z = Xb[3 * i + 2];
       const double rx = sR[0] * X + sR[1] * Y + sR[2] * Z, ry = sR[3] * X + sR[4] * Y + sR[5] * Z,
                    rz = sR[6] * X + sR[7] * Y + sR[8] * Z;
       const double xc = rx + st[0], yc = ry + st[1], zc = rz + st[2];
       const double iz = 1.0 / zc;
-      const double eu = fx * xc * iz + cx - w.xf[2 * i], ev = fy * yc * iz + cy - w.xf[2 * i + 1];
+      const double eu = fx * xc * iz + cx - xb[2 * i], ev = fy * yc * iz + cy - xb[2 * i + 1];
       // d(u,v)/dXc
       const double a0 = fx * iz, a2 = -fx * xc * iz * iz, b1 = fy * iz, b2 = -fy * yc * iz * iz;
       // dXc/dw = -[RX]x ; dXc/dt = I
@@ -686,10 +913,10 @@ pnp_refine_kernel(const double* __restrict__ K, PnpWs w, const int32_t* __restri
     double c1[1] = {0.0};
     for (int q = tid; q < ni; q += REFINE_THREADS) {
       const int i = inliers[q];
-      const double X = w.Xf[3 * i], Y = w.Xf[3 * i + 1], Z = w.Xf[3 * i + 2];
+      const double X = Xb[3 * i], Y = Xb[3 * i + 1], Z = Xb[3 * i + 2];
       const double xc = cR[0] * X + cR[1] * Y + cR[2] * Z + ct[0], yc = cR[3] * X + cR[4] * Y + cR[5] * Z + ct[1],
                    zc = cR[6] * X + cR[7] * Y + cR[8] * Z + ct[2];
-      const double eu = fx * xc / zc + cx - w.xf[2 * i], ev = fy * yc / zc + cy - w.xf[2 * i + 1];
+      const double eu = fx * xc / zc + cx - xb[2 * i], ev = fy * yc / zc + cy - xb[2 * i + 1];
       c1[0] += eu * eu + ev * ev;
     }
     block_reduce(c1, 1, red);
@@ -716,9 +943,30 @@ pnp_refine_kernel(const double* __restrict__ K, PnpWs w, const int32_t* __restri
 
 using namespace vo;
 
+static int pnp_launch(const double* X, const double* x, const int32_t* off, int n_single,
+                      long n_total, int n_frames, const double* K, int iters, double reproj_px,
+                      double conf, double* rvec, double* tvec, int32_t* inliers, int32_t* n_inl,
+                      int32_t* ok, const PnpWs& w, cudaStream_t st) {
+  const float thr2 = (float)(reproj_px * reproj_px);
+  if (n_total > 0)
+    pnp_prepare_kernel<<<(unsigned)((n_total + 255) / 256), 256, 0, st>>>(X, x, n_total, w);
+  pnp_sample_kernel<<<(n_frames + 63) / 64, 64, 0, st>>>(off, n_single, n_frames, w);
+  pnp_solve_kernel<<<dim3((iters + PNP_SOLVE_WARPS - 1) / PNP_SOLVE_WARPS, n_frames), PNP_SOLVE_WARPS * 32, 0, st>>>(
+      K, off, n_single, w);
+  pnp_score_kernel<<<dim3((iters + 7) / 8, n_frames), 256, 0, st>>>(K, off, n_single, thr2, w);
+  pnp_select_kernel<<<n_frames, 1024, 0, st>>>(K, off, n_single, conf, thr2, w, inliers, n_inl, ok);
+  pnp_refine_kernel<<<n_frames, REFINE_THREADS, 0, st>>>(K, off, n_single, w, inliers, rvec, tvec);
+  return check_launch("vo_pnp_ransac");
+}
+
 extern "C" size_t vo_pnp_workspace_bytes(int n, int iters) {
   if (n <= 0 || iters <= 0) return 0;
-  return pnp_carve(nullptr, n, iters).bytes;
+  return pnp_carve(nullptr, n, 1, iters).bytes;
+}
+
+extern "C" size_t vo_pnp_batch_workspace_bytes(long n_total, int n_frames, int iters) {
+  if (n_total <= 0 || n_frames <= 0 || iters <= 0) return 0;
+  return pnp_carve(nullptr, n_total, n_frames, iters).bytes;
 }
 
 extern "C" int vo_pnp_ransac(const double* X, const double* x, int n, const double* K, int iters,
@@ -727,18 +975,27 @@ extern "C" int vo_pnp_ransac(const double* X, const double* x, int n, const doub
                              void* stream) {
   VO_REQUIRE(X && x && K && rvec && tvec && inliers && n_inl && ok && ws, VO_ERR_INVALID_ARG,
              "vo_pnp_ransac: null pointer");
-  VO_REQUIRE(n >= 5, VO_ERR_TOO_FEW_POINTS,
-             "vo_pnp_ransac: needs >= 5 points (got %d); the 4-point P3P path is not implemented", n);
+  VO_REQUIRE(n >= 4, VO_ERR_TOO_FEW_POINTS, "vo_pnp_ransac: needs >= 4 points (got %d)", n);
   VO_REQUIRE(iters > 0 && iters <= PNP_MAX_ITERS, VO_ERR_INVALID_ARG, "vo_pnp_ransac: iters must be in 1..1024");
-  PnpWs w = pnp_carve(ws, n, iters);
+  PnpWs w = pnp_carve(ws, n, 1, iters);
   VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_pnp_ransac: workspace too small");
-  cudaStream_t st = (cudaStream_t)stream;
-  const float thr2 = (float)(reproj_px * reproj_px);
-  pnp_prepare_kernel<<<(n + 255) / 256, 256, 0, st>>>(X, x, n, w);
-  pnp_sample_kernel<<<1, 32, 0, st>>>(n, iters, w);
-  pnp_solve_kernel<<<(iters + PNP_SOLVE_WARPS - 1) / PNP_SOLVE_WARPS, PNP_SOLVE_WARPS * 32, 0, st>>>(K, iters, w);
-  pnp_score_kernel<<<(iters + 7) / 8, 256, 0, st>>>(K, n, iters, thr2, w);
-  pnp_select_kernel<<<1, 1024, 0, st>>>(K, n, iters, conf, thr2, w, inliers, n_inl, ok);
-  pnp_refine_kernel<<<1, REFINE_THREADS, 0, st>>>(K, w, inliers, rvec, tvec);
-  return check_launch("vo_pnp_ransac");
+  return pnp_launch(X, x, nullptr, n, n, 1, K, iters, reproj_px, conf, rvec, tvec, inliers, n_inl, ok, w,
+                    (cudaStream_t)stream);
+}
+
+extern "C" int vo_pnp_ransac_batch(const double* X, const double* x, const int32_t* offsets,
+                                   long n_total, int n_frames, const double* K, int iters,
+                                   double reproj_px, double conf, double* rvec, double* tvec,
+                                   int32_t* inliers, int32_t* n_inl, int32_t* ok, void* ws,
+                                   size_t ws_bytes, void* stream) {
+  VO_REQUIRE(X && x && offsets && K && rvec && tvec && inliers && n_inl && ok && ws, VO_ERR_INVALID_ARG,
+             "vo_pnp_ransac_batch: null pointer");
+  VO_REQUIRE(n_total >= 0 && n_frames >= 0 && n_frames <= 65535, VO_ERR_INVALID_ARG,
+             "vo_pnp_ransac_batch: bad sizes");
+  VO_REQUIRE(iters > 0 && iters <= PNP_MAX_ITERS, VO_ERR_INVALID_ARG, "vo_pnp_ransac_batch: iters must be in 1..1024");
+  if (n_frames == 0) return VO_OK;
+  PnpWs w = pnp_carve(ws, n_total > 0 ? n_total : 1, n_frames, iters);
+  VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_pnp_ransac_batch: workspace too small");
+  return pnp_launch(X, x, offsets, 0, n_total, n_frames, K, iters, reproj_px, conf, rvec, tvec, inliers,
+                    n_inl, ok, w, (cudaStream_t)stream);
 }

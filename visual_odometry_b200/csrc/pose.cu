@@ -221,6 +221,27 @@ __device__ __forceinline__ Rt rt_load(const double* __restrict__ R, const double
   return o;
 }
 
+// packed rows [R row-major (9) | t (3)]: the all-gather payload of the multi-GPU path
+__device__ __forceinline__ Rt rt_load_packed(const double* __restrict__ rt, int k) {
+  Rt o;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) o.m[4 * i + j] = rt[(size_t)k * 12 + 3 * i + j];
+    o.m[4 * i + 3] = rt[(size_t)k * 12 + 9 + i];
+  }
+  return o;
+}
+
+__global__ void pack_poses_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
+                                  double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * 12) return;
+  const int k = i / 12, e = i % 12;
+  out[i] = e < 9 ? R[(size_t)k * 9 + e] : t[(size_t)k * 3 + (e - 9)];
+}
+
+template <bool PACKED>
 __global__ void __launch_bounds__(CHAIN_THREADS)
 chain_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
              const double* __restrict__ P0, double* __restrict__ poses) {
@@ -233,7 +254,7 @@ chain_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
   for (int e = 0; e < 12; ++e) ident.m[e] = (e % 5 == 0) ? 1.0 : 0.0;
   // 1) product of this thread's run: rel_{k1-1} ... rel_{k0}
   Rt acc = ident;
-  for (int k = k0; k < k1; ++k) acc = rt_mul(rt_load(R, t, k), acc);
+  for (int k = k0; k < k1; ++k) acc = rt_mul(PACKED ? rt_load_packed(R, k) : rt_load(R, t, k), acc);
   sc[0][tid] = acc;
   __syncthreads();
   // 2) inclusive scan of run totals (later runs multiply on the left)
@@ -258,7 +279,7 @@ chain_kernel(const double* __restrict__ R, const double* __restrict__ t, int n,
     poses[12] = poses[13] = poses[14] = 0.0; poses[15] = 1.0;
   }
   for (int k = k0; k < k1; ++k) {
-    pre = rt_mul(rt_load(R, t, k), pre);
+    pre = rt_mul(PACKED ? rt_load_packed(R, k) : rt_load(R, t, k), pre);
     double* o = poses + (size_t)(k + 1) * 16;
 #pragma unroll
     for (int e = 0; e < 12; ++e) o[e] = pre.m[e];
@@ -284,6 +305,7 @@ extern "C" int vo_recover_pose_batch(const double* E, const double* pts, const i
   VO_REQUIRE(ws_bytes >= vo_pose_workspace_bytes(n_pairs, n_cap), VO_ERR_WORKSPACE,
              "vo_recover_pose_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
+  ProfScope prof(5, (cudaStream_t)stream);
   recover_pose_kernel<<<n_pairs, POSE_THREADS, 0, (cudaStream_t)stream>>>(
       E, pts, m, mask, n_cap, K, dist_thresh, R, t, pose_mask, n_good, (uint8_t*)ws);
   return check_launch("vo_recover_pose_batch");
@@ -304,6 +326,7 @@ extern "C" int vo_triangulate_pairs(const double* R, const double* t, const doub
   VO_REQUIRE(R && t && pts && m && K && X && n_x, VO_ERR_INVALID_ARG,
              "vo_triangulate_pairs: null pointer");
   if (n_pairs <= 0) return VO_OK;
+  ProfScope prof(6, (cudaStream_t)stream);
   triangulate_pairs_kernel<<<n_pairs, TRI_THREADS, 0, (cudaStream_t)stream>>>(R, t, pts, m, mask,
                                                                              n_cap, K, X, n_x);
   return check_launch("vo_triangulate_pairs");
@@ -312,6 +335,22 @@ extern "C" int vo_triangulate_pairs(const double* R, const double* t, const doub
 extern "C" int vo_chain_poses(const double* R, const double* t, int n_pairs, const double* P0,
                               double* poses, void* stream) {
   VO_REQUIRE(R && t && poses && n_pairs >= 0, VO_ERR_INVALID_ARG, "vo_chain_poses: bad arguments");
-  chain_kernel<<<1, CHAIN_THREADS, 0, (cudaStream_t)stream>>>(R, t, n_pairs, P0, poses);
+  ProfScope prof(7, (cudaStream_t)stream);
+  chain_kernel<false><<<1, CHAIN_THREADS, 0, (cudaStream_t)stream>>>(R, t, n_pairs, P0, poses);
   return check_launch("vo_chain_poses");
+}
+
+extern "C" int vo_pack_poses(const double* R, const double* t, int n_pairs, double* rt, void* stream) {
+  VO_REQUIRE(R && t && rt && n_pairs >= 0, VO_ERR_INVALID_ARG, "vo_pack_poses: bad arguments");
+  if (n_pairs == 0) return VO_OK;
+  pack_poses_kernel<<<(n_pairs * 12 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(R, t, n_pairs, rt);
+  return check_launch("vo_pack_poses");
+}
+
+extern "C" int vo_chain_poses_packed(const double* rt, int n_pairs, const double* P0, double* poses,
+                                     void* stream) {
+  VO_REQUIRE(rt && poses && n_pairs >= 0, VO_ERR_INVALID_ARG, "vo_chain_poses_packed: bad arguments");
+  ProfScope prof(7, (cudaStream_t)stream);
+  chain_kernel<true><<<1, CHAIN_THREADS, 0, (cudaStream_t)stream>>>(rt, nullptr, n_pairs, P0, poses);
+  return check_launch("vo_chain_poses_packed");
 }

@@ -435,8 +435,11 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = (n_cap + 255) / 256;
   cudaMemsetAsync(w.n_active, 0, (size_t)(w.max_rounds + 1) * sizeof(int32_t), st);
-  ransac_init_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(pts, m, n_cap, K, max_iters, w,
-                                                                    n_inl, status);
+  {
+    ProfScope prof(9, st);
+    ransac_init_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(pts, m, n_cap, K, max_iters, w,
+                                                                      n_inl, status);
+  }
   static int sms = 0;
   if (!sms) {
     int dev = 0;
@@ -451,7 +454,10 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
   while (it0 < max_iters) {
     if (it0 + chunk > max_iters) chunk = max_iters - it0;
     if (round >= w.max_rounds - 1) chunk = max_iters - it0 < C ? max_iters - it0 : C;  // never hit
-    ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, chunk, C, w);
+    {
+      ProfScope prof(9, st);
+      ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, chunk, C, w);
+    }
     {
       // grid sized for the first (full) round; later rounds loop over what is left
       const long want = (long)n_pairs * ((chunk + SOLVE_WARPS - 1) / SOLVE_WARPS);
@@ -476,6 +482,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
     }
     {
       const int want = (n_pairs + SCAN_WARPS - 1) / SCAN_WARPS;
+      ProfScope prof(9, st);
       ransac_scan_kernel<<<want < sms * 8 ? want : sms * 8, SCAN_WARPS * 32, 0, st>>>(
           m, round, n_pairs, it0, chunk, C, conf, adaptive, w, E);
     }
@@ -487,8 +494,11 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
       chunk = C;
     }
   }
-  ransac_mask_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(m, n_cap, K, thr_px, w, E, mask,
-                                                                    n_inl, n_iters, status);
+  {
+    ProfScope prof(9, st);
+    ransac_mask_kernel<<<dim3(nb < 8 ? nb : 8, n_pairs), 256, 0, st>>>(m, n_cap, K, thr_px, w, E, mask,
+                                                                      n_inl, n_iters, status);
+  }
   return check_launch("vo_essential_ransac_batch");
 }
 

@@ -33,13 +33,13 @@ extern "C" const char* vo_last_error_string(void) { return vo::g_err; }
 #include <mutex>
 #include <vector>
 namespace vo {
-static bool g_prof_on = false;
+static int g_prof_level = 0;   // 1: the matching / scoring / solve kernels (ids < 5); 2: every scope
 static std::mutex g_prof_mu;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof;
 
 ProfScope::ProfScope(int kernel_id, cudaStream_t stream) : id(kernel_id), st(stream) {
-  if (!g_prof_on) return;
+  if (g_prof_level == 0 || (g_prof_level == 1 && kernel_id >= 5)) return;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
@@ -73,7 +73,7 @@ extern "C" int vo_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(vo::g_prof_mu);
   for (auto& r : vo::g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
   vo::g_prof.clear();
-  vo::g_prof_on = on != 0;
+  vo::g_prof_level = on;
   return VO_OK;
 }
 

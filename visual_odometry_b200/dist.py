@@ -37,3 +37,50 @@ def gather_relative_poses(R, t, counts=None, group=None):
     dist.all_gather_into_tensor(out, packed, group=group)
     rows = torch.cat([out[r * n_max: r * n_max + counts[r]] for r in range(world)], 0)
     return rows[:, :9].reshape(-1, 3, 3).contiguous(), rows[:, 9:].contiguous()
+
+
+class PoseGather:
+    """Device path of the one collective for equal pair counts per rank: ONE pack
+    kernel writes the rank's [R|t] rows into the all-gather send buffer, NCCL gathers them, ONE
+    kernel chains the gathered rows into the trajectory.  No torch glue kernels in between;
+    buffers are allocated once.  `collective_ms()` reports the device time of the all-gather."""
+
+    def __init__(self, n_local, device, group=None):
+        from . import _lib
+        self.lib = _lib.load()
+        self._lib = _lib
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.n_local = int(n_local)
+        f64 = torch.float64
+        self.send = torch.empty(self.n_local, 12, dtype=f64, device=device)
+        self.recv = torch.empty(self.world * self.n_local, 12, dtype=f64, device=device)
+        self.poses = torch.empty(self.world * self.n_local + 1, 4, 4, dtype=f64, device=device)
+        self._evs = []
+
+    def __call__(self, R, t, time_it=False):
+        L = self._lib
+        st = L.cur_stream()
+        L.check(self.lib.vo_pack_poses(L.ptr(R), L.ptr(t), self.n_local, L.ptr(self.send), st))
+        if self.world > 1:
+            if time_it:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
+            if time_it:
+                e1.record()
+                self._evs.append((e0, e1))
+            rows = self.recv
+        else:
+            rows = self.send
+        L.check(self.lib.vo_chain_poses_packed(L.ptr(rows), self.world * self.n_local, None,
+                                               L.ptr(self.poses), st))
+        return self.poses
+
+    def collective_ms(self):
+        """mean device time of the timed all-gathers (call after a synchronize)"""
+        if not self._evs:
+            return 0.0
+        ms = sum(a.elapsed_time(b) for a, b in self._evs) / len(self._evs)
+        self._evs = []
+        return ms

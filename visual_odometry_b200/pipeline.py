@@ -34,11 +34,11 @@ class PairPipeline:
         self.do_tri, self.do_chain = triangulate, chain
         dev, P, N, F = self.dev, self.P, self.n_cap, self.F
         e = lambda *s, dt: torch.empty(*s, dtype=dt, device=dev)
-        # inputs resident in HBM
-        self.desc = e(F, N, self.D, dt=self.ddtype)
-        self.kp = e(F, N, 2, dt=F32)
-        self.nkp = e(F, dt=I32)
-        self.pairs = e(P, 2, dt=I32)
+        # inputs resident in HBM; a second set (`slot` 1) is allocated on first use by the
+        # streaming entry, so that the upload of batch k+1 overlaps the compute of batch k
+        self._slots = [dict(desc=e(F, N, self.D, dt=self.ddtype), kp=e(F, N, 2, dt=F32),
+                            nkp=e(F, dt=I32), pairs=e(P, 2, dt=I32))]
+        self._use_slot(0)
         self.K = e(3, 3, dt=F64)
         if K is not None:
             self.K.copy_(torch.as_tensor(np.asarray(K, np.float64)))
@@ -68,10 +68,20 @@ class PairPipeline:
         # kernels launched per run (for bench.py's gpu_launches claim; see launches_per_run)
         self.launches = 0
 
+    def _use_slot(self, k):
+        while len(self._slots) <= k:
+            a = self._slots[0]
+            self._slots.append({n: torch.empty_like(v) for n, v in a.items()})
+        sl = self._slots[k]
+        self.desc, self.kp, self.nkp, self.pairs = sl["desc"], sl["kp"], sl["nkp"], sl["pairs"]
+        self.slot = k
+
     # ------------------------------------------------------------------ device-resident run
-    def run_device(self, n_pairs, stream=None, p0=0, chain=None):
+    def run_device(self, n_pairs, stream=None, p0=0, chain=None, slot=None):
         """Inputs already in self.desc/kp/nkp/pairs. Asynchronous; results in the attributes.
         Processes pairs [p0, p0 + n_pairs) (outputs land in the same rows)."""
+        if slot is not None and slot != self.slot:
+            self._use_slot(slot)
         lib = self.lib
         st = _lib.cur_stream() if stream is None else stream
         N, B, a = self.n_cap, int(n_pairs), int(p0)
@@ -147,7 +157,14 @@ class PairPipeline:
                     chunk = min(chunk * 2, cap)
             else:
                 chunk = cap
-        return 2 + (1 + 4 * rounds + 1) + 1 + int(self.do_tri) + int(self.do_chain)
+        if self.descriptor == "orb":
+            # mirrors use_tensor_path (csrc/hamming.cu): expand + tcgen05 match + compact, or popc + compact
+            ndir = 2 if self.match_mode == _lib.MATCH_MUTUAL else 1
+            tc = self.n_cap >= 512 and n_pairs * ndir * ((self.n_cap + 255) // 256) >= 74
+            match = 3 if tc else 2
+        else:
+            match = 5      # norms, tiles, GEMM (+ the launch that does not apply exits), rerank, compact
+        return match + (1 + 4 * rounds + 1) + 1 + int(self.do_tri) + int(self.do_chain)
 
     # ------------------------------------------------------------------ host-buffer run (e2e)
     def _pinned(self):
@@ -224,6 +241,88 @@ class PairPipeline:
         pin["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
         main.synchronize()
         h2d = sum(pin[k][:f].numel() * pin[k].element_size() for k in ("desc", "kp", "nkp")) + \
+            pin["pairs"][:b].numel() * 4
+        d2h = b * (9 + 3) * 8 + b * 3 * 4 + (b + 1) * 16 * 8
+        return h2d, d2h
+
+    # ------------------------------------------------------------------ streamed batches (e2e)
+    def run_stream(self, n_frames, n_pairs, steps, fill=None, consume=None, after_compute=None):
+        """`steps` batches through the whole chain with the upload of batch k+1 running on a copy
+        stream while batch k computes (two input slots on the device, two pinned result slots on
+        the host).  Every batch: H2D of its frames from the pinned staging area, the chain, D2H of
+        its poses / counts.  `fill(k, pin)` may refill the pinned input buffers for batch k (called
+        once the previous upload has left them; default: the staged inputs are reused),
+        `consume(k, res)` receives batch k's host results (views of a pinned slot, valid until
+        batch k+2 is submitted), `after_compute(k)` may enqueue more work on the compute stream
+        (multi-GPU: the pose all-gather).  Returns (h2d_bytes, d2h_bytes) per batch."""
+        pin, f, b = self._pinned(), int(n_frames), int(n_pairs)
+        main = torch.cuda.current_stream()
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+        cs = self._copy_stream
+        if getattr(self, "_pin_out", None) is None:
+            mk = lambda *s, dt: torch.empty(*s, dtype=dt, pin_memory=True)
+            self._pin_out = [dict(R=mk(self.P, 3, 3, dt=F64), t=mk(self.P, 3, dt=F64),
+                                  n_inl=mk(self.P, dt=I32), n_match=mk(self.P, dt=I32),
+                                  status=mk(self.P, dt=I32), poses=mk(self.P + 1, 4, 4, dt=F64))
+                             for _ in range(2)]
+        self._use_slot(1)
+        self._use_slot(0)
+        uploaded = [None, None]       # event: inputs of the batch in this slot are on the device
+        computed = [None, None]       # event: the chain of the batch in this slot has read them
+        done = [None, None]           # event: results of the batch in this slot are on the host
+        cs.wait_stream(main)
+
+        def upload(k):
+            sl = self._slots[k & 1]
+            if fill is not None:
+                if k > 0:
+                    uploaded[(k - 1) & 1].synchronize()      # the staging area is free again
+                fill(k, pin)
+            with torch.cuda.stream(cs):
+                if computed[k & 1] is not None:
+                    cs.wait_event(computed[k & 1])           # batch k-2 no longer reads this slot
+                sl["nkp"][:f].copy_(pin["nkp"][:f], non_blocking=True)
+                sl["pairs"][:b].copy_(pin["pairs"][:b], non_blocking=True)
+                sl["desc"][:f].copy_(pin["desc"][:f], non_blocking=True)
+                sl["kp"][:f].copy_(pin["kp"][:f], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+            uploaded[k & 1] = ev
+
+        def emit(k):
+            done[k & 1].synchronize()
+            if consume is not None:
+                o = self._pin_out[k & 1]
+                consume(k, dict(R=o["R"][:b], t=o["t"][:b], n_inl=o["n_inl"][:b],
+                                n_match=o["n_match"][:b], status=o["status"][:b],
+                                poses=o["poses"][:b + 1]))
+
+        upload(0)
+        for k in range(steps):
+            if k + 1 < steps:
+                upload(k + 1)
+            main.wait_event(uploaded[k & 1])
+            self.run_device(b, slot=k & 1)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            computed[k & 1] = ev
+            if after_compute is not None:
+                after_compute(k)
+            o = self._pin_out[k & 1]
+            for name, src in (("R", self.R), ("t", self.t), ("n_inl", self.n_inl),
+                              ("n_match", self.n_match), ("status", self.status)):
+                o[name][:b].copy_(src[:b], non_blocking=True)
+            o["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            done[k & 1] = ev
+            if k >= 1:
+                emit(k - 1)
+        if steps:
+            emit(steps - 1)
+        self._use_slot(0)
+        h2d = sum(pin[n][:f].numel() * pin[n].element_size() for n in ("desc", "kp", "nkp")) + \
             pin["pairs"][:b].numel() * 4
         d2h = b * (9 + 3) * 8 + b * 3 * 4 + (b + 1) * 16 * 8
         return h2d, d2h
