@@ -65,7 +65,12 @@ int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int m
 /* ---- K6: SIFT/L2 matching on tensor cores (BFMatcher(NORM_L2), visual_slam.py:19) ----
  * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2).
  * Every frame 0..n_frames-1 is converted once (bf16 tiles + norms) and shared by its pairs.
- * Bit-exact for integer-valued descriptors (cv2 SIFT); other data: fp32 rerank of candidates. */
+ * Bit-exact for integer-valued descriptors (cv2 SIFT: exact in bf16, dot products < 2^24).
+ * Other float data (RootSIFT ...): the bf16 GEMM proposes the two best candidates per row (both
+ * directions for the cross-check) and an fp32 rerank orders them with cv2's formula; a neighbour
+ * that bf16 rounding (2^-9 relative per element) ranks third or lower is missed, i.e. the matcher
+ * is an APPROXIMATE nearest-neighbour search for non-integer descriptors (measured: identical to
+ * cv2 on > 99.9 % of the matches of near-tied float data, tests/test_gpu_match_l2.py). */
 size_t vo_match_l2_workspace_bytes(int n_frames, int n_pairs, int n_cap);
 int vo_match_l2_batch(const float* desc, const int32_t* nkp, const float* kp, int n_cap, int dim,
                       int n_frames, const int32_t* pairs, int n_pairs, int mode, double ratio,

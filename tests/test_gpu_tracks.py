@@ -119,3 +119,24 @@ def test_tracks_equal_reference_golden(cuda_dev):
             assert np.array_equal(xyz.cpu().numpy(), g[f"obj_{b}"])
             n_calls += 1
     assert n_calls == F - 2
+
+
+def test_duplicate_train_features_last_match_wins_like_the_reference(cuda_dev):
+    """knn + ratio matching can pair several queries with ONE train feature.  The reference
+    inserts feature_mapper[featureid2] = featureid1 in match order, so the last match wins; the
+    device update elects the highest match index per train feature (deterministic, twice the
+    same answer)."""
+    N = 64
+    tr = FeatureTracks(3, N)
+    q = torch.tensor([3, 5, 7, 9, 11, 13], dtype=torch.int32, device=cuda_dev)
+    t = torch.tensor([2, 4, 2, 6, 4, 2], dtype=torch.int32, device=cuda_dev)     # 2 three times, 4 twice
+    n = torch.tensor([6], dtype=torch.int32, device=cuda_dev)
+    orc = TracksOracle()
+    orc.update_feature_mapper([((0, int(a)), (1, int(b)), (0.0, 0.0)) for a, b in zip(q.tolist(), t.tolist())])
+    for _ in range(2):
+        tr.update(q, t, None, n, 0, 1)
+        ids = [tr.feature_id(1, i) for i in (2, 4, 6, 8)]
+        roots = tr.root_of(ids).cpu().tolist()
+        want = [tr.feature_id(*orc.track_feature_back_in_time((1, i))) for i in (2, 4, 6, 8)]
+        assert roots == want == [tr.feature_id(0, 13), tr.feature_id(0, 11), tr.feature_id(0, 9),
+                                 tr.feature_id(1, 8)]

@@ -41,7 +41,7 @@ constexpr int EPI_WARPS = 8;                    // warp & 3 = TMEM lane quarter,
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr int KEY_MININT = (int)0x80000000;
 
-__device__ int g_debug = 0;   // bit 1: epilogue skips the ranking, bit 2: skips the TMEM loads too
+static __device__ int g_debug = 0;   // bit 1: epilogue skips the ranking, bit 2: skips the TMEM loads too
 
 // kind::i8: A, B signed 8 bit, K-major, D = s32, M x N
 __host__ __device__ constexpr uint32_t idesc_s8_s32(int M, int N) {
@@ -66,7 +66,7 @@ __device__ __forceinline__ uint32_t spread4(uint32_t b4) {
   return 0xF0F0F0F0u ^ (x * 0xE0u);
 }
 
-__global__ void __launch_bounds__(ROWS)
+static __global__ void __launch_bounds__(ROWS)
 expand_kernel(const uint8_t* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
               int ntile, uint8_t* __restrict__ tiles) {
   const int f = blockIdx.y, tl = blockIdx.x, r = threadIdx.x;

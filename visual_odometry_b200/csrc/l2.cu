@@ -32,6 +32,7 @@
 #include <cuda_bf16.h>
 
 #include "tc.cuh"
+#include "l2_i8.cuh"
 
 namespace vo {
 
@@ -64,7 +65,8 @@ enum { L2_MODE_TOP1 = 0, L2_MODE_TOP2 = 1, L2_MODE_TOP1_COLMAX = 2, L2_MODE_TOP1
 struct L2Ws {
   __nv_bfloat16* tiles;   // [F][nblk][20480]
   float* norms;           // [F][nblk*128]   (+inf on padded rows)
-  int32_t* flags;         // [0] inexact data, [1] bits of the largest squared norm
+  int32_t* flags;         // [0] inexact data, [1] bits of the largest squared norm, [2] not uint8 data
+  uint8_t* tiles8;        // [F][ntile256][l8::TILE_BYTES] uint8 operand tiles of the integer path (l2_i8.cuh)
   float4* rowbest;        // [P][2][S][nblk*128]  (d2_1, idx_1, d2_2, idx_2) idx as int bits
   uint32_t* colpart;      // [P][nrbp*4][nblk*128] best query row of every train column among the 64
                           // rows one epilogue warp owns (256-row block x TMEM lane quarter)
@@ -87,6 +89,7 @@ static L2Ws l2_carve(void* base, int n_frames, int n_pairs, int n_cap, int split
   w.flags = (int32_t*)take(256);
   w.rowbest = (float4*)take((size_t)n_pairs * 2 * splits * nblk * L2_BLK * sizeof(float4));
   w.colpart = (uint32_t*)take((size_t)n_pairs * ((nblk + 1) / 2) * 4 * nblk * L2_BLK * sizeof(uint32_t));
+  w.tiles8 = (uint8_t*)take((size_t)n_frames * ((n_cap + l8::ROWS - 1) / l8::ROWS) * l8::TILE_BYTES);
   w.bytes = off;
   return w;
 }
@@ -134,7 +137,8 @@ l2_norm_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, 
 // tile layout (bytes): kg*2048 + rg*128 + rr*16 + kk*2  with r = 8*rg+rr, k = 8*kg+kk
 __global__ void __launch_bounds__(256)
 l2_tile_kernel(const float* __restrict__ desc, const int32_t* __restrict__ nkp, int n_cap,
-               int nblk, L2Ws w) {
+               int nblk, int skip_if_i8, L2Ws w) {
+  if (skip_if_i8 && w.flags[2] == 0) return;     // uint8 data: the integer kernel (l2_i8.cuh) runs
   const int f = blockIdx.y, blk = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = nkp[f];
@@ -524,6 +528,10 @@ template <int MODE, bool ADDM>
 __global__ void __launch_bounds__(L2_THREADS, 1)
 l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ pairs, int nblk,
                   int n_splits, int ndir, int n_items, int run_if, L2Ws w) {
+  if (run_if >= 8) {                              // bit 3: skip when the integer path applies
+    if (w.flags[2] == 0) return;
+    run_if -= 9;                                  // 8 -> -1, 9 -> 0, 10 -> 1
+  }
   constexpr bool TOP2 = (MODE == L2_MODE_TOP2);
   constexpr bool FRAG = (MODE == L2_MODE_TOP1_COLMAX_FRAG);   // fragment-shaped TMEM loads
   constexpr bool COLMAX = (MODE == L2_MODE_TOP1_COLMAX) || FRAG;
@@ -819,7 +827,8 @@ l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp,
   const float4* bwd = w.rowbest + ((size_t)pair * 2 + 1) * n_splits * stride;
   const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
   const uint32_t* colp = w.colpart + (size_t)pair * nrbp * 4 * stride;
-  const bool use_col = colmode != 0 && w.flags[0] == 0;
+  // colmode bit 1: the integer path may have run (two directions in rowbest, no column partials)
+  const bool use_col = (colmode & 1) != 0 && w.flags[0] == 0 && !((colmode & 2) != 0 && w.flags[2] == 0);
   const size_t ob = (size_t)pair * n_cap;
   const float INF = __int_as_float(0x7f800000);
   if (tid == 0) base_s = 0;
@@ -892,14 +901,14 @@ l2_compact_kernel(const int32_t* __restrict__ nkp, const float* __restrict__ kp,
 using namespace vo;
 
 static int l2_num_sms() {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-      sms = 148;
-  }
-  return sms;
+  static int sms[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!sms[dev] &&
+      (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] <= 0))
+    sms[dev] = 148;
+  return sms[dev];
 }
 
 // column splits only when there are too few (pair, direction, 256-row block) items to give every
@@ -943,23 +952,35 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   const int ndir = (mode == VO_MATCH_MUTUAL) ? 2 : 1;   // rerank grid: directions that may exist
   const int splits = l2_pick_splits(n_pairs, 1, nblk);
   L2Ws w = l2_carve(ws, n_frames, n_pairs, n_cap, splits);
-  cudaMemsetAsync(w.flags, 0, 2 * sizeof(int32_t), st);
+  const bool use_i8 = (g_l2_debug_host & 128) == 0;    // debug bit 7: bf16 kernels only
+  const int ntile8 = (n_cap + l8::ROWS - 1) / l8::ROWS;
+  cudaMemsetAsync(w.flags, 0, 4 * sizeof(int32_t), st);
   l2_norm_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
-  l2_tile_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, w);
+  if (use_i8)
+    l8::tile_kernel<<<dim3(ntile8, n_frames), 256, 0, st>>>(desc, nkp, n_cap, ntile8, w.norms, nblk * L2_BLK,
+                                                           w.tiles8, w.flags);
+  l2_tile_kernel<<<dim3(nblk, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nblk, use_i8 ? 1 : 0, w);
   typedef void (*L2Kernel)(const int32_t*, const int32_t*, int, int, int, int, int, L2Ws);
   static const L2Kernel kernels[8] = {
       l2_top2_tc_kernel<L2_MODE_TOP1, false>, l2_top2_tc_kernel<L2_MODE_TOP2, false>,
       l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, false>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX_FRAG, false>,
       l2_top2_tc_kernel<L2_MODE_TOP1, true>, l2_top2_tc_kernel<L2_MODE_TOP2, true>,
       l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX, true>, l2_top2_tc_kernel<L2_MODE_TOP1_COLMAX_FRAG, true>};
-  static bool attr_set = false;
+  static bool attr_set[64] = {false};     // cudaFuncSetAttribute is per device
   const int smem = (int)sizeof(L2Smem) + 1024;
-  if (!attr_set) {
+  const int smem8 = (int)sizeof(l8::Smem) + 1024;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!attr_set[dev]) {
     for (int k = 0; k < 8; ++k)
       if (cudaFuncSetAttribute(kernels[k], cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
           cudaSuccess)
         return check_launch("vo_match_l2_batch(smem attribute)");
-    attr_set = true;
+    if (cudaFuncSetAttribute(l8::match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem8) != cudaSuccess ||
+        cudaFuncSetAttribute(l8::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem8) != cudaSuccess)
+      return check_launch("vo_match_l2_batch(smem attribute, integer kernel)");
+    attr_set[dev] = true;
   }
   const int addm = (g_l2_debug_host & 8) ? 4 : 0;
   // experimental: fragment-shaped TMEM loads (fewer instructions, measured 3 % slower: profiles/r1_summary.md)
@@ -968,11 +989,24 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
   {
     ProfScope prof(2, st);
     const int nrbp = (nblk + L2_RBK - 1) / L2_RBK;
+    if (use_i8) {   // uint8 data (cv2 SIFT): both directions as integer MMA passes; exits at once otherwise
+      const int nd = (mode == VO_MATCH_MUTUAL) ? 2 : 1;
+      const long n_items = (long)n_pairs * nd * ntile8;
+      const int grid = (int)(n_items < l2_num_sms() ? n_items : l2_num_sms());
+      if (mode == VO_MATCH_MUTUAL)
+        l8::match_kernel<false><<<grid, l8::THREADS, smem8, st>>>(w.tiles8, nkp, pairs, n_cap, ntile8, nd, n_items,
+                                                                 w.norms, nblk * L2_BLK, splits, nblk * L2_BLK,
+                                                                 w.flags, w.rowbest);
+      else
+        l8::match_kernel<true><<<grid, l8::THREADS, smem8, st>>>(w.tiles8, nkp, pairs, n_cap, ntile8, nd, n_items,
+                                                                w.norms, nblk * L2_BLK, splits, nblk * L2_BLK,
+                                                                w.flags, w.rowbest);
+    }
     auto launch = [&](int mode_k, int nd, int run_if) {
       const long n_items = (long)n_pairs * nd * splits * nrbp;
       const int grid = (int)(n_items < l2_num_sms() ? n_items : l2_num_sms());
       kernels[mode_k + addm]<<<grid, L2_THREADS, smem, st>>>(nkp, pairs, nblk, splits, nd,
-                                                            (int)n_items, run_if, w);
+                                                            (int)n_items, use_i8 ? run_if + 9 : run_if, w);
     };
     if (mode != VO_MATCH_MUTUAL) {
       launch(L2_MODE_TOP2, 1, -1);
@@ -983,12 +1017,15 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
       // both directions + fp32 rerank.  The prep kernels decide on the device (flags[0]); the
       // launch that does not apply exits at once.
       launch(frag_layout ? L2_MODE_TOP1_COLMAX_FRAG : L2_MODE_TOP1_COLMAX, 1, 0);
-      launch(L2_MODE_TOP1, 2, 1);
+      // inexact data: TWO candidates per row in both directions, so that the fp32 rerank can
+      // undo a bf16 rank flip between the best two (a true neighbour the bf16 ranking puts third
+      // or lower is still missed: approximate for non-integer descriptors, see vo_b200.h)
+      launch(L2_MODE_TOP2, 2, 1);
     }
   }
   l2_rerank_kernel<<<dim3((n_cap + 7) / 8, n_pairs * ndir), 256, 0, st>>>(desc, nkp, n_cap, pairs,
                                                                         nblk, splits, ndir, w);
   l2_compact_kernel<<<n_pairs, L2C_THREADS, 0, st>>>(nkp, kp, n_cap, pairs, nblk, splits, mode, ratio,
-                                                    two_pass_only ? 0 : -1, w, q, t, dist, t2, dist2, pts, n_out);
+                                                    (two_pass_only ? 0 : 1) | (use_i8 ? 2 : 0), w, q, t, dist, t2, dist2, pts, n_out);
   return check_launch("vo_match_l2_batch");
 }

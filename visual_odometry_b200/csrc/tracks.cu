@@ -24,16 +24,26 @@ __global__ void tracks_reset_kernel(int32_t* __restrict__ parent, int32_t* __res
   }
 }
 
+// The reference inserts the links sequentially (feature_mapper[featureid2] = featureid1 in match
+// order), so when several matches share a train feature (knn + ratio mode; never with the
+// cross-check) the LAST one wins.  Two passes keep that deterministic: pass 0 elects the highest
+// match index per train feature (atomicMax of a tagged index: the tag bit puts it above -1 and
+// above any feature id), pass 1 lets the elected match write parent and root.
+constexpr int32_t TRACK_TAG = 0x40000000;
 __global__ void tracks_update_kernel(const int32_t* __restrict__ q, const int32_t* __restrict__ t,
                                      const uint8_t* __restrict__ mask,
                                      const int32_t* __restrict__ n_match, int f1, int f2, int n_cap,
-                                     int32_t* __restrict__ parent, int32_t* __restrict__ root) {
+                                     int pass, int32_t* __restrict__ parent, int32_t* __restrict__ root) {
   const int n = *n_match;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     if (mask && !mask[i]) continue;
     const int a = f1 * n_cap + q[i], b = f2 * n_cap + t[i];
-    parent[b] = a;
-    root[b] = root[a];
+    if (pass == 0) {
+      atomicMax(&parent[b], TRACK_TAG | i);
+    } else if (parent[b] == (TRACK_TAG | i)) {
+      parent[b] = a;
+      root[b] = root[a];
+    }
   }
 }
 
@@ -100,7 +110,7 @@ using namespace vo;
 
 extern "C" int vo_tracks_reset(int32_t* parent, int32_t* root, int32_t* root_point,
                                long n_features, void* stream) {
-  VO_REQUIRE(parent && root && root_point && n_features >= 0 && n_features < 2147483647L,
+  VO_REQUIRE(parent && root && root_point && n_features >= 0 && n_features < (1L << 30),
              VO_ERR_INVALID_ARG, "vo_tracks_reset: bad arguments");
   if (n_features == 0) return VO_OK;
   const int blocks = (int)((n_features + 255) / 256 < 1184 ? (n_features + 255) / 256 : 1184);
@@ -114,8 +124,9 @@ extern "C" int vo_tracks_update(const int32_t* q, const int32_t* t, const uint8_
   VO_REQUIRE(q && t && n_match && parent && root && n_cap > 0 && frame1 >= 0 && frame2 >= 0,
              VO_ERR_INVALID_ARG, "vo_tracks_update: bad arguments");
   const int blocks = (n_cap + 255) / 256;
-  tracks_update_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(q, t, mask, n_match, frame1, frame2,
-                                                               n_cap, parent, root);
+  for (int pass = 0; pass < 2; ++pass)
+    tracks_update_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(q, t, mask, n_match, frame1, frame2,
+                                                                 n_cap, pass, parent, root);
   return check_launch("vo_tracks_update");
 }
 
