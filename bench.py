@@ -163,20 +163,10 @@ def run_reference(args, rank, world):
 def k2_roofline(pipe, n_pairs, ms_per_step, hbm_peak):
     """K2 (Sampson scoring) as achieved HBM GB/s, the form north_star asks for: every hypothesis
     sample scored reads its pair's correspondences once, 32 bytes each.  Samples scored
-    = the iterations RANSAC ran per pair, rounded up to the round it stopped in (16, 32, 64, ...)."""
+    = the iterations RANSAC ran per pair, rounded up to the round it stopped in (16, 80, 336, 1000)."""
     it = pipe.n_iters[:n_pairs].cpu().numpy().astype("int64")
     m = pipe.n_match[:n_pairs].cpu().numpy().astype("int64")
-    done, bound = 0, []
-    cap = min(pipe.max_iters, max(256, 262144 // max(n_pairs, 1)))
-    chunk, r = min(16, cap), 0
-    while done < pipe.max_iters:
-        chunk = min(chunk, pipe.max_iters - done)
-        done += chunk
-        bound.append(done)
-        r += 1
-        if r >= 2 and chunk < cap:
-            chunk = min(chunk * 2, cap)
-    import numpy as np
+    bound = list(np.cumsum(pipe.ransac_schedule(n_pairs)))
     scored = np.array(bound)[np.searchsorted(np.array(bound), np.minimum(it, bound[-1]))]
     nbytes = float((scored * m).sum()) * 32.0
     gbs = nbytes / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else None

@@ -92,6 +92,10 @@ int vo_essential_ransac_batch(const double* pts, const int32_t* m, int n_cap, in
                               int adaptive, double* E, uint8_t* mask, int32_t* n_inl,
                               int32_t* n_iters, int32_t* status, void* ws, size_t ws_bytes,
                               void* stream);
+/* the round schedule vo_essential_ransac_batch uses for these sizes (iterations solved and scored
+ * per round; 4 kernels per round): chunks_h int [max_rounds] on the HOST, returns the number of
+ * rounds.  For launch accounting on the host side. */
+int vo_ransac_round_schedule(int max_iters, int n_pairs, int adaptive, int* chunks_h, int max_rounds);
 /* five-point minimal solver alone: samples int32 [n_samples,5] index into pts_n [m,4]
  * (normalised coords). out E [n_samples,10,9], n_models int32 [n_samples]. */
 int vo_fivept_solve(const double* pts_n, int m, const int32_t* samples, int n_samples,

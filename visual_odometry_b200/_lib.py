@@ -45,6 +45,7 @@ SIGNATURES = {
     "vo_essential_workspace_bytes": (_sz, [_i, _i, _i]),
     "vo_essential_ransac_batch": (_i, [_p, _p, _i, _i, _p, _d, _d, _i, _i, _p, _p, _p, _p, _p,
                                        _p, _sz, _p]),
+    "vo_ransac_round_schedule": (_i, [_i, _i, _i, _p, _i]),
     "vo_fivept_solve": (_i, [_p, _i, _p, _i, _p, _p, _p]),
     "vo_sampson_score": (_i, [_p, _i, _p, _i, _f, _p, _p, _p]),
     "vo_ransac_samples": (_i, [_i, _i, _p, _p]),

@@ -59,15 +59,15 @@ static RansacWs carve(void* base, int P, int n_cap, int C, int max_iters) {
   return w;
 }
 
-constexpr int RANSAC_CHUNK0 = 16;    // first rounds (adaptive runs usually stop inside them)
+constexpr int RANSAC_CHUNK0 = 16;    // first round (adaptive runs usually stop inside it)
 constexpr int RANSAC_CHUNK_MAX = 256;
 
 // Iterations solved + scored per round.  256 for big batches; for few pairs the cap grows (up to
 // the whole budget) so that a fixed-hypothesis run (config C3: 4096 hypotheses, adaptive stop
 // off) needs one or two rounds instead of sixteen latency-bound ones.  Bounded so that the
-// per-round model store (720 B per iteration per pair) stays below ~190 MB.
+// per-round model store (720 B per iteration per pair) stays below ~760 MB.
 static inline int chunk_cap(int max_iters, int n_pairs) {
-  long cap = 262144L / (n_pairs > 0 ? n_pairs : 1);
+  long cap = 1048576L / (n_pairs > 0 ? n_pairs : 1);
   if (cap < RANSAC_CHUNK_MAX) cap = RANSAC_CHUNK_MAX;
   if (cap > max_iters) cap = max_iters;
   return cap < 1 ? 1 : (int)cap;
@@ -215,6 +215,26 @@ __device__ __forceinline__ bool sampson_inlier(const double* __restrict__ E, dou
   return inl;
 }
 
+// First sieve in fp32 (twice the fp64 rate): normalised coordinates and E entries are O(1), so
+// the residual x2'Ex1 carries an absolute error of a few 1e-7 against ~7e-4 at the threshold,
+// i.e. < 1.5e-3 relative on its square; only correspondences within +-5e-3 of the threshold go on
+// to the fp64 decision above (and from there, within 1e-6, to the exact OpenCV-ordered one).
+// returns 1 inlier, 0 outlier, -1 undecided
+__device__ __forceinline__ int sampson_sieve_f32(const float* __restrict__ E, float x1, float y1,
+                                                 float x2, float y2, float t_lo, float t_hi) {
+  const float ex0 = fmaf(E[0], x1, fmaf(E[1], y1, E[2]));
+  const float ex1 = fmaf(E[3], x1, fmaf(E[4], y1, E[5]));
+  const float ex2 = fmaf(E[6], x1, fmaf(E[7], y1, E[8]));
+  const float et0 = fmaf(E[0], x2, fmaf(E[3], y2, E[6]));
+  const float et1 = fmaf(E[1], x2, fmaf(E[4], y2, E[7]));
+  const float xe = fmaf(x2, ex0, fmaf(y2, ex1, ex2));
+  const float den = fmaf(ex0, ex0, fmaf(ex1, ex1, fmaf(et0, et0, et1 * et1)));
+  const float num = xe * xe;
+  if (num < t_lo * den) return 1;
+  if (num > t_hi * den) return 0;
+  return -1;
+}
+
 // findEssentialMat: threshold /= (fx+fy)/2 ; findInliers compares with float(thr*thr)
 __device__ __forceinline__ float thr2_from_K(const double* __restrict__ K, double thr_px) {
   const double thr = thr_px / ((K[0] + K[4]) / 2.0);
@@ -226,6 +246,7 @@ __global__ void __launch_bounds__(SCORE_WARPS * 32)
 ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_pairs, int chunk,
                     int chunk_stride, const double* __restrict__ K, double thr_px, RansacWs w) {
   __shared__ double Es[SCORE_WARPS][90];
+  __shared__ float Ef[SCORE_WARPS][90];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_act = w.n_active[round];
   const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
@@ -233,6 +254,7 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
   const long n_items = (long)n_act * per_pair;
   const float thr2f = thr2_from_K(K, thr_px);
   const double t_lo = (double)thr2f * (1.0 - 1e-6), t_hi = (double)thr2f * (1.0 + 1e-6);
+  const float tf_lo = thr2f * (1.f - 5e-3f), tf_hi = thr2f * (1.f + 5e-3f);
   for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
     const int p = list[item / per_pair];
     const int s = (int)(item % per_pair) * SCORE_WARPS + warp;
@@ -241,7 +263,7 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
     if (nm == 0) continue;
     const double* src = w.models + ((size_t)p * chunk_stride + s) * 90;
     __syncwarp();
-    for (int e = lane; e < nm * 9; e += 32) Es[warp][e] = src[e];
+    for (int e = lane; e < nm * 9; e += 32) { const double v = src[e]; Es[warp][e] = v; Ef[warp][e] = (float)v; }
     __syncwarp();
     const int mp = m[p];
     const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
@@ -251,8 +273,11 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
       const bool act = i < mp;
       double4 v = make_double4(0, 0, 0, 0);
       if (act) v = ldg_d4(pts + i);
+      const float fx1 = (float)v.x, fy1 = (float)v.y, fx2 = (float)v.z, fy2 = (float)v.w;
       for (int k = 0; k < nm; ++k) {
-        const bool inl = act && sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+        int dec = act ? sampson_sieve_f32(&Ef[warp][9 * k], fx1, fy1, fx2, fy2, tf_lo, tf_hi) : 0;
+        if (dec < 0) dec = sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+        const bool inl = dec != 0;
         const unsigned b = __ballot_sync(0xffffffffu, inl);
         if (lane == k) cnt += __popc(b);
       }
@@ -401,6 +426,32 @@ __global__ void ransac_mask_kernel(const int32_t* __restrict__ m, int n_cap,
 
 using namespace vo;
 
+// Iterations per round: 16, then x4 per round up to the cap (adaptive; iterations at or beyond a
+// pair's current bound are skipped inside the kernels, so a long late round costs only the pairs
+// that still need it), or the cap straight away (fixed hypothesis count).  One definition, also
+// exported so that the host side (launch counts, bench accounting) cannot drift from it.
+static int round_schedule(int max_iters, int C, int adaptive, int* chunks, int max_rounds) {
+  int it0 = 0, n = 0;
+  int chunk = RANSAC_CHUNK0 < C ? RANSAC_CHUNK0 : C;
+  if (!adaptive) chunk = C;
+  while (it0 < max_iters && n < max_rounds) {
+    if (it0 + chunk > max_iters) chunk = max_iters - it0;
+    if (n == max_rounds - 1) chunk = max_iters - it0 < C ? max_iters - it0 : C;
+    if (chunks) chunks[n] = chunk;
+    it0 += chunk;
+    ++n;
+    if (adaptive) chunk = (chunk * 4 < C) ? chunk * 4 : C;
+    else chunk = C;
+  }
+  return n;
+}
+
+extern "C" int vo_ransac_round_schedule(int max_iters, int n_pairs, int adaptive, int* chunks_h,
+                                        int max_rounds) {
+  if (max_iters <= 0 || max_rounds <= 0) return 0;
+  return round_schedule(max_iters, chunk_cap(max_iters, n_pairs), adaptive, chunks_h, max_rounds);
+}
+
 extern "C" int vo_debug_ransac(int solve_minb) {
   g_solve_minb = solve_minb;
   return VO_OK;
@@ -447,13 +498,12 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
       sms = 148;
   }
-  int it0 = 0;
-  int chunk = RANSAC_CHUNK0 < C ? RANSAC_CHUNK0 : C;
-  int round = 0;
+  int sched[128];
+  const int n_rounds = round_schedule(max_iters, C, adaptive, sched, w.max_rounds < 128 ? w.max_rounds : 128);
   const int list_blocks = (n_pairs + 63) / 64 < sms ? (n_pairs + 63) / 64 : sms;
-  while (it0 < max_iters) {
-    if (it0 + chunk > max_iters) chunk = max_iters - it0;
-    if (round >= w.max_rounds - 1) chunk = max_iters - it0 < C ? max_iters - it0 : C;  // never hit
+  int it0 = 0;
+  for (int round = 0; round < n_rounds; ++round) {
+    const int chunk = sched[round];
     {
       ProfScope prof(9, st);
       ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, chunk, C, w);
@@ -487,12 +537,6 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
           m, round, n_pairs, it0, chunk, C, conf, adaptive, w, E);
     }
     it0 += chunk;
-    ++round;
-    if (adaptive) {
-      if (round >= 2 && chunk < C) chunk = (chunk * 2 < C) ? chunk * 2 : C;
-    } else {
-      chunk = C;
-    }
   }
   {
     ProfScope prof(9, st);

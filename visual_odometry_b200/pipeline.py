@@ -141,22 +141,19 @@ class PairPipeline:
                                "run_images: more than n_cap key points survived in some frame")
         return b
 
+    def ransac_schedule(self, n_pairs=None):
+        """iterations per RANSAC round, as vo_essential_ransac_batch schedules them"""
+        import ctypes
+        n_pairs = self.P if n_pairs is None else int(n_pairs)
+        buf = (ctypes.c_int * 128)()
+        n = self.lib.vo_ransac_round_schedule(self.max_iters, n_pairs, int(self.adaptive), buf, 128)
+        return [int(buf[k]) for k in range(n)]
+
     def launches_per_run(self, n_pairs=None):
         """Number of libvo_b200 kernels one run_device issues (memsets excluded); mirrors the
         round schedule of vo_essential_ransac_batch (csrc/ransac.cu)."""
         n_pairs = self.P if n_pairs is None else int(n_pairs)
-        cap = min(self.max_iters, max(256, 262144 // max(n_pairs, 1)))
-        rounds, it0, chunk, r = 0, 0, min(16, cap), 0
-        while it0 < self.max_iters:
-            chunk = min(chunk, self.max_iters - it0)
-            it0 += chunk
-            rounds += 1
-            r += 1
-            if self.adaptive:
-                if r >= 2 and chunk < cap:
-                    chunk = min(chunk * 2, cap)
-            else:
-                chunk = cap
+        rounds = len(self.ransac_schedule(n_pairs))
         if self.descriptor == "orb":
             # mirrors use_tensor_path (csrc/hamming.cu): expand + tcgen05 match + compact, or popc + compact
             ndir = 2 if self.match_mode == _lib.MATCH_MUTUAL else 1
