@@ -25,10 +25,12 @@ if ROOT not in sys.path:
 N_FRAMES = 1000
 N_KP = 2000
 SEED = 20261104 + 1     # seed = 20261104 + config index
-# dram__bytes_read.sum + dram__bytes_write.sum of the 999-pair K1t launch (ncu --set full); None
-# until the capture of this round exists under profiles/
-K1T_DRAM_BYTES_PER_LAUNCH = None
-K1T_TRAFFIC_SOURCE = "pending: ncu --set full capture of htc::match_kernel"
+# dram__bytes_read.sum + dram__bytes_write.sum of the 999-pair K1t launch (ncu --set full,
+# profiles/r2b_k1t_ncu_full_raw.csv: 655.41 MB read + 25.50 MB written)
+K1T_DRAM_BYTES_PER_LAUNCH = 680907264
+K1T_TRAFFIC_SOURCE = "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch " \
+                     "(profiles/r2b_k1t_ncu_full_raw.csv); algorithmic: 1000 frames x 8 operand tiles x " \
+                     "80 KB = 655.4 MB read once + 24 MB of row / column keys written: no re-reads from DRAM"
 METRIC = "frame-pairs/sec (match+E-RANSAC+pose)"
 WORKLOAD = "configs[1]: 1000-frame synthetic drone sequence, ORB 2000 kp, consecutive-pair VO " \
            "with trajectory chaining"

@@ -17,12 +17,13 @@ timeout 600 python tools/gpu_slam_traj.py orb 20 2000 5 > gpurun_out/slam_traj.l
 timeout 600 python tools/gpu_orb_bench.py 32 2000 10 > gpurun_out/orb_bench.json 2> gpurun_out/orb_bench.err
 # compute-sanitizer: the kernels that hand-roll mbarrier / bulk-copy / TMEM synchronisation
 for tool in memcheck racecheck synccheck; do
-  timeout 900 compute-sanitizer --tool $tool --print-limit 20 python tools/gpu_sanitize_cases.py > gpurun_out/sanitizer_$tool.log 2>&1; echo "rc=$?" >> gpurun_out/sanitizer_$tool.log
+  timeout 400 compute-sanitizer --tool $tool --print-limit 20 python tools/gpu_sanitize_cases.py > gpurun_out/sanitizer_$tool.log 2>&1; echo "rc=$?" >> gpurun_out/sanitizer_$tool.log
 done
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_bench_c2.csv python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_launch.log 2>&1
 if [ "$1" = "full" ]; then
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:htc.*match_kernel -s 3 -c 1 -o gpurun_out/k1t_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1t.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:l8.*match_kernel -s 2 -c 1 -o gpurun_out/k6i_full python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:l8.*match_kernel -s 40 -c 1 -o gpurun_out/k6i_full python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
 fi
 ls -la gpurun_out | head -60
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; head -c 3000 gpurun_out/bench.json

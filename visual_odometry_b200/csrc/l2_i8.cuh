@@ -15,7 +15,9 @@
 //   * the cross-check direction is a second MMA pass with the operands swapped, as in K1t: at
 //     640 tensor cycles per 128 x 256 accumulator the epilogue, not the MMA, is what is scarce.
 // Kernel skeleton = hamming_tc.cuh (persistent, warp-specialised, two 256-column accumulators that
-// double-buffer each other, work item = (pair, direction, 256-row block)).
+// double-buffer each other, work item = (pair, direction, 256-row block)), but SIXTEEN epilogue
+// warps (4 per scheduler, 64 columns each): with 8 the IMAD/max chains were latency-bound
+// (measured: 1614 clocks per accumulator against ~600 of issue).
 #pragma once
 #include "hamming_tc.cuh"
 
@@ -29,9 +31,9 @@ constexpr int TILE_BYTES = 12 * KG_BYTES + 1024;    // data 8, ones 2, ext 2, + 
 constexpr int A_BYTES = 10 * KG_BYTES;              // data + ones
 constexpr int B_BYTES = 10 * KG_BYTES;              // data + ext
 constexpr uint32_t LBO = KG_BYTES, SBO = 128;
-constexpr int NSTAGE = 4;
+constexpr int NSTAGE = 3;
 constexpr int NCC = 4;                              // ring of per-tile column constants
-constexpr int EPI_WARPS = 8;
+constexpr int EPI_WARPS = 16;                    // warp & 3 = TMEM lane quarter, warp >> 2 = 64-column quarter
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr int H_MAX = 127 * 127 * 31 + 126;         // largest floor(|b|^2/2) the ext group can hold
 constexpr int KEY_NONE_BELOW = -(H_MAX + 1) * 512;  // keys of padded columns lie below this
@@ -116,7 +118,7 @@ struct __align__(1024) Smem {
   uint8_t A[A_BYTES];
   uint8_t B[NSTAGE][B_BYTES];
   int32_t cc[NCC][ROWS];
-  uint4 part[2][2][128];         // [item parity][row block][row]: (k1, t1, k2, t2) of column half 1
+  uint4 part[2][3][2][128];      // [item parity][column quarter - 1][row block][row]: (k1, t1, k2, t2)
   uint64_t full_a, empty_a;
   uint64_t full_b[NSTAGE], empty_b[NSTAGE];
   uint64_t full_c[NCC], empty_c[NCC];
@@ -248,7 +250,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
     }
   } else {
     // ===== epilogue warps =====
-    const int quarter = warp & 3, half = warp >> 2;
+    const int quarter = warp & 3, cq = warp >> 2;
     const int rl = quarter * 32 + lane;
     const int mul = 512 + (int)(n_items < 0);      // = 512, opaque: keeps the IMAD form
     uint32_t use[2] = {0u, 0u}, n_it = 0, g = 0;
@@ -261,14 +263,14 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
       for (int t = 0; t < it.ntile; ++t, ++g) {
         const int sc = g % NCC;
         mbar_wait(&S.full_c[sc], (g / NCC) & 1);
-        const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][half * 128]);
+        const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][cq * 64]);
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb) {
           if (rb >= it.nrb) break;
           mbar_wait(&S.tmem_full[rb], use[rb] & 1);
           ++use[rb];
           tc::fence_after_sync();
-          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS + half * 128;
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS + cq * 64;
           uint32_t va[32], vb[32];
           int h = MININT, l = MININT;
           auto rank = [&](uint32_t (&v)[32], int chunk) {
@@ -293,38 +295,35 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
           tc::ld_32x32_issue(taddr + 32, vb);
           rank(va, 0);
           tc::ld_wait(vb);
-          tc::ld_32x32_issue(taddr + 64, va);
-          rank(vb, 1);
-          tc::ld_wait(va);
-          tc::ld_32x32_issue(taddr + 96, vb);
-          rank(va, 2);
-          tc::ld_wait(vb);
           tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);
-          rank(vb, 3);
+          rank(vb, 1);
           fold_tile<TOP2>(st[rb], h, l, t);
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&S.empty_c[sc]);     // this warp is done with the tile's constants
       }
       // ---- merge the two column halves, convert to squared distances, write ----
-      if (half == 1) {
+      if (cq > 0) {
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb)
-          S.part[n_it & 1][rb][rl] = make_uint4((uint32_t)st[rb].k1, (uint32_t)st[rb].t1, (uint32_t)st[rb].k2,
-                                                (uint32_t)st[rb].t2);
+          S.part[n_it & 1][cq - 1][rb][rl] = make_uint4((uint32_t)st[rb].k1, (uint32_t)st[rb].t1,
+                                                        (uint32_t)st[rb].k2, (uint32_t)st[rb].t2);
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (half == 0) {
+      asm volatile("bar.sync 1, 512;" ::: "memory");
+      if (cq == 0) {
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb) {
           if (rb >= it.nrb) break;
           Top m = st[rb];
           if (m.t1 < 0 && m.t2 >= 0) { m.k1 = m.k2; m.t1 = m.t2; m.t2 = -1; }
-          const uint4 o = S.part[n_it & 1][rb][rl];
-          insert(m, (int)o.x, (int)o.y);
-          if (TOP2) insert(m, (int)o.z, (int)o.w);
+#pragma unroll
+          for (int pq = 0; pq < 3; ++pq) {
+            const uint4 o = S.part[n_it & 1][pq][rb][rl];
+            insert(m, (int)o.x, (int)o.y);
+            if (TOP2) insert(m, (int)o.z, (int)o.w);
+          }
           const int row = it.rbp * ROWS + rb * 128 + rl;
           if (row < it.nq) {
             const int na = (int)norms[(size_t)it.fq * norm_stride + row];

@@ -85,9 +85,13 @@ __device__ __forceinline__ uint32_t cvrng_next(uint64_t& s) {
   return (uint32_t)s;
 }
 // RANSACPointSetRegistrator::getSubset: 5 distinct indices, redraw on duplicate
-__device__ __forceinline__ void draw_sample(uint64_t& s, int count, int32_t* idx) {
+// x % n for 32-bit x, n without a division (Lemire's fastmod: M = floor(2^64 / n) + 1, exact)
+__device__ __forceinline__ uint32_t fastmod_u32(uint32_t x, uint64_t M, uint32_t n) {
+  return (uint32_t)__umul64hi(M * (uint64_t)x, (uint64_t)n);
+}
+__device__ __forceinline__ void draw_sample(uint64_t& s, int count, uint64_t M, int32_t* idx) {
   for (int i = 0; i < 5;) {
-    const int v = (int)(cvrng_next(s) % (uint32_t)count);
+    const int v = (int)fastmod_u32(cvrng_next(s), M, (uint32_t)count);
     bool dup = false;
     for (int j = 0; j < i; ++j) dup |= (idx[j] == v);
     idx[i] = v;
@@ -131,10 +135,11 @@ __global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int round, i
     const int p = list[a];
     uint64_t s = w.rng[p];
     const int count = m[p];
+    const uint64_t M = 0xffffffffffffffffull / (uint32_t)count + 1ull;
     int32_t* out = w.samples + (size_t)p * chunk_stride * 5;
     for (int it = 0; it < chunk; ++it) {
       int32_t idx[5];
-      draw_sample(s, count, idx);
+      draw_sample(s, count, M, idx);
 #pragma unroll
       for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
     }
@@ -582,9 +587,10 @@ extern "C" int vo_sampson_score(const double* E, int H, const double* pts_n, int
 __global__ void samples_standalone_kernel(int count, int n_iters, int32_t* out) {
   if (blockIdx.x || threadIdx.x) return;
   uint64_t s = 0xffffffffffffffffull;
+  const uint64_t M = 0xffffffffffffffffull / (uint32_t)count + 1ull;
   for (int it = 0; it < n_iters; ++it) {
     int32_t idx[5];
-    draw_sample(s, count, idx);
+    draw_sample(s, count, M, idx);
     for (int k = 0; k < 5; ++k) out[5 * it + k] = idx[k];
   }
 }
