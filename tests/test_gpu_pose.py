@@ -116,7 +116,13 @@ def test_pipeline_sequence_vs_reference_path_and_ground_truth(cuda_dev):
         Rs.append(ref["R"]); ts.append(ref["tvec"])
     record_parity("pipeline_sequence_vs_reference_path", pairs=F - 1, inlier_counts_equal=exact,
                   pairs_with_different_mask=off_pairs)
-    assert exact >= F - 2
+    # measured (profiles/parity_r2.json): 15 of 16 pairs identical; on pair 5 ONE correspondence on
+    # the threshold flips (911 vs 912 inliers: the five-point roots differ from cv2's Durand-Kerner
+    # roots at 1e-8) and the pose stays within 2e-6 rad / 1.3e-4 of cv2's
+    assert exact >= F - 2 and len(off_pairs) <= 1
+    for o in off_pairs:
+        assert abs(o["inliers"][0] - o["inliers"][1]) <= 2
+        assert o["rot_rad_vs_cv2"] < 1e-4 and o["t_abs_vs_cv2"] < 5e-4
     if exact == F - 1:
         assert np.abs(out["poses"] - RP.chain_poses(Rs, ts)).max() < 1e-3
 
@@ -172,4 +178,4 @@ def test_full_size_c4_batch_vs_reference_path(cuda_dev):
                               "t_abs_vs_cv2": float(np.abs(out["t"][b] - ref["tvec"].ravel()).max())})
     record_parity("c4_batch_vs_reference_path", pairs_checked=3, masks_identical=exact,
                   pairs_with_different_mask=off_pairs)
-    assert exact >= 2
+    assert exact == 3                         # measured: masks identical on 3 / 3

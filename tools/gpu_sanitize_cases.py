@@ -51,11 +51,12 @@ dist = torch.empty(B, N, dtype=torch.float32, device=dev)
 n_out = torch.empty(B, dtype=torch.int32, device=dev)
 wsb = lib.vo_match_workspace_bytes(F, B, N)
 ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+nkp_d, pairs_d = torch.from_numpy(nkp).to(dev), torch.from_numpy(pairs).to(dev)
 for mode in (0, 1):
     lib.vo_debug_hamming(2)
     _lib.check(lib.vo_match_hamming_batch(
-        _lib.ptr(desc), _lib.ptr(torch.from_numpy(nkp).to(dev)), _lib.ptr(kp), N, F,
-        _lib.ptr(torch.from_numpy(pairs).to(dev)), B, mode, -1.0, _lib.ptr(q), _lib.ptr(t), _lib.ptr(dist),
+        _lib.ptr(desc), _lib.ptr(nkp_d), _lib.ptr(kp), N, F,
+        _lib.ptr(pairs_d), B, mode, -1.0, _lib.ptr(q), _lib.ptr(t), _lib.ptr(dist),
         None, None, None, _lib.ptr(n_out), _lib.ptr(ws), wsb, _lib.cur_stream()))
     torch.cuda.synchronize()
     lib.vo_debug_hamming(0)

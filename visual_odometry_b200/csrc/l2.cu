@@ -996,11 +996,11 @@ extern "C" int vo_match_l2_batch(const float* desc, const int32_t* nkp, const fl
       if (mode == VO_MATCH_MUTUAL)
         l8::match_kernel<false><<<grid, l8::THREADS, smem8, st>>>(w.tiles8, nkp, pairs, n_cap, ntile8, nd, n_items,
                                                                  w.norms, nblk * L2_BLK, splits, nblk * L2_BLK,
-                                                                 w.flags, w.rowbest);
+                                                                 w.flags, w.rowbest, (g_l2_debug_host >> 8) & 3);
       else
         l8::match_kernel<true><<<grid, l8::THREADS, smem8, st>>>(w.tiles8, nkp, pairs, n_cap, ntile8, nd, n_items,
                                                                 w.norms, nblk * L2_BLK, splits, nblk * L2_BLK,
-                                                                w.flags, w.rowbest);
+                                                                w.flags, w.rowbest, (g_l2_debug_host >> 8) & 3);
     }
     auto launch = [&](int mode_k, int nd, int run_if) {
       const long n_items = (long)n_pairs * nd * splits * nrbp;

@@ -15,9 +15,10 @@
 //   * the cross-check direction is a second MMA pass with the operands swapped, as in K1t: at
 //     640 tensor cycles per 128 x 256 accumulator the epilogue, not the MMA, is what is scarce.
 // Kernel skeleton = hamming_tc.cuh (persistent, warp-specialised, two 256-column accumulators that
-// double-buffer each other, work item = (pair, direction, 256-row block)), but SIXTEEN epilogue
-// warps (4 per scheduler, 64 columns each): with 8 the IMAD/max chains were latency-bound
-// (measured: 1614 clocks per accumulator against ~600 of issue).
+// double-buffer each other, work item = (pair, direction, 256-row block)).  Measured
+// (profiles/r2_summary.md): with the whole epilogue removed the MMA + bulk-copy side alone needs
+// 1263 clocks per accumulator (640 of MMA): at 41 KB per 1280 tensor clocks the four smem stages
+// do not cover the L2 latency; 16 epilogue warps with three stages were slower (0.396 vs 0.294 ms).
 #pragma once
 #include "hamming_tc.cuh"
 
@@ -31,9 +32,9 @@ constexpr int TILE_BYTES = 12 * KG_BYTES + 1024;    // data 8, ones 2, ext 2, + 
 constexpr int A_BYTES = 10 * KG_BYTES;              // data + ones
 constexpr int B_BYTES = 10 * KG_BYTES;              // data + ext
 constexpr uint32_t LBO = KG_BYTES, SBO = 128;
-constexpr int NSTAGE = 3;
+constexpr int NSTAGE = 4;
 constexpr int NCC = 4;                              // ring of per-tile column constants
-constexpr int EPI_WARPS = 16;                    // warp & 3 = TMEM lane quarter, warp >> 2 = 64-column quarter
+constexpr int EPI_WARPS = 8;                     // warp & 3 = TMEM lane quarter, warp >> 2 = 128-column half
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr int H_MAX = 127 * 127 * 31 + 126;         // largest floor(|b|^2/2) the ext group can hold
 constexpr int KEY_NONE_BELOW = -(H_MAX + 1) * 512;  // keys of padded columns lie below this
@@ -118,7 +119,7 @@ struct __align__(1024) Smem {
   uint8_t A[A_BYTES];
   uint8_t B[NSTAGE][B_BYTES];
   int32_t cc[NCC][ROWS];
-  uint4 part[2][3][2][128];      // [item parity][column quarter - 1][row block][row]: (k1, t1, k2, t2)
+  uint4 part[2][1][2][128];      // [item parity][column half - 1][row block][row]: (k1, t1, k2, t2)
   uint64_t full_a, empty_a;
   uint64_t full_b[NSTAGE], empty_b[NSTAGE];
   uint64_t full_c[NCC], empty_c[NCC];
@@ -169,7 +170,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
              const int32_t* __restrict__ pairs, int n_cap, int ntile_cap, int ndir, long n_items,
              const float* __restrict__ norms, int norm_stride, int n_splits, int row_stride,
-             const int32_t* __restrict__ flags, float4* __restrict__ rowbest) {
+             const int32_t* __restrict__ flags, float4* __restrict__ rowbest, int dbg) {
+  // dbg (timing experiments, results wrong): bit 0 = no ranking, bit 1 = no TMEM loads either
   if (flags[2] != 0) return;     // not uint8 data: the bf16 kernel of l2.cu runs instead
   extern __shared__ uint8_t smem_raw[];
   Smem& S = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -263,17 +265,18 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
       for (int t = 0; t < it.ntile; ++t, ++g) {
         const int sc = g % NCC;
         mbar_wait(&S.full_c[sc], (g / NCC) & 1);
-        const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][cq * 64]);
+        const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][cq * 128]);
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb) {
           if (rb >= it.nrb) break;
           mbar_wait(&S.tmem_full[rb], use[rb] & 1);
           ++use[rb];
           tc::fence_after_sync();
-          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS + cq * 64;
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS + cq * 128;
           uint32_t va[32], vb[32];
           int h = MININT, l = MININT;
           auto rank = [&](uint32_t (&v)[32], int chunk) {
+            if (dbg & 1) return;
 #pragma unroll
             for (int c4 = 0; c4 < 8; ++c4) {
               const uint4 cc = ccp[chunk * 8 + c4];       // broadcast shared-memory read
@@ -290,15 +293,24 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
               h = max(h, htc::max32(v));
             }
           };
-          tc::ld_32x32_issue(taddr, va);
-          tc::ld_wait(va);
-          tc::ld_32x32_issue(taddr + 32, vb);
+          if (dbg & 2) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) va[c] = vb[c] = (uint32_t)(c + lane);
+          } else {
+            tc::ld_32x32_issue(taddr, va);
+            tc::ld_wait(va);
+            tc::ld_32x32_issue(taddr + 32, vb);
+          }
           rank(va, 0);
-          tc::ld_wait(vb);
+          if (!(dbg & 2)) { tc::ld_wait(vb); tc::ld_32x32_issue(taddr + 64, va); }
+          rank(vb, 1);
+          if (!(dbg & 2)) { tc::ld_wait(va); tc::ld_32x32_issue(taddr + 96, vb); }
+          rank(va, 2);
+          if (!(dbg & 2)) tc::ld_wait(vb);
           tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);
-          rank(vb, 1);
+          rank(vb, 3);
           fold_tile<TOP2>(st[rb], h, l, t);
         }
         __syncwarp();
@@ -311,7 +323,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
           S.part[n_it & 1][cq - 1][rb][rl] = make_uint4((uint32_t)st[rb].k1, (uint32_t)st[rb].t1,
                                                         (uint32_t)st[rb].k2, (uint32_t)st[rb].t2);
       }
-      asm volatile("bar.sync 1, 512;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (cq == 0) {
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb) {
@@ -319,7 +331,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
           Top m = st[rb];
           if (m.t1 < 0 && m.t2 >= 0) { m.k1 = m.k2; m.t1 = m.t2; m.t2 = -1; }
 #pragma unroll
-          for (int pq = 0; pq < 3; ++pq) {
+          for (int pq = 0; pq < 1; ++pq) {
             const uint4 o = S.part[n_it & 1][pq][rb][rl];
             insert(m, (int)o.x, (int)o.y);
             if (TOP2) insert(m, (int)o.z, (int)o.w);
