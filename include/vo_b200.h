@@ -62,6 +62,21 @@ int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int m
                      int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                      int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
+/* no-allocation variant of vo_match_hamming.  It has NO counterpart in the reference and was
+ * added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it): the scratch of the
+ * match (132 bytes per key point) lives in a file-scope device array of the library
+ * (1 081 344 bytes per GPU, held until the process exits) instead of a caller workspace.
+ * Limit: n1, n2 <= vo_match_hamming_static_max_keypoints() = 8192; larger sizes are rejected with
+ * VO_ERR_WORKSPACE.  Same arguments, same results as vo_match_hamming without ws / ws_bytes; it
+ * calls no cudaMalloc / cudaFree / allocating routine.  Every call shares the one array (a call
+ * finds the previous call's contents and re-initialises what it reads): calls on one stream are
+ * independent, calls that OVERLAP on the GPU (two streams, two threads) race. */
+int vo_match_hamming_static_max_keypoints(void);
+int vo_match_hamming_static(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode,
+                            double ratio, int32_t* q, int32_t* t, float* dist, int32_t* t2,
+                            float* dist2, int32_t* n_out, void* stream);
+
 /* ---- K6: SIFT/L2 matching on tensor cores (BFMatcher(NORM_L2), visual_slam.py:19) ----
  * desc float32 [n_frames, n_cap, 128]; same outputs; dist = float32 sqrt(sum (a-b)^2).
  * Every frame 0..n_frames-1 is converted once (bf16 tiles + norms) and shared by its pairs.

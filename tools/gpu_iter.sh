@@ -1,9 +1,6 @@
 #!/bin/bash
-# one GPU-box call while iterating (K6i timing variants + capture)
+# one GPU-box call: the new no-allocation entry point alone in a fresh process, then the whole suite
 mkdir -p gpurun_out
-timeout 300 python tools/gpu_sanitize_cases.py > gpurun_out/small_cases.log 2>&1; echo "rc=$?" >> gpurun_out/small_cases.log
-timeout 300 python tools/gpu_check_l2.py 256 2>&1 | grep '"mode"' > gpurun_out/l2_i8_norank.log
-timeout 300 python tools/gpu_check_l2.py 768 2>&1 | grep '"mode"' > gpurun_out/l2_i8_noload.log
-timeout 300 python tools/gpu_check_l2.py 2>&1 | grep '"mode"\|ALL' > gpurun_out/l2_i8_default.log
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 40 -c 1 -o gpurun_out/k6i_full python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
-tail -3 gpurun_out/small_cases.log; cat gpurun_out/l2_i8_norank.log gpurun_out/l2_i8_noload.log gpurun_out/l2_i8_default.log | cut -c1-200
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > gpurun_out/pytest_no_alloc_alone.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_no_alloc_alone.log
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
+tail -4 gpurun_out/pytest_no_alloc_alone.log | cut -c1-200; tail -4 gpurun_out/pytest_gpu.log | cut -c1-200

@@ -494,3 +494,67 @@ extern "C" int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, in
   return launch_hamming(d1, d2, n1, n2, nullptr, nullptr, n_cap, nullptr, 1, mode, ratio, q, t,
                         dist, t2, dist2, nullptr, n_out, ws, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------- no-allocation variant
+// vo_match_hamming with its scratch (row top-2 keys per train split + column minima, 132 bytes per
+// key point) in a file-scope device array instead of a caller workspace: for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No
+// counterpart in the reference.
+//   * limit: max(n1, n2) <= VO_STATIC_MAX_KP = 8192 key points (1 081 344 bytes of device memory,
+//     held by every GPU that loads the library until the process exits);
+//   * the array's name is only a host-side stand-in in host code: its device address is taken
+//     once per device with cudaGetSymbolAddress (that device current) and passed to the kernels;
+//   * every call shares the array and finds the previous call's contents in it: the column minima
+//     are re-initialised by the launch group itself (cudaMemsetAsync on the caller's stream) and
+//     every row key that is read is written first, so back-to-back calls on ONE stream are
+//     independent; calls that overlap on the GPU (two streams, two host threads) RACE on it.
+// Calls no cudaMalloc / cudaFree / allocating library routine.
+constexpr int VO_STATIC_MAX_KP = 8192;
+static __device__ __align__(256) uint32_t g_static_scratch[(size_t)VO_STATIC_MAX_KP * (16 * 2 + 1)];
+
+static int static_scratch_address(void** out) {
+  static void* addr[64] = {nullptr};
+  static bool known[64] = {false};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("vo_match_hamming_static: cannot identify the current device");
+    return VO_ERR_CUDA;
+  }
+  if (!known[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("vo_match_hamming_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return VO_ERR_CUDA;
+    }
+    addr[dev] = p;
+    known[dev] = true;
+  }
+  *out = addr[dev];
+  return VO_OK;
+}
+
+extern "C" int vo_match_hamming_static_max_keypoints(void) { return VO_STATIC_MAX_KP; }
+
+extern "C" int vo_match_hamming_static(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode,
+                                       double ratio, int32_t* q, int32_t* t, float* dist, int32_t* t2,
+                                       float* dist2, int32_t* n_out, void* stream) {
+  VO_REQUIRE(q && t && dist && n_out, VO_ERR_INVALID_ARG, "vo_match_hamming_static: null pointer");
+  VO_REQUIRE(n1 >= 0 && n2 >= 0, VO_ERR_INVALID_ARG, "vo_match_hamming_static: negative descriptor count");
+  VO_REQUIRE(n1 <= VO_STATIC_MAX_KP && n2 <= VO_STATIC_MAX_KP, VO_ERR_WORKSPACE,
+             "vo_match_hamming_static: %d x %d descriptors exceed the static scratch (at most %d per "
+             "side); use vo_match_hamming with a caller workspace", n1, n2, VO_STATIC_MAX_KP);
+  VO_REQUIRE(mode == VO_MATCH_MUTUAL || mode == VO_MATCH_KNN2_RATIO, VO_ERR_INVALID_ARG,
+             "vo_match_hamming_static: bad mode %d", mode);
+  const int n_cap = n1 > n2 ? n1 : n2;
+  if (n1 == 0 || n2 == 0) {
+    cudaMemsetAsync(n_out, 0, sizeof(int32_t), (cudaStream_t)stream);
+    return check_launch("vo_match_hamming_static");
+  }
+  VO_REQUIRE(d1 && d2, VO_ERR_INVALID_ARG, "vo_match_hamming_static: null descriptors");
+  void* ws = nullptr;
+  const int rc = static_scratch_address(&ws);
+  if (rc != VO_OK) return rc;
+  return launch_hamming(d1, d2, n1, n2, nullptr, nullptr, n_cap, nullptr, 1, mode, ratio, q, t,
+                        dist, t2, dist2, nullptr, n_out, ws, (cudaStream_t)stream);
+}
