@@ -1,6 +1,5 @@
 #!/bin/bash
-# one GPU-box call: the new no-allocation entry point alone in a fresh process, then the whole suite
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q > gpurun_out/pytest_no_alloc_alone.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_no_alloc_alone.log
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
-tail -4 gpurun_out/pytest_no_alloc_alone.log | cut -c1-200; tail -4 gpurun_out/pytest_gpu.log | cut -c1-200
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
+ncu -i gpurun_out/k3_full.ncu-rep --page source --csv > gpurun_out/k3_source.csv 2>/dev/null
+ls -la gpurun_out/k3*

@@ -98,6 +98,18 @@ def triangulate_points(P1, P2, points1_2xN, points2_2xN):
     return X.cpu().numpy().T.astype(out_dtype)
 
 
+# The reference prints every relative pose and every reconstructed point cloud
+# (src/image_pair.py:313-314, 352-354); kept by default (drop-in), switched off by
+# VO_B200_QUIET=1 or `image_pair.VERBOSE = False` (the array formatting alone costs ~1 ms per pair)
+import os as _os
+VERBOSE = _os.environ.get("VO_B200_QUIET", "") in ("", "0")
+
+
+def _say(*a):
+    if VERBOSE:
+        print(*a)
+
+
 class ImagePair():
     """
     Class for working with image pairs (reference src/image_pair.py:222).
@@ -187,8 +199,8 @@ class ImagePair():
         pose = np.eye(4)
         pose[:3, :3], pose[:3, 3] = self.R, self.t.ravel()
         self.relative_pose = pose
-        print("relative movement in image pair")
-        print(self.relative_pose)
+        _say("relative movement in image pair")
+        _say(self.relative_pose)
 
     def reconstruct_3d_points(self, matches=None,
                               first_projection_matrix=None,
@@ -209,9 +221,10 @@ class ImagePair():
         self.points3d_reconstr = X
         self.matches_with_3d_information = [
             Match3D(*mt, (X[0, k], X[1, k], X[2, k])) for k, mt in enumerate(matches)]
-        print("Reconstructed points")
-        print(self.points3d_reconstr.transpose().shape)
-        print(self.points3d_reconstr.transpose())
+        _say("Reconstructed points")
+        if VERBOSE:
+            _say(self.points3d_reconstr.transpose().shape)
+            _say(self.points3d_reconstr.transpose())
 
     # ------------------------------------------------------------------ legacy API (:46-220)
     def set_images(self, img1, img2):
