@@ -707,11 +707,14 @@ extern "C" int vo_bundle_adjust(double* poses, const uint8_t* fixed, int n_cams,
   BAWs w = ba_carve(base, C, P, M);
   const int nbo = (M + BA_THREADS - 1) / BA_THREADS, nbp = (P + BA_THREADS - 1) / BA_THREADS;
   const int nbp4 = (int)(((size_t)P * BA_PT_LANES + BA_THREADS - 1) / BA_THREADS);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[64] = {false};     // cudaFuncSetAttribute is per device
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  cur_dev &= 63;
+  if (!attr_done[cur_dev]) {
     cudaFuncSetAttribute(ba_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(double) * ((size_t)6 * BA_MAX_CAMS * (6 * BA_MAX_CAMS + 1) + 12 * BA_MAX_CAMS)));
-    attr_done = true;
+    attr_done[cur_dev] = true;
   }
 
   // adjacency lists

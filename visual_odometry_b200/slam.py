@@ -59,7 +59,10 @@ class DeviceSlam:
         p = self.pipe
         f = getattr(self, "_n_frames", 0)
         if f >= self.max_frames:
-            raise RuntimeError("DeviceSlam: max_frames exceeded")
+            # the track arrays are sized for max_frames * n_cap feature ids up front (flat device
+            # arrays, no ring buffer): a stream longer than that needs a new DeviceSlam (the
+            # reference's dicts grow without bound; its camera window is 18 frames)
+            raise RuntimeError("DeviceSlam: max_frames exceeded (track arrays are sized up front)")
         n = int(desc.shape[0])
         p.desc[f, :n].copy_(torch.from_numpy(np.ascontiguousarray(desc)))
         p.kp[f, :n].copy_(torch.from_numpy(np.ascontiguousarray(kp, np.float32)))
