@@ -276,7 +276,9 @@ def bench_configs(dev, peaks):
         flop = 2.0 * 5000 * 5000 * 128 * 64
         tf = flop / (r["match_kernel_ms"] * 1e-3) / 1e12 if r["match_kernel_ms"] else None
         r["what"] = "configs[2]: SIFT 5000 kp, L2 knn + ratio 0.75 on tcgen05, E-RANSAC 4096 fixed hypotheses, 64 pairs"
-        r["roofline_k6"] = {"kernel": "l2_top2_tc_kernel (K6)", "bound": "tensor", "achieved": tf,
+        r["roofline_k6"] = {"kernel": "l8::match_kernel (K6i: integer SIFT data as a uint8 tcgen05 kind::i8 contraction; "
+                                      "other float data runs the bf16 kernel l2_top2_tc_kernel)",
+                            "bound": "tensor", "achieved": tf,
                             "peak": peaks.get("bf16_tflops"), "unit": "TFLOP/s",
                             "frac": (tf / peaks["bf16_tflops"]) if tf and peaks.get("bf16_tflops") else None,
                             "peak_kind": "bf16_tflops (burst: the kernel is timed alone)",
@@ -491,6 +493,15 @@ def run_ours(args, rank, world, local_rank):
     sync_all()
     if gather:
         gather.collective_ms()
+    # one step's upload alone, every rank at the same time: what the host side can deliver.  When
+    # this is longer than the device step, the end-to-end rate is bound by host->device bandwidth.
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record()
+    for name in ("desc", "kp", "nkp"):
+        getattr(pipe, name).copy_(pin[name], non_blocking=True)
+    h1.record()
+    sync_all()
+    h2d_alone_ms = h0.elapsed_time(h1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     h2d, d2h = pipe.run_stream(N_FRAMES, B, args.steps, after_compute=after)
@@ -512,10 +523,10 @@ def run_ours(args, rank, world, local_rank):
     k2_ms = kernels_ms["ransac_score (K2)"]
     lib.vo_profile_enable(0)
 
-    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([dev_ms, e2e_ms, h2d_alone_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    dev_ms, e2e_ms, h2d_alone_ms = float(t[0]), float(t[1]), float(t[2])
 
     strong = None
     if world > 1 and not args.no_configs:
@@ -529,6 +540,7 @@ def run_ours(args, rank, world, local_rank):
         return
 
     steps = args.steps
+    steps_for_bound = max(steps, 1)
     total_pairs = B * world * steps
     value = total_pairs / (dev_ms * 1e-3)
     k1_avg_s = (k1_ms / max(k1_n, 1)) * 1e-3
@@ -559,6 +571,10 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": e2e_step,
                 "h2d_exposed_ms": max(0.0, e2e_step - dev_ms / steps),
                 "collective_ms": collective_ms,
+                "h2d_alone_ms": h2d_alone_ms,
+                "h2d_gbs_per_rank_all_ranks_uploading": (h2d / 1e9) / (h2d_alone_ms * 1e-3) if h2d_alone_ms > 0 else None,
+                "bound": "host->device bandwidth (one step's upload alone takes longer than the device step)"
+                if h2d_alone_ms > dev_ms / steps_for_bound else "device",
                 "api": "PairPipeline.run_stream: per step H2D from pinned host buffers, the chain, D2H of "
                        "poses and counts; the upload of step k+1 overlaps the compute of step k"},
         "gpu_launches": int((pipe.launches_per_run() + (1 if world > 1 else 0)) * steps),

@@ -1,5 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
-ncu -i gpurun_out/k3_full.ncu-rep --page source --csv > gpurun_out/k3_source.csv 2>/dev/null
-ls -la gpurun_out/k3*
+timeout 300 python tools/gpu_check_l2.py 2>&1 | grep 'ALL\|FAIL\|MISMATCH' > gpurun_out/l2_i8_ok.log
+timeout 300 python tools/gpu_check_l2.py 256 2>&1 | grep 'ALL\|FAIL\|MISMATCH' >> gpurun_out/l2_i8_ok.log
+timeout 300 python tools/gpu_check_l2.py 512 2>&1 | grep 'ALL\|FAIL\|MISMATCH' >> gpurun_out/l2_i8_ok.log
+for m in 0 1; do for f in 0 256 512 128; do timeout 120 python tools/gpu_l2_one.py $m $f; done; done > gpurun_out/l2_one.log 2>&1
+for f in 2 10 26 1; do timeout 120 python tools/gpu_hamming_one.py $f; done > gpurun_out/k1t_one.log 2>&1
+timeout 300 python -m pytest tests/test_gpu_match.py tests/test_gpu_match_l2.py -x -q 2>&1 | tail -2 > gpurun_out/pytest_match.log
+cat gpurun_out/l2_i8_ok.log gpurun_out/l2_one.log gpurun_out/k1t_one.log gpurun_out/pytest_match.log | cut -c1-200

@@ -294,12 +294,11 @@ static size_t popc_workspace_bytes(int n_pairs, int n_cap) {
 }
 
 // bits 0..1: 0 = choose by batch size, 1 = always the popc kernel, 2 = always the tensor-core
-// kernel (needs n_frames > 0); bits 2..: htc::g_debug (timing experiments)
+// kernel (needs n_frames > 0); bits 3..4: timing-experiment instantiations of the tensor kernel
 static int g_hamming_debug = 0;
 extern "C" int vo_debug_hamming(int flags) {
   g_hamming_debug = flags;
-  const int kd = flags >> 2;
-  return cudaMemcpyToSymbol(htc::g_debug, &kd, sizeof(int)) == cudaSuccess ? VO_OK : VO_ERR_CUDA;
+  return VO_OK;
 }
 
 static int device_sms() {
@@ -421,7 +420,9 @@ static int launch_hamming_tc(const uint8_t* desc, const int32_t* nkp, const floa
   dev &= 63;
   if (!attr_set[dev]) {
     if (cudaFuncSetAttribute(htc::match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
-        cudaFuncSetAttribute(htc::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+        cudaFuncSetAttribute(htc::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(htc::match_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(htc::match_kernel<false, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
       return check_launch("vo_match_hamming_batch(smem attribute)");
     attr_set[dev] = true;
   }
@@ -434,7 +435,14 @@ static int launch_hamming_tc(const uint8_t* desc, const int32_t* nkp, const floa
   const int grid = (int)(n_items < device_sms() ? n_items : device_sms());
   {
     ProfScope prof(0, st);
-    if (mode == VO_MATCH_MUTUAL)
+    const int kd = (g_hamming_debug >> 2) & 6;     // timing experiments: compile-time instantiations
+    if (mode == VO_MATCH_MUTUAL && kd == 2)
+      htc::match_kernel<false, 2><<<grid, htc::THREADS, smem, st>>>(w.tiles, nkp, pairs, n_cap, ntile, ndir,
+                                                                   n_items, w.rowbest, w.colmin);
+    else if (mode == VO_MATCH_MUTUAL && kd == 6)
+      htc::match_kernel<false, 6><<<grid, htc::THREADS, smem, st>>>(w.tiles, nkp, pairs, n_cap, ntile, ndir,
+                                                                   n_items, w.rowbest, w.colmin);
+    else if (mode == VO_MATCH_MUTUAL)
       htc::match_kernel<false><<<grid, htc::THREADS, smem, st>>>(w.tiles, nkp, pairs, n_cap, ntile, ndir,
                                                                 n_items, w.rowbest, w.colmin);
     else

@@ -41,7 +41,6 @@ constexpr int EPI_WARPS = 8;                    // warp & 3 = TMEM lane quarter,
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr int KEY_MININT = (int)0x80000000;
 
-static __device__ int g_debug = 0;   // bit 1: epilogue skips the ranking, bit 2: skips the TMEM loads too
 
 // kind::i8: A, B signed 8 bit, K-major, D = s32, M x N
 __host__ __device__ constexpr uint32_t idesc_s8_s32(int M, int N) {
@@ -187,7 +186,9 @@ __device__ __forceinline__ uint32_t out_key(int g) {
   return (h << 16) | (65535u - ((uint32_t)g & 65535u));
 }
 
-template <bool TOP2>
+// DBG (compile time; a run-time switch around the TMEM loads would cost time by itself): timing
+// experiments whose results are wrong: 2 = the epilogue skips the ranking, 6 = and the TMEM loads.
+template <bool TOP2, int DBG = 0>
 __global__ void __launch_bounds__(THREADS, 1)
 match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
              const int32_t* __restrict__ pairs, int n_cap, int ntile_cap, int ndir, long n_items,
@@ -209,7 +210,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = S.tmem_base;
-  const int dbg = g_debug;
+  constexpr int dbg = DBG;
 
   if (warp == EPI_WARPS + 1) {
     // ===== bulk-copy producer: the row operand once per item, 72 KB per column tile =====
@@ -286,7 +287,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
           uint32_t va[32], vb[32];
           int h = KEY_MININT, l = KEY_MININT;
           auto rank = [&](const uint32_t (&v)[32]) {
-            if (dbg & 2) return;
+            if constexpr ((dbg & 2) != 0) return;
             if (TOP2) {
               int ch, cl;
               top2_32(v, ch, cl);
@@ -295,20 +296,25 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
               h = max(h, max32(v));
             }
           };
-          if (dbg & 4) {
+          if constexpr ((dbg & 4) != 0) {
 #pragma unroll
             for (int c = 0; c < 32; ++c) va[c] = vb[c] = (uint32_t)(c + lane);
+            rank(va);
+            rank(vb);
+            rank(va);
           } else {
             tc::ld_32x32_issue(taddr, va);
             tc::ld_wait(va);
             tc::ld_32x32_issue(taddr + 32, vb);
+            rank(va);
+            tc::ld_wait(vb);
+            tc::ld_32x32_issue(taddr + 64, va);
+            rank(vb);
+            tc::ld_wait(va);
+            tc::ld_32x32_issue(taddr + 96, vb);
+            rank(va);
+            tc::ld_wait(vb);
           }
-          rank(va);
-          if (!(dbg & 4)) { tc::ld_wait(vb); tc::ld_32x32_issue(taddr + 64, va); }
-          rank(vb);
-          if (!(dbg & 4)) { tc::ld_wait(va); tc::ld_32x32_issue(taddr + 96, vb); }
-          rank(va);
-          if (!(dbg & 4)) tc::ld_wait(vb);
           tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);   // accumulator rb is in registers

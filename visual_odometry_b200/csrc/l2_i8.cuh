@@ -18,7 +18,7 @@
 // double-buffer each other, work item = (pair, direction, 256-row block)).  Measured
 // (profiles/r2_summary.md): with the whole epilogue removed the MMA + bulk-copy side alone needs
 // 1263 clocks per accumulator (640 of MMA): at 41 KB per 1280 tensor clocks the four smem stages
-// do not cover the L2 latency; 16 epilogue warps with three stages were slower (0.396 vs 0.294 ms).
+// do not cover the L2 latency (see profiles/r2_summary.md for the latency model and the variants).
 #pragma once
 #include "hamming_tc.cuh"
 
@@ -157,6 +157,13 @@ __device__ __forceinline__ void insert(Top& s, int k, int t) {
   else if (s.t2 < 0 || before(k, t, s.k2, s.t2)) { s.k2 = k; s.t2 = t; }
 }
 
+// 16-byte shared-memory load with an explicit state space; volatile without a memory clobber:
+// ordered against the barrier / TMEM asm statements around it, free against the arithmetic
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+  return v;
+}
 __device__ __forceinline__ int imad_i(int a, int b, int c) {
   int d;
   asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
@@ -165,13 +172,16 @@ __device__ __forceinline__ int imad_i(int a, int b, int c) {
 
 // rowbest layout of l2.cu: float4 (d2_1, idx_1 bits, d2_2, idx_2 bits) at
 // [((pair * 2 + dir) * n_splits + split) * row_stride + row]
-template <bool TOP2>
+// VARIANT (compile time: a RUN-time switch around the TMEM loads costs 15-25 % by itself, measured):
+// 0 = TMEM loads pipelined with the ranking, accumulator released after the last load;
+// 1 = the same with explicit ld.shared for the per-column constants;
+// 2 = four loads back to back, release, then ranking (128 live value registers).
+template <bool TOP2, int VARIANT>
 __global__ void __launch_bounds__(THREADS, 1)
 match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
              const int32_t* __restrict__ pairs, int n_cap, int ntile_cap, int ndir, long n_items,
              const float* __restrict__ norms, int norm_stride, int n_splits, int row_stride,
-             const int32_t* __restrict__ flags, float4* __restrict__ rowbest, int dbg) {
-  // dbg (timing experiments, results wrong): bit 0 = no ranking, bit 1 = no TMEM loads either
+             const int32_t* __restrict__ flags, float4* __restrict__ rowbest) {
   if (flags[2] != 0) return;     // not uint8 data: the bf16 kernel of l2.cu runs instead
   extern __shared__ uint8_t smem_raw[];
   Smem& S = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -266,6 +276,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
         const int sc = g % NCC;
         mbar_wait(&S.full_c[sc], (g / NCC) & 1);
         const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][cq * 128]);
+        const uint32_t ccs = smem_u32(&S.cc[sc][cq * 128]);
 #pragma unroll
         for (int rb = 0; rb < 2; ++rb) {
           if (rb >= it.nrb) break;
@@ -276,10 +287,10 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
           uint32_t va[32], vb[32];
           int h = MININT, l = MININT;
           auto rank = [&](uint32_t (&v)[32], int chunk) {
-            if (dbg & 1) return;
 #pragma unroll
             for (int c4 = 0; c4 < 8; ++c4) {
-              const uint4 cc = ccp[chunk * 8 + c4];       // broadcast shared-memory read
+              // broadcast shared-memory read of four column constants
+              const uint4 cc = VARIANT >= 1 ? lds128(ccs + (chunk * 8 + c4) * 16) : ccp[chunk * 8 + c4];
               v[4 * c4 + 0] = (uint32_t)imad_i((int)v[4 * c4 + 0], mul, (int)cc.x);
               v[4 * c4 + 1] = (uint32_t)imad_i((int)v[4 * c4 + 1], mul, (int)cc.y);
               v[4 * c4 + 2] = (uint32_t)imad_i((int)v[4 * c4 + 2], mul, (int)cc.z);
@@ -293,20 +304,37 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
               h = max(h, htc::max32(v));
             }
           };
-          if (dbg & 2) {
-#pragma unroll
-            for (int c = 0; c < 32; ++c) va[c] = vb[c] = (uint32_t)(c + lane);
-          } else {
+          if constexpr (VARIANT == 2) {
+            uint32_t vc[32], vd[32];
             tc::ld_32x32_issue(taddr, va);
-            tc::ld_wait(va);
             tc::ld_32x32_issue(taddr + 32, vb);
+            tc::ld_32x32_issue(taddr + 64, vc);
+            tc::ld_32x32_issue(taddr + 96, vd);
+            tc::ld_wait(va);
+            tc::ld_wait(vb);
+            tc::ld_wait(vc);
+            tc::ld_wait(vd);
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);   // the accumulator is in registers
+            rank(va, 0);
+            rank(vb, 1);
+            rank(vc, 2);
+            rank(vd, 3);
+            fold_tile<TOP2>(st[rb], h, l, t);
+            continue;
           }
+          tc::ld_32x32_issue(taddr, va);
+          tc::ld_wait(va);
+          tc::ld_32x32_issue(taddr + 32, vb);
           rank(va, 0);
-          if (!(dbg & 2)) { tc::ld_wait(vb); tc::ld_32x32_issue(taddr + 64, va); }
+          tc::ld_wait(vb);
+          tc::ld_32x32_issue(taddr + 64, va);
           rank(vb, 1);
-          if (!(dbg & 2)) { tc::ld_wait(va); tc::ld_32x32_issue(taddr + 96, vb); }
+          tc::ld_wait(va);
+          tc::ld_32x32_issue(taddr + 96, vb);
           rank(va, 2);
-          if (!(dbg & 2)) tc::ld_wait(vb);
+          tc::ld_wait(vb);
           tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);
