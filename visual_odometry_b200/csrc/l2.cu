@@ -553,7 +553,10 @@ l2_top2_tc_kernel(const int32_t* __restrict__ nkp, const int32_t* __restrict__ p
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = S.tmem_base;
-  const int dbg = g_l2_debug;
+  // (the round-1 timing switches read g_l2_debug here at run time; branches around the TMEM loads
+  // cost time by themselves, measured on K6i in round 2, so they are compiled out: the measurements
+  // they produced are in profiles/r1_summary.md)
+  constexpr int dbg = 0;
 
   if (warp == L2_EPI_WARPS + 1) {
     // ===== TMA producer: A blocks once per item, one 40 KB bulk copy per B tile =====
