@@ -59,9 +59,19 @@ class PoseGather:
         self._evs = []
 
     def __call__(self, R, t, time_it=False):
+        self.pack(R, t)
+        return self.collect(time_it)
+
+    def pack(self, R, t):
+        """this rank's [R|t] rows -> the all-gather send buffer (current stream)"""
+        L = self._lib
+        L.check(self.lib.vo_pack_poses(L.ptr(R), L.ptr(t), self.n_local, L.ptr(self.send), L.cur_stream()))
+
+    def collect(self, time_it=False):
+        """all-gather of the packed rows + chaining (current stream, which may be a side stream:
+        the collective of batch k can then run beside the matching of batch k + 1)"""
         L = self._lib
         st = L.cur_stream()
-        L.check(self.lib.vo_pack_poses(L.ptr(R), L.ptr(t), self.n_local, L.ptr(self.send), st))
         if self.world > 1:
             if time_it:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
