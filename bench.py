@@ -576,7 +576,11 @@ def run_ours(args, rank, world, local_rank):
     lib.vo_profile_enable(0)
 
     t = torch.tensor([dev_ms, e2e_ms, h2d_alone_ms], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
+        allv = torch.empty(world, 3, dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allv, t)
+        per_rank = allv.cpu().numpy()
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms, h2d_alone_ms = float(t[0]), float(t[1]), float(t[2])
 
@@ -661,6 +665,12 @@ def run_ours(args, rank, world, local_rank):
         "roofline_k2": k2_roofline(pipe, B, k2_ms, peaks.get("hbm_gbs")),
         "wall_s_timed_region": wall,
     }
+    if per_rank is not None:
+        # the headline uses the MAX over ranks; the spread shows what is straggler (one GPU or one
+        # PCIe path slower than the others) and what is the collective
+        out["per_rank"] = {"device_ms_per_step": [round(float(v) / steps, 4) for v in per_rank[:, 0]],
+                           "e2e_ms_per_step": [round(float(v) / steps, 4) for v in per_rank[:, 1]],
+                           "h2d_alone_ms": [round(float(v), 4) for v in per_rank[:, 2]]}
     if strong is not None:
         out["strong_c4"] = strong
     if world == 1 and not args.no_configs:

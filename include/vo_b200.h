@@ -317,6 +317,13 @@ int vo_profile_enable(int on);
 int vo_profile_read(int kernel_id, double* total_ms, int* launches);
 int vo_measure_popc_peak(double* popc32_per_s, void* stream);
 
+/* Page-locked host staging memory for the frame uploads of the host-buffer entry (bench.py e2e;
+ * PairPipeline with VO_B200_PINNED=wc).  write_combined != 0 asks for cudaHostAllocWriteCombined:
+ * the host writes it at full speed but reads it very slowly, and device reads of it are not
+ * snooped — an upload-only buffer.  Free with vo_host_free.  No reference counterpart. */
+int vo_host_alloc(void** ptr, size_t bytes, int write_combined);
+int vo_host_free(void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,6 +61,8 @@ SIGNATURES = {
     "vo_profile_enable": (_i, [_i]),
     "vo_profile_read": (_i, [_i, _p, _p]),
     "vo_measure_popc_peak": (_i, [_p, _p]),
+    "vo_host_alloc": (_i, [_p, _sz, _i]),
+    "vo_host_free": (_i, [_p]),
     "vo_pnp_workspace_bytes": (_sz, [_i, _i]),
     "vo_pnp_ransac": (_i, [_p, _p, _i, _p, _i, _d, _d, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_pnp_batch_workspace_bytes": (_sz, [C.c_long, _i, _i]),

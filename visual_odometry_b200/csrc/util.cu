@@ -126,3 +126,16 @@ extern "C" int vo_measure_popc_peak(double* popc32_per_s, void* stream) {
   *popc32_per_s = (double)grid.x * block.x * (double)iters * 32.0 / (best * 1e-3);
   return vo::check_launch("vo_measure_popc_peak");
 }
+
+extern "C" int vo_host_alloc(void** ptr, size_t bytes, int write_combined) {
+  VO_REQUIRE(ptr && bytes > 0, VO_ERR_INVALID_ARG, "vo_host_alloc: null pointer or zero size");
+  *ptr = nullptr;
+  unsigned flags = cudaHostAllocPortable | (write_combined ? cudaHostAllocWriteCombined : 0u);
+  if (cudaHostAlloc(ptr, bytes, flags) != cudaSuccess) return vo::check_launch("vo_host_alloc");
+  return VO_OK;
+}
+
+extern "C" int vo_host_free(void* ptr) {
+  if (ptr && cudaFreeHost(ptr) != cudaSuccess) return vo::check_launch("vo_host_free");
+  return VO_OK;
+}

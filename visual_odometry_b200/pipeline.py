@@ -8,6 +8,9 @@ followed by the north-star trajectory chaining P_k = [R_k|t_k] P_{k-1} for conse
 All stages are launches of libvo_b200 kernels on one CUDA stream; buffers are allocated once.
 `run_host` is the end-to-end entry (host numpy in, host numpy out, copies inside).
 """
+import ctypes
+import os
+
 import numpy as np
 import torch
 
@@ -15,6 +18,30 @@ from . import _lib
 from . import geometry as G
 
 F64, I32, U8, F32 = torch.float64, torch.int32, torch.uint8, torch.float32
+
+
+class _HostBuffer:
+    """Owner of one vo_host_alloc block; the tensor made from it keeps it alive."""
+
+    def __init__(self, nbytes, write_combined=True):
+        self.lib = _lib.load()
+        p = ctypes.c_void_p()
+        _lib.check(self.lib.vo_host_alloc(ctypes.byref(p), nbytes, int(write_combined)))
+        self.ptr, self.nbytes = p.value, nbytes
+
+    def __del__(self):
+        if getattr(self, "ptr", None):
+            self.lib.vo_host_free(ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+    @staticmethod
+    def tensor(owner, shape, dtype):
+        n = int(np.prod(shape)) * torch.empty(0, dtype=dtype).element_size()
+        hb = _HostBuffer(max(n, 1))
+        raw = (ctypes.c_uint8 * hb.nbytes).from_address(hb.ptr)
+        t = torch.frombuffer(raw, dtype=torch.uint8, count=n).view(dtype).reshape(*shape)
+        owner.__dict__.setdefault("_host_blocks", []).append((hb, raw))
+        return t
 
 
 class PairPipeline:
@@ -167,9 +194,13 @@ class PairPipeline:
     def _pinned(self):
         if self._pin is None:
             pin = lambda *s, dt: torch.empty(*s, dtype=dt, pin_memory=True)
+            up = pin
+            if os.environ.get("VO_B200_PINNED", "") == "wc":
+                # upload-only buffers in write-combined page-locked memory (vo_host_alloc)
+                up = lambda *s, dt: _HostBuffer.tensor(self, s, dt)
             self._pin = dict(
-                desc=pin(self.F, self.n_cap, self.D, dt=self.ddtype),
-                kp=pin(self.F, self.n_cap, 2, dt=F32), nkp=pin(self.F, dt=I32),
+                desc=up(self.F, self.n_cap, self.D, dt=self.ddtype),
+                kp=up(self.F, self.n_cap, 2, dt=F32), nkp=pin(self.F, dt=I32),
                 pairs=pin(self.P, 2, dt=I32),
                 R=pin(self.P, 3, 3, dt=F64), t=pin(self.P, 3, dt=F64),
                 n_inl=pin(self.P, dt=I32), n_match=pin(self.P, dt=I32),
