@@ -304,13 +304,34 @@ int vo_orb_fast_score_map(const uint8_t* images, int n_frames, int width, int he
                           int fast_threshold, int edge_threshold, uint8_t* scores,
                           uint32_t* corners, int32_t* n_corners, int32_t* hist, void* stream);
 
+/* ---- N4: SIFT extraction, replaces `cv2.SIFT_create()` (/root/reference/src/visual_slam.py:17,
+ * src/image_and_keypoints.py:12) + `detectAndCompute(image, None)` (src/frame_generator.py:25,
+ * src/image_and_keypoints.py:46) for a batch of equally sized gray frames, with cv2's default
+ * parameters (nfeatures 0 = all key points, 3 octave layers, contrast 0.04, edge 10, sigma 1.6,
+ * image doubled).  images uint8 [n_frames, height, width] on the device.
+ * kp float32 [n_frames, cap, 6] = (x, y, size, angle, response, octave word — the int cv2 packs
+ * octave / layer / sub-layer into, < 2^24 so exact as float), in cv2's output order
+ * (KeyPoint12_LessThan, duplicates removed); desc uint8 [n_frames, cap, 128] (cv2 returns the same
+ * integers as float32); n_out int32 [n_frames]; status int32 [n_frames] = 1 when more than `cap`
+ * key points were found in a frame (that frame's output is incomplete: call again with a larger
+ * cap).  pyramid_out: NULL, or float32 [n_frames, sum over octaves of 6 * h_o * w_o] receiving the Gaussian
+ * pyramid (6 layers of h_o x w_o per octave, octave after octave) (tests: bit-exact against cv2.GaussianBlur).  vo_sift_octaves writes the octave
+ * sizes to HOST arrays (16 entries) and returns the number of octaves (0 = bad size). */
+int vo_sift_octaves(int width, int height, int32_t* w_h, int32_t* h_h);
+size_t vo_sift_workspace_bytes(int n_frames, int width, int height, int cap);
+int vo_sift_detect_batch(const uint8_t* images, int n_frames, int width, int height, int cap,
+                         float* kp, uint8_t* desc, int32_t* n_out, int32_t* status,
+                         float* pyramid_out, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,
  * and the INT/popc issue-rate ceiling K1 is judged against (MEASURED_PEAKS.json has no integer
  * entry; SURVEY.md section 8d asks for a popc microbenchmark on the box).
  * kernel_id: 0 = the Hamming N1 x N2 pass (K1 popc kernel or K1t tcgen05 kernel), 1 = ransac_score_kernel
  * (K2), 2 = l2 tensor-core GEMM (K6), 3 = ransac_solve_kernel (K3), 4 = K1t operand expansion,
  * 5 = recover_pose_kernel (K5), 6 = triangulate_pairs_kernel (K4), 7 = chain_kernel,
- * 8 = match_compact_kernel, 9 = RANSAC control kernels (init / sample / scan / mask).
+ * 8 = match_compact_kernel, 9 = RANSAC control kernels (init / sample / scan / mask),
+ * 10 = SIFT pyramid (upsample, blurs, halving), 11 = SIFT extrema / orientation / ordering,
+ * 12 = SIFT descriptors.
  * on: 0 = off, 1 = ids 0..4 only (two event records per scope: cheap enough for a timed region),
  * 2 = every scope. */
 int vo_profile_enable(int on);

@@ -1,0 +1,783 @@
+// sift.cu — N4: SIFT feature extraction for a batch of equally sized frames, the
+// detector the reference builds at /root/reference/src/visual_slam.py:17
+// (`cv2.SIFT_create()`) and calls at /root/reference/src/frame_generator.py:25
+// (`detectAndCompute(frame.image, None)`).  The algorithm is OpenCV's (features2d sift.dispatch.cpp
+// / sift.simd.hpp; restated on the CPU in oracle/cv_sift.py, which is pinned against the cv2
+// binary): base image doubled, sigma 1.6, 3 layers per octave, contrast 0.04, edge 10,
+// nfeatures 0 (all key points).
+//
+// Compiled with -fmad=false (Makefile EXTRA_sift): the Gaussian pyramid is BIT-exact against
+// cv2.GaussianBlur on an AVX2/FMA host because the fused and the separately rounded operations
+// are written out with intrinsics exactly where cv2's vector loops and scalar tails have them.
+//
+// Layout in HBM (workspace): per frame one Gaussian pyramid, octave after octave, 6 layers of
+// h_o x w_o floats each; DoG values are differences of two layers computed where they are used
+// (no DoG pyramid is stored).  Key points leave as float32 [F, cap, 6] = (x, y, size, angle,
+// response, octave word) in cv2's order (KeyPoint12_LessThan, duplicates removed) and
+// descriptors as uint8 [F, cap, 128] (cv2 stores the same integers as float32).
+#include <math.h>
+
+#include "common.cuh"
+
+namespace vo {
+namespace sift {
+
+constexpr int NL = 3;                 // nOctaveLayers
+constexpr int LAYERS = NL + 3;        // Gaussian layers per octave
+constexpr int MAX_OCT = 16;
+constexpr int BORDER = 5;             // SIFT_IMG_BORDER
+constexpr int MAX_R = 15;             // largest Gaussian half width (sigma 3.09 -> 13)
+constexpr int ORI_BINS = 36;
+constexpr int CAND_WORDS = 10;
+
+struct Geom {
+  int n_oct;
+  int h[MAX_OCT], w[MAX_OCT];
+  long long off[MAX_OCT];             // float offset of octave o inside one frame's pyramid
+  long long frame_stride;             // floats per frame
+};
+
+struct Kernels {                      // the six Gaussian kernels: [0] base blur, [1..5] layers
+  int r[LAYERS];
+  float f[LAYERS][2 * MAX_R + 1];     // full symmetric kernel, 2 r + 1 taps
+};
+
+static int make_geom(int width, int height, Geom* g) {
+  // nOctaves = cvRound(log(min(cols, rows)) / log(2) - 2) - firstOctave, firstOctave = -1
+  const double v = log((double)(width < height ? width : height)) / log(2.0) - 2.0;
+  const int n_oct = (int)nearbyint(v) + 1;
+  if (n_oct < 1 || n_oct > MAX_OCT) return -1;
+  g->n_oct = n_oct;
+  long long off = 0;
+  int h = 2 * height, w = 2 * width;
+  for (int o = 0; o < n_oct; ++o) {
+    if (h < 1 || w < 1) return -1;
+    g->h[o] = h; g->w[o] = w; g->off[o] = off;
+    off += (long long)LAYERS * h * w;
+    h /= 2; w /= 2;
+  }
+  g->frame_stride = off;
+  return 0;
+}
+
+// getGaussianKernel(ksize = cvRound(sigma * 8 + 1) | 1, sigma, CV_32F): double arithmetic,
+// normalised, stored as float
+static int make_kernel(double sigma, int* r_out, float* f) {
+  int ksize = (int)nearbyint(sigma * 8.0 + 1.0) | 1;
+  const int r = ksize / 2;
+  if (r > MAX_R) return -1;
+  double k[2 * MAX_R + 1], sum = 0.0;
+  for (int i = 0; i < ksize; ++i) {
+    const double x = (double)(i - r);
+    k[i] = exp(-(x * x) / (2.0 * sigma * sigma));
+    sum += k[i];
+  }
+  for (int i = 0; i < ksize; ++i) f[i] = (float)(k[i] / sum);
+  *r_out = r;
+  return 0;
+}
+
+static int make_kernels(Kernels* K) {
+  const float sigma = 1.6f, init = 0.5f;
+  float d = sigma * sigma - init * init * 4.f;
+  const float sig_diff = sqrtf(d > 0.01f ? d : 0.01f);
+  if (make_kernel((double)sig_diff, &K->r[0], K->f[0])) return -1;
+  const double kk = pow(2.0, 1.0 / NL);
+  for (int i = 1; i < LAYERS; ++i) {
+    const double prev = pow(kk, (double)(i - 1)) * 1.6;   // SIFT_Impl::sigma is a double here
+    const double total = prev * kk;
+    if (make_kernel(sqrt(total * total - prev * prev), &K->r[i], K->f[i])) return -1;
+  }
+  return 0;
+}
+
+__device__ __forceinline__ int reflect101(int i, int n) {
+  if (n == 1) return 0;
+  const int period = 2 * (n - 1);
+  i %= period;
+  if (i < 0) i += period;
+  return i >= n ? period - i : i;
+}
+
+// ------------------------------------------------------------------ S1: uint8 -> float, 2x linear
+// resize(INTER_LINEAR) by exactly 2: taps (d + 0.5) / 2 - 0.5, weights 0.25 / 0.75, clamped; all
+// products and sums are exact in float, so the order does not matter.
+__global__ void upsample_kernel(const uint8_t* __restrict__ img, int h, int w, float* __restrict__ out,
+                                long long out_stride) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  const int f = blockIdx.z;
+  if (x >= 2 * w) return;
+  const uint8_t* src = img + (size_t)f * h * w;
+  auto taps = [](int d, int n, int& i0, int& i1, float& a) {
+    const float fx = (d + 0.5f) * 0.5f - 0.5f;
+    i0 = (int)floorf(fx);
+    a = fx - i0;
+    if (i0 < 0) { i0 = 0; a = 0.f; }
+    if (i0 >= n - 1) { i1 = n - 1; i0 = i0 < n - 1 ? i0 : n - 1; a = 0.f; } else { i1 = i0 + 1; }
+  };
+  int x0, x1, y0, y1; float ax, ay;
+  taps(x, w, x0, x1, ax);
+  taps(y, h, y0, y1, ay);
+  const float r0 = src[(size_t)y0 * w + x0] * (1.f - ax) + src[(size_t)y0 * w + x1] * ax;
+  const float r1 = src[(size_t)y1 * w + x0] * (1.f - ax) + src[(size_t)y1 * w + x1] * ax;
+  out[(size_t)f * out_stride + (size_t)y * 2 * w + x] = r0 * (1.f - ay) + r1 * ay;
+}
+
+// ------------------------------------------------------------------ S2: separable Gaussian blur
+// One block = a 64 x 32 output tile: the row pass of the tile's rows plus r halo rows goes to
+// shared memory, the column pass reads it.  Operation order = cv2's (see oracle/cv_sift.py blur):
+// rows: k = 0 .. 2r, fused multiply-add, except the last w % 4 columns (multiply, then add);
+// columns: f0 * x, then fma(x[-k] + x[+k], f[k], acc), except the last w % 8 columns.
+constexpr int TW = 64, TH = 32;
+__global__ void __launch_bounds__(256)
+blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w, long long stride,
+            Kernels K, int ki) {
+  __shared__ float rowp[TH + 2 * MAX_R][TW];
+  __shared__ float fk[2 * MAX_R + 1];
+  const int r = K.r[ki];
+  const int tid = threadIdx.x;
+  if (tid <= 2 * r) fk[tid] = K.f[ki][tid];
+  __syncthreads();
+  const float* s = src + (size_t)blockIdx.z * stride;
+  float* d = dst + (size_t)blockIdx.z * stride;
+  const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+  const int row_tail = (w / 4) * 4, col_tail = (w / 8) * 8;
+  const int rows = TH + 2 * r;
+  for (int i = tid; i < rows * TW; i += 256) {
+    const int ry = i / TW, cx = i % TW;
+    const int x = x0 + cx;
+    if (x >= w) continue;
+    const int y = reflect101(y0 - r + ry, h);
+    const float* line = s + (size_t)y * w;
+    float acc;
+    if (x - r >= 0 && x + r < w) {
+      const float* p = line + x - r;
+      acc = __fmul_rn(p[0], fk[0]);
+      if (x < row_tail) {
+        for (int k = 1; k <= 2 * r; ++k) acc = __fmaf_rn(p[k], fk[k], acc);
+      } else {
+        for (int k = 1; k <= 2 * r; ++k) acc = __fadd_rn(__fmul_rn(p[k], fk[k]), acc);
+      }
+    } else {
+      acc = __fmul_rn(line[reflect101(x - r, w)], fk[0]);
+      if (x < row_tail) {
+        for (int k = 1; k <= 2 * r; ++k) acc = __fmaf_rn(line[reflect101(x - r + k, w)], fk[k], acc);
+      } else {
+        for (int k = 1; k <= 2 * r; ++k)
+          acc = __fadd_rn(__fmul_rn(line[reflect101(x - r + k, w)], fk[k]), acc);
+      }
+    }
+    rowp[ry][cx] = acc;
+  }
+  __syncthreads();
+  for (int i = tid; i < TH * TW; i += 256) {
+    const int ty = i / TW, cx = i % TW;
+    const int x = x0 + cx, y = y0 + ty;
+    if (x >= w || y >= h) continue;
+    float acc = __fmul_rn(fk[r], rowp[ty + r][cx]);
+    if (x < col_tail) {
+      for (int k = 1; k <= r; ++k)
+        acc = __fmaf_rn(__fadd_rn(rowp[ty + r - k][cx], rowp[ty + r + k][cx]), fk[r + k], acc);
+    } else {
+      for (int k = 1; k <= r; ++k)
+        acc = __fadd_rn(__fmul_rn(__fadd_rn(rowp[ty + r - k][cx], rowp[ty + r + k][cx]), fk[r + k]), acc);
+    }
+    d[(size_t)y * w + x] = acc;
+  }
+}
+
+// ------------------------------------------------------------------ S3: next octave's first layer
+// resize(INTER_NEAREST) to (w / 2, h / 2): sx = min(floor(x * (w / (w / 2))), w - 1) in double
+__global__ void halve_kernel(const float* __restrict__ src, int h, int w, float* __restrict__ dst,
+                             int dh, int dw, long long stride) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= dw) return;
+  const double fx = (double)w / dw, fy = (double)h / dh;
+  int sx = (int)floor(x * fx), sy = (int)floor(y * fy);
+  sx = sx < w - 1 ? sx : w - 1;
+  sy = sy < h - 1 ? sy : h - 1;
+  dst[(size_t)blockIdx.z * stride + (size_t)y * dw + x] =
+      src[(size_t)blockIdx.z * stride + (size_t)sy * w + sx];
+}
+
+// ------------------------------------------------------------------ S4: extrema + refinement
+// DoG layer l (0 .. 4) of an octave = Gaussian layer l + 1 minus layer l, computed on the fly.
+struct Octave {
+  const float* g;       // Gaussian layer 0 of this octave for this frame
+  int h, w;
+  __device__ __forceinline__ float gauss(int layer, int r, int c) const {
+    return g[(size_t)layer * h * w + (size_t)r * w + c];
+  }
+  __device__ __forceinline__ float dog(int layer, int r, int c) const {
+    const size_t ls = (size_t)h * w, p = (size_t)r * w + c;
+    return __fsub_rn(g[(layer + 1) * ls + p], g[layer * ls + p]);
+  }
+};
+
+struct Cand {           // refined extremum, CAND_WORDS 32-bit words in the candidate list
+  int o, layer, r, c;
+  float x, y, size, response;
+  int octave_word;
+};
+
+// Matx33f::solve(DECOMP_LU) = Cramer's rule in float; singular -> 0
+__device__ __forceinline__ void solve3(const float a[3][3], const float b[3], float x[3]) {
+  float d = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) -
+            a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) +
+            a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+  if (d == 0.f) { x[0] = x[1] = x[2] = 0.f; return; }
+  d = 1.f / d;
+  x[0] = d * (b[0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) -
+              a[0][1] * (b[1] * a[2][2] - a[1][2] * b[2]) +
+              a[0][2] * (b[1] * a[2][1] - a[1][1] * b[2]));
+  x[1] = d * (a[0][0] * (b[1] * a[2][2] - a[1][2] * b[2]) -
+              b[0] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) +
+              a[0][2] * (a[1][0] * b[2] - b[1] * a[2][0]));
+  x[2] = d * (a[0][0] * (a[1][1] * b[2] - b[1] * a[2][1]) -
+              a[0][1] * (a[1][0] * b[2] - b[1] * a[2][0]) +
+              b[0] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]));
+}
+
+// adjustLocalExtrema; `layer` is the DoG layer (1 .. 3)
+__device__ bool adjust_local_extrema(const Octave& O, int octv, int layer, int r, int c, Cand* out) {
+  const float img_scale = 1.f / 255.f;
+  const float deriv_scale = img_scale * 0.5f;
+  const float second_deriv_scale = img_scale;
+  const float cross_deriv_scale = img_scale * 0.25f;
+  float xi = 0.f, xr = 0.f, xc = 0.f;
+  int i = 0;
+  for (; i < 5; ++i) {
+    const float dD[3] = {(O.dog(layer, r, c + 1) - O.dog(layer, r, c - 1)) * deriv_scale,
+                         (O.dog(layer, r + 1, c) - O.dog(layer, r - 1, c)) * deriv_scale,
+                         (O.dog(layer + 1, r, c) - O.dog(layer - 1, r, c)) * deriv_scale};
+    const float v2 = O.dog(layer, r, c) * 2.f;
+    const float dxx = (O.dog(layer, r, c + 1) + O.dog(layer, r, c - 1) - v2) * second_deriv_scale;
+    const float dyy = (O.dog(layer, r + 1, c) + O.dog(layer, r - 1, c) - v2) * second_deriv_scale;
+    const float dss = (O.dog(layer + 1, r, c) + O.dog(layer - 1, r, c) - v2) * second_deriv_scale;
+    const float dxy = (O.dog(layer, r + 1, c + 1) - O.dog(layer, r + 1, c - 1) -
+                       O.dog(layer, r - 1, c + 1) + O.dog(layer, r - 1, c - 1)) * cross_deriv_scale;
+    const float dxs = (O.dog(layer + 1, r, c + 1) - O.dog(layer + 1, r, c - 1) -
+                       O.dog(layer - 1, r, c + 1) + O.dog(layer - 1, r, c - 1)) * cross_deriv_scale;
+    const float dys = (O.dog(layer + 1, r + 1, c) - O.dog(layer + 1, r - 1, c) -
+                       O.dog(layer - 1, r + 1, c) + O.dog(layer - 1, r - 1, c)) * cross_deriv_scale;
+    const float H[3][3] = {{dxx, dxy, dxs}, {dxy, dyy, dys}, {dxs, dys, dss}};
+    float X[3];
+    solve3(H, dD, X);
+    xi = -X[2]; xr = -X[1]; xc = -X[0];
+    if (fabsf(xi) < 0.5f && fabsf(xr) < 0.5f && fabsf(xc) < 0.5f) break;
+    const float big = (float)(2147483647 / 3);
+    if (fabsf(xi) > big || fabsf(xr) > big || fabsf(xc) > big) return false;
+    c += __float2int_rn(xc);
+    r += __float2int_rn(xr);
+    layer += __float2int_rn(xi);
+    if (layer < 1 || layer > NL || c < BORDER || c >= O.w - BORDER || r < BORDER || r >= O.h - BORDER)
+      return false;
+  }
+  if (i >= 5) return false;
+  const float dD[3] = {(O.dog(layer, r, c + 1) - O.dog(layer, r, c - 1)) * deriv_scale,
+                       (O.dog(layer, r + 1, c) - O.dog(layer, r - 1, c)) * deriv_scale,
+                       (O.dog(layer + 1, r, c) - O.dog(layer - 1, r, c)) * deriv_scale};
+  const float t = dD[0] * xc + dD[1] * xr + dD[2] * xi;
+  const float contr = O.dog(layer, r, c) * img_scale + t * 0.5f;
+  if (fabsf(contr) * NL < 0.04f) return false;
+  const float v2 = O.dog(layer, r, c) * 2.f;
+  const float dxx = (O.dog(layer, r, c + 1) + O.dog(layer, r, c - 1) - v2) * second_deriv_scale;
+  const float dyy = (O.dog(layer, r + 1, c) + O.dog(layer, r - 1, c) - v2) * second_deriv_scale;
+  const float dxy = (O.dog(layer, r + 1, c + 1) - O.dog(layer, r + 1, c - 1) -
+                     O.dog(layer, r - 1, c + 1) + O.dog(layer, r - 1, c - 1)) * cross_deriv_scale;
+  const float tr = dxx + dyy, det = dxx * dyy - dxy * dxy;
+  const float e = 10.f;
+  if (det <= 0.f || tr * tr * e >= (e + 1.f) * (e + 1.f) * det) return false;
+  out->o = octv; out->layer = layer; out->r = r; out->c = c;
+  out->x = (c + xc) * (float)(1 << octv);
+  out->y = (r + xr) * (float)(1 << octv);
+  out->octave_word = octv + (layer << 8) + ((int)nearbyint(((double)xi + 0.5) * 255.0) << 16);
+  out->size = 1.6f * powf(2.f, (layer + xi) / NL) * (float)(1 << octv) * 2.f;
+  out->response = fabsf(contr);
+  return true;
+}
+
+// one thread per pixel of one octave; all three DoG layers
+__global__ void __launch_bounds__(256)
+extrema_kernel(const float* __restrict__ pyr, Geom G, int octv, int cap, int32_t* __restrict__ n_cand,
+               int32_t* __restrict__ cand, int32_t* __restrict__ status) {
+  const int f = blockIdx.z;
+  Octave O{pyr + (size_t)f * G.frame_stride + G.off[octv], G.h[octv], G.w[octv]};
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int r = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (c < BORDER || c >= O.w - BORDER || r < BORDER || r >= O.h - BORDER) return;
+  for (int layer = 1; layer <= NL; ++layer) {
+    const float val = O.dog(layer, r, c);
+    if (!(fabsf(val) > 1.f)) continue;      // threshold = floor(0.5 * 0.04 / 3 * 255) = 1
+    bool ext = true;
+    if (val > 0.f) {
+      for (int l = layer - 1; l <= layer + 1 && ext; ++l)
+        for (int dy = -1; dy <= 1 && ext; ++dy)
+          for (int dx = -1; dx <= 1; ++dx)
+            if (val < O.dog(l, r + dy, c + dx)) { ext = false; break; }
+    } else {
+      for (int l = layer - 1; l <= layer + 1 && ext; ++l)
+        for (int dy = -1; dy <= 1 && ext; ++dy)
+          for (int dx = -1; dx <= 1; ++dx)
+            if (val > O.dog(l, r + dy, c + dx)) { ext = false; break; }
+    }
+    if (!ext) continue;
+    Cand k;
+    if (!adjust_local_extrema(O, octv, layer, r, c, &k)) continue;
+    const int slot = atomicAdd(&n_cand[f], 1);
+    if (slot >= cap) { status[f] = 1; continue; }
+    int32_t* w = cand + ((size_t)f * cap + slot) * CAND_WORDS;
+    w[0] = k.o; w[1] = k.layer; w[2] = k.r; w[3] = k.c;
+    w[4] = __float_as_int(k.x); w[5] = __float_as_int(k.y); w[6] = __float_as_int(k.size);
+    w[7] = __float_as_int(k.response); w[8] = k.octave_word;
+  }
+}
+
+// ------------------------------------------------------------------ hal::fastAtan2 (degrees)
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  const float k = (float)(180.0 / 3.14159265358979323846);
+  const float p1 = 0.9997878412794807f * k, p3 = -0.3258083974640975f * k;
+  const float p5 = 0.1555786518463281f * k, p7 = -0.04432655554792128f * k;
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float eps = (float)2.2204460492503131e-16;
+  float a, c, c2;
+  if (ax >= ay) {
+    c = ay / (ax + eps);
+    c2 = c * c;
+    a = (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+  } else {
+    c = ax / (ay + eps);
+    c2 = c * c;
+    a = 90.f - (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+  }
+  if (x < 0.f) a = 180.f - a;
+  if (y < 0.f) a = 360.f - a;
+  return a;
+}
+
+// ------------------------------------------------------------------ S5: orientations
+// One block of 64 threads per refined extremum: the window's samples (bin, weight * magnitude) go
+// to shared memory in row-major order, then thread b sums bin b IN THAT ORDER (cv2's scalar
+// accumulation), so the histogram does not depend on scheduling.
+constexpr int ORI_MAX_RADIUS = 24;
+constexpr int ORI_MAX_SAMPLES = (2 * ORI_MAX_RADIUS + 1) * (2 * ORI_MAX_RADIUS + 1);
+constexpr int KP_WORDS = 6;
+__global__ void __launch_bounds__(64)
+orient_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* __restrict__ n_cand,
+              const int32_t* __restrict__ cand, int32_t* __restrict__ n_raw, float* __restrict__ raw,
+              int32_t* __restrict__ status) {
+  const int f = blockIdx.y;
+  const int n_c = n_cand[f] < cap ? n_cand[f] : cap;
+  __shared__ float contrib[ORI_MAX_SAMPLES];
+  __shared__ uint8_t bins[ORI_MAX_SAMPLES];
+  __shared__ float temp[ORI_BINS + 4], hist[ORI_BINS];
+  for (int ci = blockIdx.x; ci < n_c; ci += gridDim.x) {
+    const int32_t* w = cand + ((size_t)f * cap + ci) * CAND_WORDS;
+    const int octv = w[0], layer = w[1], pr = w[2], pc = w[3];
+    const float size = __int_as_float(w[6]);
+    const float* img = pyr + (size_t)f * G.frame_stride + G.off[octv] +
+                       (size_t)layer * G.h[octv] * G.w[octv];
+    const int h = G.h[octv], wd = G.w[octv];
+    const float scl_octv = size * 0.5f / (float)(1 << octv);
+    int radius = __float2int_rn(4.5f * scl_octv);       // SIFT_ORI_RADIUS = 3 * 1.5
+    if (radius > ORI_MAX_RADIUS) radius = ORI_MAX_RADIUS;   // unreachable: scl_octv < 4.1
+    const float sigma = 1.5f * scl_octv;
+    const float expf_scale = -1.f / (2.f * sigma * sigma);
+    const int side = 2 * radius + 1, len = side * side;
+    for (int k = threadIdx.x; k < len; k += 64) {
+      const int i = k / side - radius, j = k % side - radius;
+      const int y = pr + i, x = pc + j;
+      uint8_t b = 255;
+      float v = 0.f;
+      if (y > 0 && y < h - 1 && x > 0 && x < wd - 1) {
+        const float dx = img[(size_t)y * wd + x + 1] - img[(size_t)y * wd + x - 1];
+        const float dy = img[(size_t)(y - 1) * wd + x] - img[(size_t)(y + 1) * wd + x];
+        const float wgt = expf((float)(i * i + j * j) * expf_scale);
+        const float ori = fast_atan2_deg(dy, dx);
+        const float mag = sqrtf(dx * dx + dy * dy);
+        int bin = __float2int_rn((ORI_BINS / 360.f) * ori);
+        if (bin >= ORI_BINS) bin -= ORI_BINS;
+        if (bin < 0) bin += ORI_BINS;
+        b = (uint8_t)bin;
+        v = wgt * mag;
+      }
+      bins[k] = b;
+      contrib[k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < ORI_BINS) {
+      float s = 0.f;
+      const uint8_t me = (uint8_t)threadIdx.x;
+      for (int k = 0; k < len; ++k)
+        if (bins[k] == me) s += contrib[k];
+      temp[threadIdx.x + 2] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      temp[0] = temp[ORI_BINS];
+      temp[1] = temp[ORI_BINS + 1];
+      temp[ORI_BINS + 2] = temp[2];
+      temp[ORI_BINS + 3] = temp[3];
+    }
+    __syncthreads();
+    if (threadIdx.x < ORI_BINS) {
+      const float* t = temp + threadIdx.x + 2;
+      hist[threadIdx.x] = (t[-2] + t[2]) * (1.f / 16.f) + (t[-1] + t[1]) * (4.f / 16.f) + t[0] * (6.f / 16.f);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float omax = hist[0];
+      for (int b = 1; b < ORI_BINS; ++b) omax = fmaxf(omax, hist[b]);
+      const float mag_thr = omax * 0.8f;
+      for (int j = 0; j < ORI_BINS; ++j) {
+        const int l = j > 0 ? j - 1 : ORI_BINS - 1, r2 = j < ORI_BINS - 1 ? j + 1 : 0;
+        if (hist[j] > hist[l] && hist[j] > hist[r2] && hist[j] >= mag_thr) {
+          float bin = j + 0.5f * (hist[l] - hist[r2]) / (hist[l] - 2.f * hist[j] + hist[r2]);
+          bin = bin < 0.f ? ORI_BINS + bin : (bin >= ORI_BINS ? bin - ORI_BINS : bin);
+          float angle = 360.f - (360.f / ORI_BINS) * bin;
+          if (fabsf(angle - 360.f) < 1.1920929e-07f) angle = 0.f;
+          const int slot = atomicAdd(&n_raw[f], 1);
+          if (slot >= cap) { status[f] = 1; continue; }
+          float* o = raw + ((size_t)f * cap + slot) * KP_WORDS;
+          o[0] = __int_as_float(w[4]); o[1] = __int_as_float(w[5]); o[2] = size; o[3] = angle;
+          o[4] = __int_as_float(w[7]); o[5] = __int_as_float(w[8]);     // octave word as raw bits
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ S6: cv2's output order
+// KeyPoint12_LessThan: x, y ascending; size descending; angle ascending; response, octave
+// descending.  rank = number of key points that sort before this one (index breaks full ties).
+__device__ __forceinline__ bool kp_less(const float* a, int ia, const float* b, int ib) {
+  if (a[0] != b[0]) return a[0] < b[0];
+  if (a[1] != b[1]) return a[1] < b[1];
+  if (a[2] != b[2]) return a[2] > b[2];
+  if (a[3] != b[3]) return a[3] < b[3];
+  if (a[4] != b[4]) return a[4] > b[4];
+  const int oa = __float_as_int(a[5]), ob = __float_as_int(b[5]);
+  if (oa != ob) return oa > ob;
+  return ia < ib;
+}
+
+__global__ void __launch_bounds__(256)
+rank_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restrict__ raw,
+            float* __restrict__ sorted) {
+  const int f = blockIdx.y;
+  const int n = n_raw[f] < cap ? n_raw[f] : cap;
+  __shared__ float tile[256][KP_WORDS];
+  const float* base = raw + (size_t)f * cap * KP_WORDS;
+  for (int i0 = blockIdx.x * 256; i0 < n; i0 += gridDim.x * 256) {
+    const int i = i0 + threadIdx.x;
+    float me[KP_WORDS];
+    if (i < n)
+      for (int q = 0; q < KP_WORDS; ++q) me[q] = base[(size_t)i * KP_WORDS + q];
+    int rank = 0;
+    for (int j0 = 0; j0 < n; j0 += 256) {
+      __syncthreads();
+      if (j0 + threadIdx.x < n)
+        for (int q = 0; q < KP_WORDS; ++q) tile[threadIdx.x][q] = base[(size_t)(j0 + threadIdx.x) * KP_WORDS + q];
+      __syncthreads();
+      if (i < n) {
+        const int m = n - j0 < 256 ? n - j0 : 256;
+        for (int j = 0; j < m; ++j) rank += kp_less(tile[j], j0 + j, me, i) ? 1 : 0;
+      }
+    }
+    if (i < n) {
+      float* o = sorted + ((size_t)f * cap + rank) * KP_WORDS;
+      for (int q = 0; q < KP_WORDS; ++q) o[q] = me[q];
+    }
+    __syncthreads();
+  }
+}
+
+// removeDuplicatedSorted (equal x, y, size, angle as the predecessor), then the firstOctave = -1
+// correction: octave byte - 1, point and size halved.  One block per frame.
+__global__ void __launch_bounds__(256)
+finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restrict__ sorted,
+                float* __restrict__ kp, int32_t* __restrict__ n_out) {
+  const int f = blockIdx.x;
+  const int n = n_raw[f] < cap ? n_raw[f] : cap;
+  const float* s = sorted + (size_t)f * cap * KP_WORDS;
+  __shared__ int warp_sums[8];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < n; i0 += 256) {
+    const int i = i0 + threadIdx.x;
+    int keep = 0;
+    if (i < n) {
+      keep = 1;
+      if (i > 0) {
+        const float* a = s + (size_t)(i - 1) * KP_WORDS;
+        const float* b = s + (size_t)i * KP_WORDS;
+        if (a[0] == b[0] && a[1] == b[1] && a[2] == b[2] && a[3] == b[3]) keep = 0;
+      }
+    }
+    const unsigned ball = __ballot_sync(0xffffffffu, keep);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) warp_sums[wid] = __popc(ball);
+    __syncthreads();
+    int before = carry;
+    for (int q = 0; q < wid; ++q) before += warp_sums[q];
+    const int pos = before + __popc(ball & ((1u << lane) - 1u));
+    if (keep) {
+      const float* b = s + (size_t)i * KP_WORDS;
+      float* o = kp + ((size_t)f * cap + pos) * KP_WORDS;
+      int octw = __float_as_int(b[5]);
+      octw = (octw & ~255) | ((octw - 1) & 255);
+      o[0] = b[0] * 0.5f; o[1] = b[1] * 0.5f; o[2] = b[2] * 0.5f; o[3] = b[3]; o[4] = b[4];
+      o[5] = (float)octw;                      // < 2^24: exact
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int q = 0; q < 8; ++q) t += warp_sums[q];
+      carry += t;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) n_out[f] = carry;
+}
+
+// ------------------------------------------------------------------ S7: descriptors
+// One block of 128 threads per key point; thread t owns output bin t = (row i, column j,
+// orientation k) of the 4 x 4 x 8 histogram.  The window is walked in row-major order in pieces
+// of DESC_CHUNK samples: all threads compute the samples of a piece (bin coordinates and the
+// eight trilinear shares, cv2's operation order) into shared memory, then every thread adds the
+// shares that land in ITS bin in sample order — the float sums are those of cv2's scalar loop,
+// independent of scheduling, and no atomics are needed.
+constexpr int DESC_CHUNK = 1024;
+__global__ void __launch_bounds__(128)
+describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* __restrict__ n_kp,
+                const float* __restrict__ kp, uint8_t* __restrict__ desc) {
+  const int f = blockIdx.y;
+  const int n = n_kp[f];
+  __shared__ float share[8][DESC_CHUNK];
+  __shared__ uint16_t where[DESC_CHUNK];       // (r0 + 1) | (c0 + 1) << 4 | o0 << 8; 0xffff = none
+  __shared__ float rawd[128];
+  __shared__ float s_scale;
+  const int t = threadIdx.x;
+  const unsigned ti = (t >> 5) + 1, tj = ((t >> 3) & 3) + 1, tk = t & 7;
+  constexpr int d = 4, nb = 8;
+  for (int idx = blockIdx.x; idx < n; idx += gridDim.x) {
+    const float* k = kp + ((size_t)f * cap + idx) * KP_WORDS;
+    // calcDescriptors: unpackOctave and back to the octave's own pixel grid
+    const int octw = (int)k[5];
+    int octave = octw & 255;
+    const int layer = (octw >> 8) & 255;
+    octave = octave < 128 ? octave : (-128 | octave);
+    const float scale = octave >= 0 ? 1.f / (float)(1 << octave) : (float)(1 << -octave);
+    const int o = octave + 1;                                 // firstOctave = -1
+    const float* img = pyr + (size_t)f * G.frame_stride + G.off[o] + (size_t)layer * G.h[o] * G.w[o];
+    const int rows = G.h[o], cols = G.w[o];
+    const float ptx = k[0] * scale, pty = k[1] * scale;
+    float ori = 360.f - k[3];
+    if (fabsf(ori - 360.f) < 1.1920929e-07f) ori = 0.f;
+    const float scl = k[2] * scale * 0.5f;
+    const int px = __float2int_rn(ptx), py = __float2int_rn(pty);
+    float cos_t = cosf(ori * (float)(3.14159265358979323846 / 180.0));
+    float sin_t = sinf(ori * (float)(3.14159265358979323846 / 180.0));
+    const float bins_per_rad = nb / 360.f;
+    const float exp_scale = -1.f / (d * d * 0.5f);
+    const float hist_width = 3.f * scl;
+    int radius = __float2int_rn(hist_width * 1.4142135623730951f * (d + 1) * 0.5f);
+    const int diag = (int)sqrt((double)cols * cols + (double)rows * rows);
+    radius = radius < diag ? radius : diag;
+    cos_t /= hist_width;
+    sin_t /= hist_width;
+    const int side = 2 * radius + 1;
+    const long len = (long)side * side;
+    float acc = 0.f, acc_wrap = 0.f;          // bin (i, j, k) and, for k == 0, bin (i, j, 8)
+    for (long base = 0; base < len; base += DESC_CHUNK) {
+      __syncthreads();
+      for (int q = t; q < DESC_CHUNK; q += 128) {
+        uint16_t wv = 0xffff;
+        const long s = base + q;
+        if (s < len) {
+          const int i = (int)(s / side) - radius, j = (int)(s % side) - radius;
+          const float c_rot = j * cos_t - i * sin_t;
+          const float r_rot = j * sin_t + i * cos_t;
+          float rbin = r_rot + d / 2 - 0.5f;
+          float cbin = c_rot + d / 2 - 0.5f;
+          const int r = py + i, c = px + j;
+          if (rbin > -1.f && rbin < d && cbin > -1.f && cbin < d && r > 0 && r < rows - 1 && c > 0 &&
+              c < cols - 1) {
+            const float dx = img[(size_t)r * cols + c + 1] - img[(size_t)r * cols + c - 1];
+            const float dy = img[(size_t)(r - 1) * cols + c] - img[(size_t)(r + 1) * cols + c];
+            const float wgt = expf((c_rot * c_rot + r_rot * r_rot) * exp_scale);
+            const float og = fast_atan2_deg(dy, dx);
+            const float mag = sqrtf(dx * dx + dy * dy) * wgt;
+            float obin = (og - ori) * bins_per_rad;
+            const int r0 = (int)floorf(rbin), c0 = (int)floorf(cbin);
+            int o0 = (int)floorf(obin);
+            rbin -= r0; cbin -= c0; obin -= o0;
+            if (o0 < 0) o0 += nb;
+            if (o0 >= nb) o0 -= nb;
+            const float v_r1 = mag * rbin, v_r0 = mag - v_r1;
+            const float v_rc11 = v_r1 * cbin, v_rc10 = v_r1 - v_rc11;
+            const float v_rc01 = v_r0 * cbin, v_rc00 = v_r0 - v_rc01;
+            const float v111 = v_rc11 * obin, v110 = v_rc11 - v111;
+            const float v101 = v_rc10 * obin, v100 = v_rc10 - v101;
+            const float v011 = v_rc01 * obin, v010 = v_rc01 - v011;
+            const float v001 = v_rc00 * obin, v000 = v_rc00 - v001;
+            share[0][q] = v000; share[1][q] = v001; share[2][q] = v010; share[3][q] = v011;
+            share[4][q] = v100; share[5][q] = v101; share[6][q] = v110; share[7][q] = v111;
+            wv = (uint16_t)((r0 + 1) | ((c0 + 1) << 4) | (o0 << 8));
+          }
+        }
+        where[q] = wv;
+      }
+      __syncthreads();
+      const int m = len - base < DESC_CHUNK ? (int)(len - base) : DESC_CHUNK;
+      for (int q = 0; q < m; ++q) {
+        const unsigned wv = where[q];
+        const unsigned a = ti - (wv & 15u), b = tj - ((wv >> 4) & 15u);
+        if ((a | b) > 1u) continue;
+        const unsigned oo = wv >> 8;
+        const unsigned e = tk - oo;
+        if (e <= 1u) acc += share[a * 4 + b * 2 + e][q];
+        if (tk == 0 && oo == nb - 1) acc_wrap += share[a * 4 + b * 2 + 1][q];
+      }
+    }
+    // circular orientation bins: hist[0] += hist[n] (hist[n + 1] never receives anything)
+    rawd[t] = tk == 0 ? acc + acc_wrap : acc;
+    __syncthreads();
+    if (t == 0) {
+      float nrm2 = 0.f;
+      for (int q = 0; q < 128; ++q) nrm2 += rawd[q] * rawd[q];
+      const float thr = sqrtf(nrm2) * 0.2f;
+      nrm2 = 0.f;
+      for (int q = 0; q < 128; ++q) {
+        const float v = fminf(rawd[q], thr);
+        rawd[q] = v;
+        nrm2 += v * v;
+      }
+      s_scale = 512.f / fmaxf(sqrtf(nrm2), 1.1920929e-07f);
+    }
+    __syncthreads();
+    const int v = __float2int_rn(rawd[t] * s_scale);
+    desc[((size_t)f * cap + idx) * 128 + t] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ workspace
+struct Ws {
+  float* pyr;        // [F] Gaussian pyramids
+  int32_t* n_cand;   // [F]
+  int32_t* n_raw;    // [F]
+  int32_t* cand;     // [F, cap, CAND_WORDS]
+  float* raw;        // [F, cap, KP_WORDS]
+  float* sorted;     // [F, cap, KP_WORDS]
+  size_t bytes;
+};
+
+static Ws carve(void* base, const Geom& G, int n_frames, int cap) {
+  Ws w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? (char*)base + off : nullptr;
+    off += (bytes + 255) / 256 * 256;
+    return p;
+  };
+  w.pyr = (float*)take((size_t)n_frames * G.frame_stride * 4);
+  w.n_cand = (int32_t*)take((size_t)n_frames * 4);
+  w.n_raw = (int32_t*)take((size_t)n_frames * 4);
+  w.cand = (int32_t*)take((size_t)n_frames * cap * CAND_WORDS * 4);
+  w.raw = (float*)take((size_t)n_frames * cap * KP_WORDS * 4);
+  w.sorted = (float*)take((size_t)n_frames * cap * KP_WORDS * 4);
+  w.bytes = off;
+  return w;
+}
+
+}  // namespace sift
+}  // namespace vo
+
+using namespace vo::sift;
+
+extern "C" int vo_sift_octaves(int width, int height, int32_t* w_h, int32_t* h_h) {
+  Geom G;
+  if (make_geom(width, height, &G)) return 0;
+  for (int o = 0; o < G.n_oct; ++o) {
+    if (w_h) w_h[o] = G.w[o];
+    if (h_h) h_h[o] = G.h[o];
+  }
+  return G.n_oct;
+}
+
+extern "C" size_t vo_sift_workspace_bytes(int n_frames, int width, int height, int cap) {
+  Geom G;
+  if (n_frames < 1 || cap < 1 || width < 2 || height < 2 || make_geom(width, height, &G)) return 0;
+  return carve(nullptr, G, n_frames, cap).bytes;
+}
+
+extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int width, int height,
+                                    int cap, float* kp, uint8_t* desc, int32_t* n_out,
+                                    int32_t* status, float* pyramid_out, void* ws, size_t ws_bytes,
+                                    void* stream) {
+  VO_REQUIRE(images && kp && desc && n_out && status && ws, VO_ERR_INVALID_ARG,
+             "vo_sift_detect_batch: null pointer");
+  VO_REQUIRE(n_frames >= 1 && cap >= 1 && width >= 2 && height >= 2, VO_ERR_INVALID_ARG,
+             "vo_sift_detect_batch: bad sizes (%d frames, %d x %d, cap %d)", n_frames, width, height, cap);
+  VO_REQUIRE(n_frames <= 65535, VO_ERR_INVALID_ARG, "vo_sift_detect_batch: at most 65535 frames per call");
+  Geom G;
+  VO_REQUIRE(make_geom(width, height, &G) == 0, VO_ERR_INVALID_ARG,
+             "vo_sift_detect_batch: image size %d x %d gives no valid octave count", width, height);
+  Kernels K;
+  VO_REQUIRE(make_kernels(&K) == 0, VO_ERR_INVALID_ARG, "vo_sift_detect_batch: Gaussian kernel too wide");
+  const Ws w = carve(ws, G, n_frames, cap);
+  VO_REQUIRE(ws_bytes >= w.bytes, VO_ERR_WORKSPACE, "vo_sift_detect_batch: workspace %zu < %zu bytes",
+             ws_bytes, w.bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int F = n_frames;
+  cudaMemsetAsync(w.n_cand, 0, (size_t)F * 4, st);
+  cudaMemsetAsync(w.n_raw, 0, (size_t)F * 4, st);
+  cudaMemsetAsync(status, 0, (size_t)F * 4, st);
+  cudaMemsetAsync(n_out, 0, (size_t)F * 4, st);
+  {
+    vo::ProfScope prof(10, st);
+    // base image: 2x upsampling into layer 1's slot, blurred into layer 0
+    float* l0 = w.pyr + G.off[0];
+    float* tmp = l0 + (size_t)G.h[0] * G.w[0];
+    upsample_kernel<<<dim3((2 * width + 255) / 256, 2 * height, F), 256, 0, st>>>(images, height, width,
+                                                                                tmp, G.frame_stride);
+    blur_kernel<<<dim3((G.w[0] + TW - 1) / TW, (G.h[0] + TH - 1) / TH, F), 256, 0, st>>>(
+        tmp, l0, G.h[0], G.w[0], G.frame_stride, K, 0);
+    for (int o = 0; o < G.n_oct; ++o) {
+      const size_t ls = (size_t)G.h[o] * G.w[o];
+      float* base = w.pyr + G.off[o];
+      if (o > 0) {
+        const float* src = w.pyr + G.off[o - 1] + (size_t)NL * G.h[o - 1] * G.w[o - 1];
+        halve_kernel<<<dim3((G.w[o] + 255) / 256, G.h[o], F), 256, 0, st>>>(
+            src, G.h[o - 1], G.w[o - 1], base, G.h[o], G.w[o], G.frame_stride);
+      }
+      for (int i = 1; i < LAYERS; ++i)
+        blur_kernel<<<dim3((G.w[o] + TW - 1) / TW, (G.h[o] + TH - 1) / TH, F), 256, 0, st>>>(
+            base + (i - 1) * ls, base + i * ls, G.h[o], G.w[o], G.frame_stride, K, i);
+    }
+  }
+  {
+    vo::ProfScope prof(11, st);
+    for (int o = 0; o < G.n_oct; ++o) {
+      if (G.h[o] <= 2 * BORDER || G.w[o] <= 2 * BORDER) continue;
+      extrema_kernel<<<dim3((G.w[o] + 31) / 32, (G.h[o] + 7) / 8, F), 256, 0, st>>>(
+          w.pyr, G, o, cap, w.n_cand, w.cand, status);
+    }
+    const int bx = cap < 2048 ? cap : 2048;
+    orient_kernel<<<dim3(bx, F), 64, 0, st>>>(w.pyr, G, cap, w.n_cand, w.cand, w.n_raw, w.raw, status);
+    rank_kernel<<<dim3((cap + 255) / 256 < 16 ? (cap + 255) / 256 : 16, F), 256, 0, st>>>(cap, w.n_raw, w.raw,
+                                                                                         w.sorted);
+    finalize_kernel<<<F, 256, 0, st>>>(cap, w.n_raw, w.sorted, kp, n_out);
+  }
+  {
+    vo::ProfScope prof(12, st);
+    const int bx = cap < 2048 ? cap : 2048;
+    describe_kernel<<<dim3(bx, F), 128, 0, st>>>(w.pyr, G, cap, n_out, kp, desc);
+  }
+  if (pyramid_out)
+    cudaMemcpyAsync(pyramid_out, w.pyr, (size_t)F * G.frame_stride * 4, cudaMemcpyDeviceToDevice, st);
+  return vo::check_launch("vo_sift_detect_batch");
+}
