@@ -142,19 +142,22 @@ class PairPipeline:
 
     # ------------------------------------------------------------------ images in (N4 front end)
     def run_images(self, images, detector, pairs=None):
-        """Frames as IMAGES: ORB extraction (orb.OrbDetector.detect_batch, csrc/orb.cu) writes
+        """Frames as IMAGES: feature extraction (orb.OrbDetector.detect_batch, csrc/orb.cu, for an
+        "orb" pipeline; sift.SiftDetector.detect_batch, csrc/sift.cu, for a "sift" one — the
+        reference's live configuration, src/visual_slam.py:17-19) writes
         descriptors and key points straight into this pipeline's frame arrays on the device, then
         the hot path runs on `pairs` (default: consecutive frames).  What the reference does per
         frame in FrameGenerator.make_frame + match_current_and_previous_frame
         (src/frame_generator.py:10-38, src/visual_slam.py:286-307), for a whole sequence without a
         host round trip.  Returns the number of pairs; results are in the attributes."""
-        if self.descriptor != "orb":
-            raise ValueError("run_images: the GPU front end extracts ORB features")
         out = detector.detect_batch(images, cap=self.n_cap)
         f = int(out["n"].shape[0])
         if f > self.F:
             raise ValueError("run_images: more frames than max_frames")
-        self.desc[:f].copy_(out["desc"])
+        if out["desc"].shape[-1] != self.D:
+            raise ValueError("run_images: a %d-byte-descriptor detector on a '%s' pipeline"
+                             % (out["desc"].shape[-1], self.descriptor))
+        self.desc[:f].copy_(out["desc"])       # SIFT: uint8 -> the float32 rows cv2 would hand over
         self.kp[:f].copy_(out["kp"][:, :, :2])
         self.nkp[:f].copy_(out["n"])
         if pairs is None:
