@@ -129,43 +129,91 @@ __global__ void upsample_kernel(const uint8_t* __restrict__ img, int h, int w, f
 // rows: k = 0 .. 2r, fused multiply-add, except the last w % 4 columns (multiply, then add);
 // columns: f0 * x, then fma(x[-k] + x[+k], f[k], acc), except the last w % 8 columns.
 constexpr int TW = 64, TH = 32;
+// R = half width (5, 6, 8, 10, 13 for cv2's six sigmas).  The tile plus its halo is staged in
+// shared memory once (coalesced, borders reflected there); the row pass keeps a window of 8 + 2R
+// inputs in registers for 8 adjacent outputs of one row (lanes = rows, odd strides: no bank
+// conflicts), the column pass does the same down a column (lanes = columns).  Blocks that contain
+// columns of cv2's scalar tails take the per-output form of the same arithmetic.
+template <int R>
 __global__ void __launch_bounds__(256)
 blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w, long long stride,
             Kernels K, int ki) {
-  __shared__ float rowp[TH + 2 * MAX_R][TW];
-  __shared__ float fk[2 * MAX_R + 1];
-  const int r = K.r[ki];
+  constexpr int ROWS = TH + 2 * R, COLS = TW + 2 * R, IS = COLS | 1, RS = TW + 1;
+  __shared__ float in[ROWS][IS];
+  __shared__ float rowp[ROWS][RS];
+  __shared__ float fk[2 * R + 1];
   const int tid = threadIdx.x;
-  if (tid <= 2 * r) fk[tid] = K.f[ki][tid];
-  __syncthreads();
+  if (tid <= 2 * R) fk[tid] = K.f[ki][tid];
   const float* s = src + (size_t)blockIdx.z * stride;
   float* d = dst + (size_t)blockIdx.z * stride;
   const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
   const int row_tail = (w / 4) * 4, col_tail = (w / 8) * 8;
-  const int rows = TH + 2 * r;
-  for (int i = tid; i < rows * TW; i += 256) {
+  const int x_end = x0 + TW < w ? x0 + TW : w;
+  const bool tails = x_end > col_tail;            // col_tail <= row_tail
+  {
+    const int lane = tid & 31, wrp = tid >> 5;
+    const bool inside = x0 - R >= 0 && x0 + TW + R <= w;
+    for (int ry = wrp; ry < ROWS; ry += 8) {
+      const float* line = s + (size_t)reflect101(y0 - R + ry, h) * w;
+      if (inside) {
+        for (int cx = lane; cx < COLS; cx += 32) in[ry][cx] = line[x0 - R + cx];
+      } else {
+        for (int cx = lane; cx < COLS; cx += 32) in[ry][cx] = line[reflect101(x0 - R + cx, w)];
+      }
+    }
+  }
+  __syncthreads();
+  if (!tails) {
+    for (int task = tid; task < 8 * 64; task += 256) {
+      const int g = task >> 6, row = task & 63;
+      if (row >= ROWS) continue;
+      float win[8 + 2 * R], acc[8];
+#pragma unroll
+      for (int m = 0; m < 8 + 2 * R; ++m) win[m] = in[row][8 * g + m];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = __fmul_rn(win[j], fk[0]);
+#pragma unroll
+      for (int k = 1; k <= 2 * R; ++k) {
+        const float f = fk[k];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = __fmaf_rn(win[j + k], f, acc[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rowp[row][8 * g + j] = acc[j];
+    }
+    __syncthreads();
+    const int col = tid & 63, q = tid >> 6;
+    float win[8 + 2 * R], acc[8];
+#pragma unroll
+    for (int m = 0; m < 8 + 2 * R; ++m) win[m] = rowp[8 * q + m][col];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = __fmul_rn(fk[R], win[j + R]);
+#pragma unroll
+    for (int k = 1; k <= R; ++k) {
+      const float f = fk[R + k];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = __fmaf_rn(__fadd_rn(win[j + R - k], win[j + R + k]), f, acc[j]);
+    }
+    const int x = x0 + col;
+    if (x < w) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int y = y0 + 8 * q + j;
+        if (y < h) d[(size_t)y * w + x] = acc[j];
+      }
+    }
+    return;
+  }
+  for (int i = tid; i < ROWS * TW; i += 256) {
     const int ry = i / TW, cx = i % TW;
     const int x = x0 + cx;
     if (x >= w) continue;
-    const int y = reflect101(y0 - r + ry, h);
-    const float* line = s + (size_t)y * w;
-    float acc;
-    if (x - r >= 0 && x + r < w) {
-      const float* p = line + x - r;
-      acc = __fmul_rn(p[0], fk[0]);
-      if (x < row_tail) {
-        for (int k = 1; k <= 2 * r; ++k) acc = __fmaf_rn(p[k], fk[k], acc);
-      } else {
-        for (int k = 1; k <= 2 * r; ++k) acc = __fadd_rn(__fmul_rn(p[k], fk[k]), acc);
-      }
+    const float* p = &in[ry][cx];
+    float acc = __fmul_rn(p[0], fk[0]);
+    if (x < row_tail) {
+      for (int k = 1; k <= 2 * R; ++k) acc = __fmaf_rn(p[k], fk[k], acc);
     } else {
-      acc = __fmul_rn(line[reflect101(x - r, w)], fk[0]);
-      if (x < row_tail) {
-        for (int k = 1; k <= 2 * r; ++k) acc = __fmaf_rn(line[reflect101(x - r + k, w)], fk[k], acc);
-      } else {
-        for (int k = 1; k <= 2 * r; ++k)
-          acc = __fadd_rn(__fmul_rn(line[reflect101(x - r + k, w)], fk[k]), acc);
-      }
+      for (int k = 1; k <= 2 * R; ++k) acc = __fadd_rn(__fmul_rn(p[k], fk[k]), acc);
     }
     rowp[ry][cx] = acc;
   }
@@ -174,16 +222,30 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
     const int ty = i / TW, cx = i % TW;
     const int x = x0 + cx, y = y0 + ty;
     if (x >= w || y >= h) continue;
-    float acc = __fmul_rn(fk[r], rowp[ty + r][cx]);
+    float acc = __fmul_rn(fk[R], rowp[ty + R][cx]);
     if (x < col_tail) {
-      for (int k = 1; k <= r; ++k)
-        acc = __fmaf_rn(__fadd_rn(rowp[ty + r - k][cx], rowp[ty + r + k][cx]), fk[r + k], acc);
+      for (int k = 1; k <= R; ++k)
+        acc = __fmaf_rn(__fadd_rn(rowp[ty + R - k][cx], rowp[ty + R + k][cx]), fk[R + k], acc);
     } else {
-      for (int k = 1; k <= r; ++k)
-        acc = __fadd_rn(__fmul_rn(__fadd_rn(rowp[ty + r - k][cx], rowp[ty + r + k][cx]), fk[r + k]), acc);
+      for (int k = 1; k <= R; ++k)
+        acc = __fadd_rn(__fmul_rn(__fadd_rn(rowp[ty + R - k][cx], rowp[ty + R + k][cx]), fk[R + k]), acc);
     }
     d[(size_t)y * w + x] = acc;
   }
+}
+
+static int launch_blur(const float* src, float* dst, int h, int w, long long stride, const Kernels& K,
+                       int ki, int n_frames, cudaStream_t st) {
+  const dim3 grid((w + TW - 1) / TW, (h + TH - 1) / TH, n_frames);
+  switch (K.r[ki]) {
+    case 5: blur_kernel<5><<<grid, 256, 0, st>>>(src, dst, h, w, stride, K, ki); break;
+    case 6: blur_kernel<6><<<grid, 256, 0, st>>>(src, dst, h, w, stride, K, ki); break;
+    case 8: blur_kernel<8><<<grid, 256, 0, st>>>(src, dst, h, w, stride, K, ki); break;
+    case 10: blur_kernel<10><<<grid, 256, 0, st>>>(src, dst, h, w, stride, K, ki); break;
+    case 13: blur_kernel<13><<<grid, 256, 0, st>>>(src, dst, h, w, stride, K, ki); break;
+    default: return -1;
+  }
+  return 0;
 }
 
 // ------------------------------------------------------------------ S3: next octave's first layer
@@ -306,20 +368,46 @@ extrema_kernel(const float* __restrict__ pyr, Geom G, int octv, int cap, int32_t
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   const int r = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (c < BORDER || c >= O.w - BORDER || r < BORDER || r >= O.h - BORDER) return;
+  // centre values of the five DoG layers first: most pixels fail the threshold on all three
+  const size_t ls = (size_t)O.h * O.w, pc = (size_t)r * O.w + c;
+  float gc[LAYERS];
+#pragma unroll
+  for (int l = 0; l < LAYERS; ++l) gc[l] = O.g[l * ls + pc];
+  bool any = false;
+#pragma unroll
+  for (int l = 1; l <= NL; ++l) any |= fabsf(__fsub_rn(gc[l + 1], gc[l])) > 1.f;   // threshold = 1
+  if (!any) return;
+  // 3 x 3 neighbourhoods of the five DoG layers in registers (54 loads instead of up to 162)
+  float dn[LAYERS - 1][9];
+  {
+    float prev[9], cur[9];
+#pragma unroll
+    for (int q = 0; q < 9; ++q) prev[q] = O.g[pc + (q / 3 - 1) * O.w + (q % 3 - 1)];
+#pragma unroll
+    for (int l = 1; l < LAYERS; ++l) {
+#pragma unroll
+      for (int q = 0; q < 9; ++q) {
+        cur[q] = O.g[l * ls + pc + (q / 3 - 1) * O.w + (q % 3 - 1)];
+        dn[l - 1][q] = __fsub_rn(cur[q], prev[q]);
+        prev[q] = cur[q];
+      }
+    }
+  }
+#pragma unroll
   for (int layer = 1; layer <= NL; ++layer) {
-    const float val = O.dog(layer, r, c);
+    const float val = dn[layer][4];
     if (!(fabsf(val) > 1.f)) continue;      // threshold = floor(0.5 * 0.04 / 3 * 255) = 1
     bool ext = true;
     if (val > 0.f) {
-      for (int l = layer - 1; l <= layer + 1 && ext; ++l)
-        for (int dy = -1; dy <= 1 && ext; ++dy)
-          for (int dx = -1; dx <= 1; ++dx)
-            if (val < O.dog(l, r + dy, c + dx)) { ext = false; break; }
+#pragma unroll
+      for (int l = layer - 1; l <= layer + 1; ++l)
+#pragma unroll
+        for (int q = 0; q < 9; ++q) ext &= !(val < dn[l][q]);
     } else {
-      for (int l = layer - 1; l <= layer + 1 && ext; ++l)
-        for (int dy = -1; dy <= 1 && ext; ++dy)
-          for (int dx = -1; dx <= 1; ++dx)
-            if (val > O.dog(l, r + dy, c + dx)) { ext = false; break; }
+#pragma unroll
+      for (int l = layer - 1; l <= layer + 1; ++l)
+#pragma unroll
+        for (int q = 0; q < 9; ++q) ext &= !(val > dn[l][q]);
     }
     if (!ext) continue;
     Cand k;
@@ -545,22 +633,26 @@ finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restr
 // ------------------------------------------------------------------ S7: descriptors
 // One block of 128 threads per key point; thread t owns output bin t = (row i, column j,
 // orientation k) of the 4 x 4 x 8 histogram.  The window is walked in row-major order in pieces
-// of DESC_CHUNK samples: all threads compute the samples of a piece (bin coordinates and the
-// eight trilinear shares, cv2's operation order) into shared memory, then every thread adds the
-// shares that land in ITS bin in sample order — the float sums are those of cv2's scalar loop,
-// independent of scheduling, and no atomics are needed.
-constexpr int DESC_CHUNK = 1024;
+// of DESC_CHUNK samples, a quarter per warp: the warp computes the samples that fall inside the
+// descriptor (bin coordinates and the eight trilinear shares, cv2's operation order) and packs them
+// in order into its part of shared memory; then every thread adds the shares that land in ITS bin,
+// warp part after warp part, in sample order — the float sums are those of cv2's scalar loop,
+// independent of scheduling, and no atomics are needed.  A 16-bit cell mask per sample lets a
+// thread skip the samples that do not touch its (i, j) cell with three instructions.
+constexpr int DESC_CHUNK = 1024, DESC_PART = DESC_CHUNK / 4;
 __global__ void __launch_bounds__(128)
 describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* __restrict__ n_kp,
                 const float* __restrict__ kp, uint8_t* __restrict__ desc) {
   const int f = blockIdx.y;
   const int n = n_kp[f];
   __shared__ float share[8][DESC_CHUNK];
-  __shared__ uint16_t where[DESC_CHUNK];       // (r0 + 1) | (c0 + 1) << 4 | o0 << 8; 0xffff = none
+  __shared__ __align__(16) uint32_t where[DESC_CHUNK];   // cell mask | (r0 + 1) << 16 | (c0 + 1) << 19 | o0 << 22
+  __shared__ int part_count[4];
   __shared__ float rawd[128];
   __shared__ float s_scale;
-  const int t = threadIdx.x;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const unsigned ti = (t >> 5) + 1, tj = ((t >> 3) & 3) + 1, tk = t & 7;
+  const unsigned cell = t >> 3;
   constexpr int d = 4, nb = 8;
   for (int idx = blockIdx.x; idx < n; idx += gridDim.x) {
     const float* k = kp + ((size_t)f * cap + idx) * KP_WORDS;
@@ -589,57 +681,83 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
     cos_t /= hist_width;
     sin_t /= hist_width;
     const int side = 2 * radius + 1;
-    const long len = (long)side * side;
+    const int len = side * side;              // radius <= image diagonal: fits an int
     float acc = 0.f, acc_wrap = 0.f;          // bin (i, j, k) and, for k == 0, bin (i, j, 8)
-    for (long base = 0; base < len; base += DESC_CHUNK) {
+    for (int base = 0; base < len; base += DESC_CHUNK) {
       __syncthreads();
-      for (int q = t; q < DESC_CHUNK; q += 128) {
-        uint16_t wv = 0xffff;
-        const long s = base + q;
+      int filled = 0;                         // samples this warp has packed so far
+      for (int u = 0; u < DESC_PART / 32; ++u) {
+        const int s = base + warp * DESC_PART + u * 32 + lane;
+        bool ok = false;
+        float rbin = 0.f, cbin = 0.f, c_rot = 0.f, r_rot = 0.f;
+        int r = 0, c = 0;
         if (s < len) {
-          const int i = (int)(s / side) - radius, j = (int)(s % side) - radius;
-          const float c_rot = j * cos_t - i * sin_t;
-          const float r_rot = j * sin_t + i * cos_t;
-          float rbin = r_rot + d / 2 - 0.5f;
-          float cbin = c_rot + d / 2 - 0.5f;
-          const int r = py + i, c = px + j;
-          if (rbin > -1.f && rbin < d && cbin > -1.f && cbin < d && r > 0 && r < rows - 1 && c > 0 &&
-              c < cols - 1) {
-            const float dx = img[(size_t)r * cols + c + 1] - img[(size_t)r * cols + c - 1];
-            const float dy = img[(size_t)(r - 1) * cols + c] - img[(size_t)(r + 1) * cols + c];
-            const float wgt = expf((c_rot * c_rot + r_rot * r_rot) * exp_scale);
-            const float og = fast_atan2_deg(dy, dx);
-            const float mag = sqrtf(dx * dx + dy * dy) * wgt;
-            float obin = (og - ori) * bins_per_rad;
-            const int r0 = (int)floorf(rbin), c0 = (int)floorf(cbin);
-            int o0 = (int)floorf(obin);
-            rbin -= r0; cbin -= c0; obin -= o0;
-            if (o0 < 0) o0 += nb;
-            if (o0 >= nb) o0 -= nb;
-            const float v_r1 = mag * rbin, v_r0 = mag - v_r1;
-            const float v_rc11 = v_r1 * cbin, v_rc10 = v_r1 - v_rc11;
-            const float v_rc01 = v_r0 * cbin, v_rc00 = v_r0 - v_rc01;
-            const float v111 = v_rc11 * obin, v110 = v_rc11 - v111;
-            const float v101 = v_rc10 * obin, v100 = v_rc10 - v101;
-            const float v011 = v_rc01 * obin, v010 = v_rc01 - v011;
-            const float v001 = v_rc00 * obin, v000 = v_rc00 - v001;
-            share[0][q] = v000; share[1][q] = v001; share[2][q] = v010; share[3][q] = v011;
-            share[4][q] = v100; share[5][q] = v101; share[6][q] = v110; share[7][q] = v111;
-            wv = (uint16_t)((r0 + 1) | ((c0 + 1) << 4) | (o0 << 8));
+          const int si = s / side;
+          const int i = si - radius, j = s - si * side - radius;
+          c_rot = j * cos_t - i * sin_t;
+          r_rot = j * sin_t + i * cos_t;
+          rbin = r_rot + d / 2 - 0.5f;
+          cbin = c_rot + d / 2 - 0.5f;
+          r = py + i;
+          c = px + j;
+          ok = rbin > -1.f && rbin < d && cbin > -1.f && cbin < d && r > 0 && r < rows - 1 && c > 0 &&
+               c < cols - 1;
+        }
+        const unsigned ball = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+          const int q = warp * DESC_PART + filled + __popc(ball & ((1u << lane) - 1u));
+          const float dx = img[(size_t)r * cols + c + 1] - img[(size_t)r * cols + c - 1];
+          const float dy = img[(size_t)(r - 1) * cols + c] - img[(size_t)(r + 1) * cols + c];
+          const float wgt = expf((c_rot * c_rot + r_rot * r_rot) * exp_scale);
+          const float og = fast_atan2_deg(dy, dx);
+          const float mag = sqrtf(dx * dx + dy * dy) * wgt;
+          float obin = (og - ori) * bins_per_rad;
+          const int r0 = (int)floorf(rbin), c0 = (int)floorf(cbin);
+          int o0 = (int)floorf(obin);
+          rbin -= r0; cbin -= c0; obin -= o0;
+          if (o0 < 0) o0 += nb;
+          if (o0 >= nb) o0 -= nb;
+          const float v_r1 = mag * rbin, v_r0 = mag - v_r1;
+          const float v_rc11 = v_r1 * cbin, v_rc10 = v_r1 - v_rc11;
+          const float v_rc01 = v_r0 * cbin, v_rc00 = v_r0 - v_rc01;
+          const float v111 = v_rc11 * obin, v110 = v_rc11 - v111;
+          const float v101 = v_rc10 * obin, v100 = v_rc10 - v101;
+          const float v011 = v_rc01 * obin, v010 = v_rc01 - v011;
+          const float v001 = v_rc00 * obin, v000 = v_rc00 - v001;
+          share[0][q] = v000; share[1][q] = v001; share[2][q] = v010; share[3][q] = v011;
+          share[4][q] = v100; share[5][q] = v101; share[6][q] = v110; share[7][q] = v111;
+          unsigned m = 0;
+#pragma unroll
+          for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+              const int ci = r0 + a, cj = c0 + b;
+              if (ci >= 0 && ci < d && cj >= 0 && cj < d) m |= 1u << (ci * 4 + cj);
+            }
+          where[q] = m | ((unsigned)(r0 + 1) << 16) | ((unsigned)(c0 + 1) << 19) | ((unsigned)o0 << 22);
+        }
+        filled += __popc(ball);
+      }
+      if (lane == 0) part_count[warp] = filled;
+      __syncthreads();
+      for (int part = 0; part < 4; ++part) {
+        const int m = part_count[part];
+        const int q0 = part * DESC_PART;
+        for (int q4 = q0; q4 < q0 + m; q4 += 4) {       // four samples per shared-memory load
+          const uint4 w4 = *reinterpret_cast<const uint4*>(&where[q4]);
+          const unsigned wvs[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const unsigned wv = wvs[u];
+            const int q = q4 + u;
+            if (q >= q0 + m || !((wv >> cell) & 1u)) continue;
+            const unsigned a = ti - ((wv >> 16) & 7u), b = tj - ((wv >> 19) & 7u);
+            const unsigned oo = (wv >> 22) & 7u;
+            const unsigned e = tk - oo;
+            if (e <= 1u) acc += share[a * 4 + b * 2 + e][q];
+            if (tk == 0 && oo == nb - 1) acc_wrap += share[a * 4 + b * 2 + 1][q];
           }
         }
-        where[q] = wv;
-      }
-      __syncthreads();
-      const int m = len - base < DESC_CHUNK ? (int)(len - base) : DESC_CHUNK;
-      for (int q = 0; q < m; ++q) {
-        const unsigned wv = where[q];
-        const unsigned a = ti - (wv & 15u), b = tj - ((wv >> 4) & 15u);
-        if ((a | b) > 1u) continue;
-        const unsigned oo = wv >> 8;
-        const unsigned e = tk - oo;
-        if (e <= 1u) acc += share[a * 4 + b * 2 + e][q];
-        if (tk == 0 && oo == nb - 1) acc_wrap += share[a * 4 + b * 2 + 1][q];
       }
     }
     // circular orientation bins: hist[0] += hist[n] (hist[n + 1] never receives anything)
@@ -744,8 +862,8 @@ extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int wid
     float* tmp = l0 + (size_t)G.h[0] * G.w[0];
     upsample_kernel<<<dim3((2 * width + 255) / 256, 2 * height, F), 256, 0, st>>>(images, height, width,
                                                                                 tmp, G.frame_stride);
-    blur_kernel<<<dim3((G.w[0] + TW - 1) / TW, (G.h[0] + TH - 1) / TH, F), 256, 0, st>>>(
-        tmp, l0, G.h[0], G.w[0], G.frame_stride, K, 0);
+    VO_REQUIRE(launch_blur(tmp, l0, G.h[0], G.w[0], G.frame_stride, K, 0, F, st) == 0, VO_ERR_INVALID_ARG,
+               "vo_sift_detect_batch: no blur kernel for half width %d", K.r[0]);
     for (int o = 0; o < G.n_oct; ++o) {
       const size_t ls = (size_t)G.h[o] * G.w[o];
       float* base = w.pyr + G.off[o];
@@ -755,8 +873,9 @@ extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int wid
             src, G.h[o - 1], G.w[o - 1], base, G.h[o], G.w[o], G.frame_stride);
       }
       for (int i = 1; i < LAYERS; ++i)
-        blur_kernel<<<dim3((G.w[o] + TW - 1) / TW, (G.h[o] + TH - 1) / TH, F), 256, 0, st>>>(
-            base + (i - 1) * ls, base + i * ls, G.h[o], G.w[o], G.frame_stride, K, i);
+        VO_REQUIRE(launch_blur(base + (i - 1) * ls, base + i * ls, G.h[o], G.w[o], G.frame_stride, K, i, F,
+                               st) == 0,
+                   VO_ERR_INVALID_ARG, "vo_sift_detect_batch: no blur kernel for half width %d", K.r[i]);
     }
   }
   {
