@@ -353,6 +353,49 @@ def bench_configs(dev, peaks):
         torch.cuda.empty_cache()
     except Exception as ex:
         res["error_n2"] = repr(ex)
+
+    # ---- N4: SIFT extraction (the reference's live detector, src/visual_slam.py:17), 32 frames 480 x 640
+    try:
+        from visual_odometry_b200 import synth
+        from visual_odometry_b200.sift import SiftDetector
+        F, H, W = 32, 480, 640
+        imgs = torch.from_numpy(np.stack([synth.textured_image(H, W, 100 + i) for i in range(F)])).to(dev)
+        det = SiftDetector(device=dev)
+        out = det.detect_batch(imgs)
+        lib.vo_profile_enable(2)
+        ms = timed(lambda: det.detect_batch(imgs), warm=1, reps=3)
+        parts = {}
+        for kid, name in ((10, "pyramid"), (11, "extrema_orientation_order"), (12, "descriptors")):
+            tot, cnt = ctypes.c_double(0), ctypes.c_int(0)
+            lib.vo_profile_read(kid, ctypes.byref(tot), ctypes.byref(cnt))
+            parts[name] = tot.value / max(cnt.value, 1)
+        lib.vo_profile_enable(0)
+        floats = sum(6 * w * h for w, h in det.octaves(W, H))
+        # per frame: the pyramid written once, 5 of 6 layers read once as blur sources, all layers
+        # read once by the extrema pass, the image read once
+        alg = 4.0 * floats * (1 + 5.0 / 6 + 1) + H * W
+        gbs = alg * F / (ms * 1e-3) / 1e9
+        entry = {"what": "32 frames 480 x 640 -> key points + 128-byte descriptors in cv2's order "
+                         "(cv2.SIFT_create() defaults)", "ms": ms, "frames_per_s": F / ms * 1e3,
+                 "key_points_per_frame": float(out["n"].float().mean().item()), "stage_ms": parts,
+                 "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
+                              "frac": gbs / hbm if hbm else None,
+                              "algorithmic": "%.1f MB per frame (pyramid of %d floats: 1 write + 5/6 blur "
+                                             "reads + 1 extrema read)" % (alg / 1e6, floats)}}
+        try:
+            import cv2
+            t0 = time.perf_counter()
+            for i in range(4):
+                cv2.SIFT_create().detectAndCompute(imgs[i].cpu().numpy(), None)
+            entry["cv2_cpu_ms_per_frame"] = (time.perf_counter() - t0) / 4 * 1e3
+            entry["cv2_threads"] = cv2.getNumThreads()
+        except ImportError:
+            pass
+        res["N4_sift_extraction"] = entry
+        del imgs, det, out
+        torch.cuda.empty_cache()
+    except Exception as ex:
+        res["error_n4"] = repr(ex)
     return res
 
 

@@ -45,7 +45,7 @@ def test_reference_visual_slam_runs_on_compat_modules(compat_path):
                        [802.832, 565.427, 240.124], atol=1e-3)
     assert vs.cv2 is initials.cv2 and hasattr(vs.cv2, "solvePnPRansac")
     # the matcher VisualSlam.__init__ builds (src/visual_slam.py:19) is the B200 one, and so is the
-    # ORB detector of the commented-out line 16 / of ImageAndKeypoints; SIFT stays cv2's
+    # ORB detector of the commented-out line 16 / of ImageAndKeypoints and the live SIFT detector (:17)
     from visual_odometry_b200.matcher import B200Matcher, NORM_L2
     from visual_odometry_b200.orb import OrbDetector
     assert isinstance(slam.bf, B200Matcher) and slam.bf.normType == NORM_L2 and slam.bf.crossCheck
@@ -53,7 +53,10 @@ def test_reference_visual_slam_runs_on_compat_modules(compat_path):
     assert isinstance(det, OrbDetector) and det.nfeatures == 700 and det.nlevels == 8
     with pytest.raises(NotImplementedError):
         vs.cv2.ORB_create(WTA_K=3)
-    assert type(slam.detector).__module__.startswith("cv2")
+    from visual_odometry_b200.sift import SiftDetector
+    assert isinstance(slam.detector, SiftDetector)
+    with pytest.raises(NotImplementedError):
+        vs.cv2.SIFT_create(nfeatures=500)
     # namedtuples keep the reference's field order
     assert initials.Match._fields == ('featureid1', 'featureid2', 'keypoint1', 'keypoint2',
                                       'descriptor1', 'descriptor2', 'distance', 'color')
@@ -116,3 +119,17 @@ def test_reference_run_loop_returns_when_headless(compat_path, tmp_path, monkeyp
     for _ in range(12):
         vs.cv2.imread(str(tmp_path / "f00.jpg"))
         assert vs.cv2.waitKey(400000) == -1
+
+
+def test_patched_map_statistics_on_an_empty_map_like_the_reference(compat_path):
+    """VisualSlam.run prints map statistics after frame 0, when the map is empty and its
+    camera_matrix is still None (src/visual_slam.py:354, src/map.py:236-239): the reference's loops
+    over no observations return 0 and touch nothing; the GPU drop-ins must do the same."""
+    from visual_odometry_b200 import compat
+    compat.install(reference_src=REF, patch_map=True)
+    ref_map = importlib.import_module("map")
+    m = ref_map.Map()
+    assert m.camera_matrix is None
+    assert m.calculate_reprojection_error() == 0
+    m.remove_observations_with_reprojection_errors_above_threshold()
+    m.show_map_statistics()

@@ -640,13 +640,14 @@ finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restr
 // independent of scheduling, and no atomics are needed.  A 16-bit cell mask per sample lets a
 // thread skip the samples that do not touch its (i, j) cell with three instructions.
 constexpr int DESC_CHUNK = 1024, DESC_PART = DESC_CHUNK / 4;
+constexpr int DESC_STRIDE = DESC_PART + 4;      // a part's list is padded to a multiple of 4 with empty words
 __global__ void __launch_bounds__(128)
 describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* __restrict__ n_kp,
                 const float* __restrict__ kp, uint8_t* __restrict__ desc) {
   const int f = blockIdx.y;
   const int n = n_kp[f];
-  __shared__ float share[8][DESC_CHUNK];
-  __shared__ __align__(16) uint32_t where[DESC_CHUNK];   // cell mask | (r0 + 1) << 16 | (c0 + 1) << 19 | o0 << 22
+  __shared__ float share[8][4 * DESC_STRIDE];
+  __shared__ __align__(16) uint32_t where[4 * DESC_STRIDE];   // cell mask | (r0 + 1) << 16 | (c0 + 1) << 19 | o0 << 22
   __shared__ int part_count[4];
   __shared__ float rawd[128];
   __shared__ float s_scale;
@@ -705,7 +706,7 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
         }
         const unsigned ball = __ballot_sync(0xffffffffu, ok);
         if (ok) {
-          const int q = warp * DESC_PART + filled + __popc(ball & ((1u << lane) - 1u));
+          const int q = warp * DESC_STRIDE + filled + __popc(ball & ((1u << lane) - 1u));
           const float dx = img[(size_t)r * cols + c + 1] - img[(size_t)r * cols + c - 1];
           const float dy = img[(size_t)(r - 1) * cols + c] - img[(size_t)(r + 1) * cols + c];
           const float wgt = expf((c_rot * c_rot + r_rot * r_rot) * exp_scale);
@@ -738,24 +739,28 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
         }
         filled += __popc(ball);
       }
+      if (lane < 4) where[warp * DESC_STRIDE + filled + lane] = 0u;
       if (lane == 0) part_count[warp] = filled;
       __syncthreads();
       for (int part = 0; part < 4; ++part) {
         const int m = part_count[part];
-        const int q0 = part * DESC_PART;
+        const int q0 = part * DESC_STRIDE;
         for (int q4 = q0; q4 < q0 + m; q4 += 4) {       // four samples per shared-memory load
           const uint4 w4 = *reinterpret_cast<const uint4*>(&where[q4]);
           const unsigned wvs[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const unsigned wv = wvs[u];
-            const int q = q4 + u;
-            if (q >= q0 + m || !((wv >> cell) & 1u)) continue;
+            const unsigned wv = wvs[u];              // 0 behind the part's last sample
+            const bool in_cell = (wv >> cell) & 1u;
+            if (!__any_sync(0xffffffffu, in_cell)) continue;      // warp-uniform skip
             const unsigned a = ti - ((wv >> 16) & 7u), b = tj - ((wv >> 19) & 7u);
             const unsigned oo = (wv >> 22) & 7u;
-            const unsigned e = tk - oo;
-            if (e <= 1u) acc += share[a * 4 + b * 2 + e][q];
-            if (tk == 0 && oo == nb - 1) acc_wrap += share[a * 4 + b * 2 + 1][q];
+            const bool wraps = tk == 0 && oo == nb - 1;           // share of bin 8 -> bin 0's extra sum
+            const unsigned e = wraps ? 1u : tk - oo;
+            const bool hit = in_cell && e <= 1u;
+            const float v = hit ? share[a * 4 + b * 2 + e][q4 + u] : 0.f;   // + 0 leaves a sum as it is
+            acc += wraps ? 0.f : v;
+            acc_wrap += wraps ? v : 0.f;
           }
         }
       }

@@ -2,9 +2,9 @@
 
 src/visual_slam.py calls cv2.solvePnPRansac (:231) and cv2.Rodrigues (:243) directly, so the only
 way to move them to the GPU with that file unchanged is to rebind the name `cv2`.
-The matcher and the ORB detector the reference constructs through that name come from this
-package too (B200Matcher, OrbDetector); SIFT extraction is not implemented on the GPU and stays
-cv2's.  Everything not overridden forwards to the real OpenCV module (image I/O, resize, drawing).
+The matcher and the detectors the reference constructs through that name come from this
+package too (B200Matcher, OrbDetector, SiftDetector).  Everything not overridden forwards to the
+real OpenCV module (image I/O, resize, drawing).
 """
 import numpy as np
 
@@ -44,6 +44,14 @@ class _Cv2Namespace:
                                       "patchSize 31 only")
         from . import orb
         return orb.OrbDetector(nfeatures, scaleFactor, nlevels, edgeThreshold, fastThreshold)
+
+    def SIFT_create(self, nfeatures=0, nOctaveLayers=3, contrastThreshold=0.04, edgeThreshold=10,
+                    sigma=1.6, *a, **k):
+        """the live detector of src/visual_slam.py:17 / src/image_and_keypoints.py:12"""
+        if a or k:
+            raise NotImplementedError("B200 path: SIFT with cv2.SIFT_create()'s default parameters only")
+        from . import sift
+        return sift.SiftDetector(nfeatures, nOctaveLayers, contrastThreshold, edgeThreshold, sigma)
 
     # ---- headless GUI ----
     def imread(self, *a, **k):

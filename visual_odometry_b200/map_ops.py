@@ -67,6 +67,9 @@ def calculate_reprojection_error(self, threshold=10):
     """Drop-in for Map.calculate_reprojection_error (map.py:72-97): returns the total squared
     error (a 1-element array like the reference, whose dx/dy are 1-element arrays) and prints
     the observations above `threshold` as the reference does."""
+    if len(self.observations) == 0:
+        return 0        # like the reference's loop over no observations (camera_matrix may be None:
+        #                 VisualSlam.run prints the statistics of the still empty map after frame 0)
     out = reprojection_errors(*flatten_map(self), threshold)
     sq = out["sqerr"].cpu().numpy()
     for i in np.nonzero(sq > threshold)[0]:
@@ -77,6 +80,8 @@ def calculate_reprojection_error(self, threshold=10):
 
 def remove_observations_with_reprojection_errors_above_threshold(self, threshold=100):
     """Drop-in for map.py:46-70: keeps observations with sqerr < threshold, in order."""
+    if len(self.observations) == 0:
+        return
     out = reprojection_errors(*flatten_map(self), threshold)
     keep = out["keep"].cpu().numpy()
     self.observations = [o for o, k in zip(self.observations, keep) if k]
