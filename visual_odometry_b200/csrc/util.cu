@@ -32,19 +32,33 @@ extern "C" const char* vo_last_error_string(void) { return vo::g_err; }
 // ---------------------------------------------------------------- profiling hooks
 #include <mutex>
 #include <vector>
+
+#include <nvtx3/nvToolsExt.h>
 namespace vo {
 static int g_prof_level = 0;   // 1: the matching / scoring / solve kernels (ids < 5); 2: every scope
 static std::mutex g_prof_mu;
 struct ProfRec { int id; cudaEvent_t e0, e1; };
 static std::vector<ProfRec> g_prof;
 
+// NVTX range around every scope (named like the profile ids of include/vo_b200.h): visible in
+// Nsight Systems / ncu --nvtx; costs one null-pointer test when no tool is attached.
+static const char* scope_name(int id) {
+  static const char* names[] = {"vo:match",         "vo:ransac_score",  "vo:l2_gemm",      "vo:ransac_solve",
+                                "vo:hamming_expand", "vo:recover_pose",  "vo:triangulate",  "vo:chain",
+                                "vo:match_compact",  "vo:ransac_control", "vo:sift_pyramid", "vo:sift_extrema",
+                                "vo:sift_describe"};
+  return id >= 0 && id < (int)(sizeof(names) / sizeof(names[0])) ? names[id] : "vo:scope";
+}
+
 ProfScope::ProfScope(int kernel_id, cudaStream_t stream) : id(kernel_id), st(stream) {
+  nvtxRangePushA(scope_name(kernel_id));
   if (g_prof_level == 0 || (g_prof_level == 1 && kernel_id >= 5)) return;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
 }
 ProfScope::~ProfScope() {
+  nvtxRangePop();
   if (!e0) return;
   cudaEventRecord(e1, st);
   std::lock_guard<std::mutex> lk(g_prof_mu);
