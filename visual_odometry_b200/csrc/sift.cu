@@ -631,29 +631,29 @@ finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restr
 }
 
 // ------------------------------------------------------------------ S7: descriptors
-// One block of 128 threads per key point; thread t owns output bin t = (row i, column j,
-// orientation k) of the 4 x 4 x 8 histogram.  The window is walked in row-major order in pieces
-// of DESC_CHUNK samples, a quarter per warp: the warp computes the samples that fall inside the
-// descriptor (bin coordinates and the eight trilinear shares, cv2's operation order) and packs them
-// in order into its part of shared memory; then every thread adds the shares that land in ITS bin,
-// warp part after warp part, in sample order — the float sums are those of cv2's scalar loop,
-// independent of scheduling, and no atomics are needed.  A 16-bit cell mask per sample lets a
-// thread skip the samples that do not touch its (i, j) cell with three instructions.
-constexpr int DESC_CHUNK = 1024, DESC_PART = DESC_CHUNK / 4;
-constexpr int DESC_STRIDE = DESC_PART + 4;      // a part's list is padded to a multiple of 4 with empty words
+// One block of 128 threads per key point; warp i owns row i of the 4 x 4 x 8 histogram and lane
+// (j, k) its bin.  The window is walked in row-major order in pieces of 4 x DESC_PART samples, a
+// quarter per warp: the warp computes the samples that fall inside the descriptor (bin coordinates,
+// trilinear shares in cv2's operation order) and routes each to the lists of the one or two
+// histogram rows it touches — ballot compaction keeps every list in sample order, one segment per
+// producing warp.  Then warp i walks row i's four segments in order and every lane adds the share
+// that lands in ITS bin: the float sums are those of cv2's scalar loop, independent of scheduling,
+// no atomics.  A sample costs the consumer ~12 instructions and only the rows it touches see it.
+constexpr int DESC_PART = 128;                   // samples per warp and piece
+constexpr int DESC_STRIDE = DESC_PART + 4;       // segment padded with empty words to a multiple of 4
 __global__ void __launch_bounds__(128)
 describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* __restrict__ n_kp,
                 const float* __restrict__ kp, uint8_t* __restrict__ desc) {
   const int f = blockIdx.y;
   const int n = n_kp[f];
-  __shared__ float share[8][4 * DESC_STRIDE];
-  __shared__ __align__(16) uint32_t where[4 * DESC_STRIDE];   // cell mask | (r0 + 1) << 16 | (c0 + 1) << 19 | o0 << 22
-  __shared__ int part_count[4];
+  // segment (row R, producing warp p) = index R * 4 + p
+  __shared__ float share[16][4][DESC_STRIDE];                 // [segment][b * 2 + e][sample]
+  __shared__ __align__(4) uint8_t meta[16][DESC_STRIDE];      // (c0 + 1) | o0 << 3; 0xff = none
+  __shared__ int seg_count[16];
   __shared__ float rawd[128];
   __shared__ float s_scale;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const unsigned ti = (t >> 5) + 1, tj = ((t >> 3) & 3) + 1, tk = t & 7;
-  const unsigned cell = t >> 3;
+  const unsigned tj = ((t >> 3) & 3) + 1, tk = t & 7;
   constexpr int d = 4, nb = 8;
   for (int idx = blockIdx.x; idx < n; idx += gridDim.x) {
     const float* k = kp + ((size_t)f * cap + idx) * KP_WORDS;
@@ -684,9 +684,9 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
     const int side = 2 * radius + 1;
     const int len = side * side;              // radius <= image diagonal: fits an int
     float acc = 0.f, acc_wrap = 0.f;          // bin (i, j, k) and, for k == 0, bin (i, j, 8)
-    for (int base = 0; base < len; base += DESC_CHUNK) {
+    for (int base = 0; base < len; base += 4 * DESC_PART) {
       __syncthreads();
-      int filled = 0;                         // samples this warp has packed so far
+      int fill[4] = {0, 0, 0, 0};             // samples this warp has routed to rows 0 .. 3
       for (int u = 0; u < DESC_PART / 32; ++u) {
         const int s = base + warp * DESC_PART + u * 32 + lane;
         bool ok = false;
@@ -704,61 +704,64 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
           ok = rbin > -1.f && rbin < d && cbin > -1.f && cbin < d && r > 0 && r < rows - 1 && c > 0 &&
                c < cols - 1;
         }
-        const unsigned ball = __ballot_sync(0xffffffffu, ok);
+        if (!__any_sync(0xffffffffu, ok)) continue;
+        int r0 = -9, c0 = 0, o0 = 0;
+        float v_r0 = 0.f, v_r1 = 0.f, obin = 0.f;
         if (ok) {
-          const int q = warp * DESC_STRIDE + filled + __popc(ball & ((1u << lane) - 1u));
           const float dx = img[(size_t)r * cols + c + 1] - img[(size_t)r * cols + c - 1];
           const float dy = img[(size_t)(r - 1) * cols + c] - img[(size_t)(r + 1) * cols + c];
           const float wgt = expf((c_rot * c_rot + r_rot * r_rot) * exp_scale);
           const float og = fast_atan2_deg(dy, dx);
           const float mag = sqrtf(dx * dx + dy * dy) * wgt;
-          float obin = (og - ori) * bins_per_rad;
-          const int r0 = (int)floorf(rbin), c0 = (int)floorf(cbin);
-          int o0 = (int)floorf(obin);
+          obin = (og - ori) * bins_per_rad;
+          r0 = (int)floorf(rbin);
+          c0 = (int)floorf(cbin);
+          o0 = (int)floorf(obin);
           rbin -= r0; cbin -= c0; obin -= o0;
           if (o0 < 0) o0 += nb;
           if (o0 >= nb) o0 -= nb;
-          const float v_r1 = mag * rbin, v_r0 = mag - v_r1;
-          const float v_rc11 = v_r1 * cbin, v_rc10 = v_r1 - v_rc11;
-          const float v_rc01 = v_r0 * cbin, v_rc00 = v_r0 - v_rc01;
-          const float v111 = v_rc11 * obin, v110 = v_rc11 - v111;
-          const float v101 = v_rc10 * obin, v100 = v_rc10 - v101;
-          const float v011 = v_rc01 * obin, v010 = v_rc01 - v011;
-          const float v001 = v_rc00 * obin, v000 = v_rc00 - v001;
-          share[0][q] = v000; share[1][q] = v001; share[2][q] = v010; share[3][q] = v011;
-          share[4][q] = v100; share[5][q] = v101; share[6][q] = v110; share[7][q] = v111;
-          unsigned m = 0;
-#pragma unroll
-          for (int a = 0; a < 2; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b) {
-              const int ci = r0 + a, cj = c0 + b;
-              if (ci >= 0 && ci < d && cj >= 0 && cj < d) m |= 1u << (ci * 4 + cj);
-            }
-          where[q] = m | ((unsigned)(r0 + 1) << 16) | ((unsigned)(c0 + 1) << 19) | ((unsigned)o0 << 22);
+          v_r1 = mag * rbin;
+          v_r0 = mag - v_r1;
         }
-        filled += __popc(ball);
+#pragma unroll
+        for (int R = 0; R < 4; ++R) {
+          const bool lower = r0 == R, upper = r0 + 1 == R;      // share of row r0 / of row r0 + 1
+          const bool keep = lower || upper;
+          const unsigned ball = __ballot_sync(0xffffffffu, keep);
+          if (keep) {
+            const int q = fill[R] + __popc(ball & ((1u << lane) - 1u));
+            const int seg = R * 4 + warp;
+            const float v_r = upper ? v_r1 : v_r0;
+            const float v_c1 = v_r * cbin, v_c0 = v_r - v_c1;
+            const float v_11 = v_c1 * obin, v_10 = v_c1 - v_11;
+            const float v_01 = v_c0 * obin, v_00 = v_c0 - v_01;
+            share[seg][0][q] = v_00; share[seg][1][q] = v_01;
+            share[seg][2][q] = v_10; share[seg][3][q] = v_11;
+            meta[seg][q] = (uint8_t)((c0 + 1) | (o0 << 3));
+          }
+          fill[R] += __popc(ball);
+        }
       }
-      if (lane < 4) where[warp * DESC_STRIDE + filled + lane] = 0u;
-      if (lane == 0) part_count[warp] = filled;
+#pragma unroll
+      for (int R = 0; R < 4; ++R) {
+        if (lane < 4) meta[R * 4 + warp][fill[R] + lane] = 0xff;
+        if (lane == 0) seg_count[R * 4 + warp] = fill[R];
+      }
       __syncthreads();
-      for (int part = 0; part < 4; ++part) {
-        const int m = part_count[part];
-        const int q0 = part * DESC_STRIDE;
-        for (int q4 = q0; q4 < q0 + m; q4 += 4) {       // four samples per shared-memory load
-          const uint4 w4 = *reinterpret_cast<const uint4*>(&where[q4]);
-          const unsigned wvs[4] = {w4.x, w4.y, w4.z, w4.w};
+      for (int p = 0; p < 4; ++p) {           // row `warp`: the segments of producers 0 .. 3
+        const int seg = warp * 4 + p;
+        const int m = seg_count[seg];
+        for (int q4 = 0; q4 < m; q4 += 4) {
+          const uint32_t m4 = *reinterpret_cast<const uint32_t*>(&meta[seg][q4]);
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const unsigned wv = wvs[u];              // 0 behind the part's last sample
-            const bool in_cell = (wv >> cell) & 1u;
-            if (!__any_sync(0xffffffffu, in_cell)) continue;      // warp-uniform skip
-            const unsigned a = ti - ((wv >> 16) & 7u), b = tj - ((wv >> 19) & 7u);
-            const unsigned oo = (wv >> 22) & 7u;
-            const bool wraps = tk == 0 && oo == nb - 1;           // share of bin 8 -> bin 0's extra sum
+            const unsigned mv = (m4 >> (8 * u)) & 0xffu;        // 0xff behind the last sample
+            const unsigned b = tj - (mv & 7u);
+            const unsigned oo = (mv >> 3) & 7u;
+            const bool wraps = tk == 0 && oo == nb - 1;         // share of bin 8 -> bin 0's extra sum
             const unsigned e = wraps ? 1u : tk - oo;
-            const bool hit = in_cell && e <= 1u;
-            const float v = hit ? share[a * 4 + b * 2 + e][q4 + u] : 0.f;   // + 0 leaves a sum as it is
+            const bool hit = b <= 1u && e <= 1u && mv != 0xffu;
+            const float v = hit ? share[seg][b * 2 + e][q4 + u] : 0.f;   // + 0 leaves a sum as it is
             acc += wraps ? 0.f : v;
             acc_wrap += wraps ? v : 0.f;
           }
