@@ -99,6 +99,17 @@ __device__ __forceinline__ int reflect101(int i, int n) {
   return i >= n ? period - i : i;
 }
 
+// one fold covers every position a tile's halo can reach unless the image is smaller than the halo
+__device__ __forceinline__ int reflect_once(int i, int n) {
+  int j = i < 0 ? -i : i;
+  j = j >= n ? 2 * (n - 1) - j : j;
+  return (unsigned)j < (unsigned)n ? j : reflect101(i, n);
+}
+
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src_gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+
 // ------------------------------------------------------------------ S1: uint8 -> float, 2x linear
 // resize(INTER_LINEAR) by exactly 2: taps (d + 0.5) / 2 - 0.5, weights 0.25 / 0.75, clamped; all
 // products and sums are exact in float, so the order does not matter.
@@ -151,16 +162,21 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
   const int x_end = x0 + TW < w ? x0 + TW : w;
   const bool tails = x_end > col_tail;            // col_tail <= row_tail
   {
+    // staging: asynchronous 4-byte copies (no register round trip, all of a warp's rows in flight)
     const int lane = tid & 31, wrp = tid >> 5;
     const bool inside = x0 - R >= 0 && x0 + TW + R <= w;
     for (int ry = wrp; ry < ROWS; ry += 8) {
-      const float* line = s + (size_t)reflect101(y0 - R + ry, h) * w;
-      if (inside) {
-        for (int cx = lane; cx < COLS; cx += 32) in[ry][cx] = line[x0 - R + cx];
-      } else {
-        for (int cx = lane; cx < COLS; cx += 32) in[ry][cx] = line[reflect101(x0 - R + cx, w)];
+      const float* line = s + (size_t)reflect_once(y0 - R + ry, h) * w;
+#pragma unroll
+      for (int it = 0; it < (COLS + 31) / 32; ++it) {
+        const int cx = lane + 32 * it;
+        if (cx < COLS) {
+          const int x = inside ? x0 - R + cx : reflect_once(x0 - R + cx, w);
+          cp_async4(&in[ry][cx], line + x);
+        }
       }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
   }
   __syncthreads();
   if (!tails) {
@@ -196,11 +212,11 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
     }
     const int x = x0 + col;
     if (x < w) {
+      float* dp = d + (size_t)(y0 + 8 * q) * w + x;
+      const int left = h - (y0 + 8 * q);          // rows of this group inside the image
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int y = y0 + 8 * q + j;
-        if (y < h) d[(size_t)y * w + x] = acc[j];
-      }
+      for (int j = 0; j < 8; ++j)
+        if (j < left) dp[(size_t)j * w] = acc[j];
     }
     return;
   }
