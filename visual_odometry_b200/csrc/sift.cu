@@ -393,37 +393,33 @@ extrema_kernel(const float* __restrict__ pyr, Geom G, int octv, int cap, int32_t
 #pragma unroll
   for (int l = 1; l <= NL; ++l) any |= fabsf(__fsub_rn(gc[l + 1], gc[l])) > 1.f;   // threshold = 1
   if (!any) return;
-  // 3 x 3 neighbourhoods of the five DoG layers in registers (54 loads instead of up to 162)
-  float dn[LAYERS - 1][9];
-  {
-    float prev[9], cur[9];
+  float dc[LAYERS - 1];
 #pragma unroll
-    for (int q = 0; q < 9; ++q) prev[q] = O.g[pc + (q / 3 - 1) * O.w + (q % 3 - 1)];
-#pragma unroll
-    for (int l = 1; l < LAYERS; ++l) {
-#pragma unroll
-      for (int q = 0; q < 9; ++q) {
-        cur[q] = O.g[l * ls + pc + (q / 3 - 1) * O.w + (q % 3 - 1)];
-        dn[l - 1][q] = __fsub_rn(cur[q], prev[q]);
-        prev[q] = cur[q];
-      }
-    }
-  }
+  for (int l = 0; l < LAYERS - 1; ++l) dc[l] = __fsub_rn(gc[l + 1], gc[l]);
 #pragma unroll
   for (int layer = 1; layer <= NL; ++layer) {
-    const float val = dn[layer][4];
+    const float val = dc[layer];
     if (!(fabsf(val) > 1.f)) continue;      // threshold = floor(0.5 * 0.04 / 3 * 255) = 1
+    const bool pos = val > 0.f;
+    // the 8 neighbours in the same DoG layer first (nine of ten candidates end here), then the
+    // 9 + 9 of the layers below and above; the two Gaussian layers loaded here are reused there
+    float lo[9], hi[9];
     bool ext = true;
-    if (val > 0.f) {
 #pragma unroll
-      for (int l = layer - 1; l <= layer + 1; ++l)
+    for (int q = 0; q < 9; ++q) {
+      const size_t p = pc + (q / 3 - 1) * O.w + (q % 3 - 1);
+      lo[q] = O.g[layer * ls + p];
+      hi[q] = O.g[(layer + 1) * ls + p];
+      const float nb = __fsub_rn(hi[q], lo[q]);
+      ext &= pos ? !(val < nb) : !(val > nb);
+    }
+    if (!ext) continue;
 #pragma unroll
-        for (int q = 0; q < 9; ++q) ext &= !(val < dn[l][q]);
-    } else {
-#pragma unroll
-      for (int l = layer - 1; l <= layer + 1; ++l)
-#pragma unroll
-        for (int q = 0; q < 9; ++q) ext &= !(val > dn[l][q]);
+    for (int q = 0; q < 9; ++q) {
+      const size_t p = pc + (q / 3 - 1) * O.w + (q % 3 - 1);
+      const float below = __fsub_rn(lo[q], O.g[(layer - 1) * ls + p]);
+      const float above = __fsub_rn(O.g[(layer + 2) * ls + p], hi[q]);
+      ext &= pos ? !(val < below) && !(val < above) : !(val > below) && !(val > above);
     }
     if (!ext) continue;
     Cand k;
