@@ -120,7 +120,10 @@ def cpu_reference_rate(seq, n_sample, workers):
     Returns pairs/s over the wall time of the pool."""
     import multiprocessing as mp
     jobs = [(seq.desc[b], seq.kp[b], seq.desc[b + 1], seq.kp[b + 1], seq.K) for b in range(n_sample)]
-    ctx = mp.get_context("fork")
+    # spawn, not fork: the parent may already have started cv2's thread pool (the cv2 figures of
+    # the configs block) and holds a CUDA context; a forked child of such a process deadlocks in
+    # cv2.setNumThreads
+    ctx = mp.get_context("spawn")
     with ctx.Pool(workers) as pool:
         pool.map(_cpu_pair_worker, jobs[:workers])           # warm-up (imports, page-in)
         t0 = time.perf_counter()
