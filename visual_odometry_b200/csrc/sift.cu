@@ -648,9 +648,10 @@ finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restr
 // quarter per warp: the warp computes the samples that fall inside the descriptor (bin coordinates,
 // trilinear shares in cv2's operation order) and routes each to the lists of the one or two
 // histogram rows it touches — ballot compaction keeps every list in sample order, one segment per
-// producing warp.  Then warp i walks row i's four segments in order and every lane adds the share
-// that lands in ITS bin: the float sums are those of cv2's scalar loop, independent of scheduling,
-// no atomics.  A sample costs the consumer ~12 instructions and only the rows it touches see it.
+// producing warp.  Then warp i walks row i's four segments in order, eight samples at a time, one
+// lane per (sample, column, orientation) share; shares of different samples for the same bin are
+// added in sample order (match.any rank), the rest in parallel: the float sums are those of cv2's
+// scalar loop, independent of scheduling, no atomics.
 constexpr int DESC_PART = 128;                   // samples per warp and piece
 constexpr int DESC_STRIDE = DESC_PART + 4;       // segment padded with empty words to a multiple of 4
 __global__ void __launch_bounds__(128)
@@ -662,6 +663,7 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
   __shared__ float share[16][4][DESC_STRIDE];                 // [segment][b * 2 + e][sample]
   __shared__ __align__(4) uint8_t meta[16][DESC_STRIDE];      // (c0 + 1) | o0 << 3; 0xff = none
   __shared__ int seg_count[16];
+  __shared__ float hrow[4][36];
   __shared__ float rawd[128];
   __shared__ float s_scale;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -695,7 +697,7 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
     sin_t /= hist_width;
     const int side = 2 * radius + 1;
     const int len = side * side;              // radius <= image diagonal: fits an int
-    float acc = 0.f, acc_wrap = 0.f;          // bin (i, j, k) and, for k == 0, bin (i, j, 8)
+    for (int q = lane; q < 36; q += 32) hrow[warp][q] = 0.f;   // bins (j, k = 0 .. 8) of this warp's row
     for (int base = 0; base < len; base += 4 * DESC_PART) {
       __syncthreads();
       int fill[4] = {0, 0, 0, 0};             // samples this warp has routed to rows 0 .. 3
@@ -760,26 +762,35 @@ describe_kernel(const float* __restrict__ pyr, Geom G, int cap, const int32_t* _
         if (lane == 0) seg_count[R * 4 + warp] = fill[R];
       }
       __syncthreads();
-      for (int p = 0; p < 4; ++p) {           // row `warp`: the segments of producers 0 .. 3
+      // row `warp`: the segments of producers 0 .. 3 in order, eight samples at a time: lane
+      // (s, b, e) carries the share of sample s for column c0 + b and orientation o0 + e; shares
+      // of different samples that land in the same bin are added in sample order (rank among
+      // the lanes with the same bin), everything else in parallel
+      float* hist = hrow[warp];
+      for (int p = 0; p < 4; ++p) {
         const int seg = warp * 4 + p;
         const int m = seg_count[seg];
-        for (int q4 = 0; q4 < m; q4 += 4) {
-          const uint32_t m4 = *reinterpret_cast<const uint32_t*>(&meta[seg][q4]);
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const unsigned mv = (m4 >> (8 * u)) & 0xffu;        // 0xff behind the last sample
-            const unsigned b = tj - (mv & 7u);
-            const unsigned oo = (mv >> 3) & 7u;
-            const bool wraps = tk == 0 && oo == nb - 1;         // share of bin 8 -> bin 0's extra sum
-            const unsigned e = wraps ? 1u : tk - oo;
-            const bool hit = b <= 1u && e <= 1u && mv != 0xffu;
-            const float v = hit ? share[seg][b * 2 + e][q4 + u] : 0.f;   // + 0 leaves a sum as it is
-            acc += wraps ? 0.f : v;
-            acc_wrap += wraps ? v : 0.f;
+        for (int q8 = 0; q8 < m; q8 += 8) {
+          const int q = q8 + (lane >> 2);
+          const unsigned b = (lane >> 1) & 1u, e = lane & 1u;
+          const unsigned mv = q < m ? meta[seg][q] : 0xffu;
+          const int j = (int)(mv & 7u) - 1 + (int)b;
+          const bool ok = mv != 0xffu && j >= 0 && j < d;
+          const int bin = j * 9 + (int)((mv >> 3) & 7u) + (int)e;
+          const float v = ok ? share[seg][b * 2 + e][q] : 0.f;
+          const unsigned peers = __match_any_sync(0xffffffffu, ok ? bin : 64 + lane);
+          const int rank = __popc(peers & ((1u << lane) - 1u));
+          const int steps = __reduce_max_sync(0xffffffffu, ok ? rank + 1 : 0);
+          for (int st = 0; st < steps; ++st) {
+            if (ok && rank == st) hist[bin] += v;
+            __syncwarp();
           }
         }
       }
     }
+    __syncthreads();
+    const float acc = hrow[warp][(tj - 1) * 9 + tk];
+    const float acc_wrap = tk == 0 ? hrow[warp][(tj - 1) * 9 + 8] : 0.f;
     // circular orientation bins: hist[0] += hist[n] (hist[n + 1] never receives anything)
     rawd[t] = tk == 0 ? acc + acc_wrap : acc;
     __syncthreads();
