@@ -91,8 +91,10 @@ def test_pyramid_is_bit_exact_and_key_points_equal_the_oracle(cuda_dev, h, w, se
     check(res[0][0], res[0][1], okp, odesc)
 
 
-@pytest.mark.parametrize("kind,h,w", [("texture", 375, 1242), ("texture", 1080, 1920), ("noise", 200, 300),
-                                      ("blocks", 256, 256), ("flat", 64, 80)])
+@pytest.mark.parametrize("kind,h,w", [("texture", 375, 1242), ("texture", 1080, 1920), ("texture", 2160, 3840),
+                                      ("noise", 200, 300),
+                                      ("blocks", 256, 256), ("flat", 64, 80), ("noise", 24, 20),
+                                      ("noise", 17, 33), ("smooth", 40, 56)])
 def test_equals_live_cv2(cuda_dev, kind, h, w):
     """Against cv2 itself on the box: noise has ~10 key points per 100 pixels of the doubled image
     (the capacity path), the block image exactly repeated structure, a flat image no key point."""
@@ -105,6 +107,9 @@ def test_equals_live_cv2(cuda_dev, kind, h, w):
         img[:, w // 2:] = img[:, :w // 2]
     elif kind == "flat":
         img = np.full((h, w), 77, np.uint8)
+    elif kind == "smooth":       # images smaller than the widest blur's halo: the general reflection
+        import cv2
+        img = cv2.resize(rng.integers(0, 256, (5, 7), dtype=np.uint8), (w, h), interpolation=cv2.INTER_CUBIC)
     else:
         img = synth.textured_image(h, w, h + w)
     ref, rdesc = cv_ref(img)
