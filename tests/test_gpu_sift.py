@@ -202,3 +202,20 @@ def test_image_sequence_to_poses_on_the_device_with_sift(cuda_dev):
         tdir = np.degrees(np.arccos(np.clip(tg[k] @ t_true, -1, 1)))
         assert int(pipe.n_inl[k].item()) > 100, (k, int(pipe.n_inl[k].item()))
         assert ang < 2.0 and tdir < 15.0, (k, ang, tdir)
+
+
+def test_slam_loop_from_images_with_sift(cuda_dev):
+    """DeviceSlam.run_images on the reference's live configuration: rendered frames -> SIFT
+    extraction -> L2 matching -> E-RANSAC / pose / triangulation -> map stage (PnP, map growth,
+    bundle adjustment, pruning) without descriptors or key points touching the host."""
+    pytest.importorskip("cv2")
+    from test_gpu_orb import _render_two_plane_sequence
+    from visual_odometry_b200.slam import DeviceSlam
+    images, K, cams = _render_two_plane_sequence(6)
+    slam = DeviceSlam(K, 4096, 6, descriptor="sift", ba_iterations=10)
+    log = slam.run_images(images, SiftDetector())
+    assert len(log) == 5
+    assert log[0]["n_points"] > 300 and log[0]["n_obs"] >= 2 * log[0]["n_points"] - 5
+    assert sum(bool(e["pnp_ok"]) for e in log[1:]) >= 3, log
+    assert log[-1]["n_points"] > log[0]["n_points"] // 2
+    assert len(log[-1]["cameras"]) >= 4

@@ -45,9 +45,10 @@ class DeviceSlam:
         return [self.step(b) for b in range(F - 1)]
 
     def run_images(self, images, detector):
-        """The same loop fed with IMAGES (uint8 [F,H,W] or BGR [F,H,W,3]): ORB extraction on the
-        device (orb.OrbDetector, reference src/frame_generator.py:25) writes straight into the
-        pipeline's frame arrays, then the hot path and the per-frame map stage as in `run`."""
+        """The same loop fed with IMAGES (uint8 [F,H,W] or BGR [F,H,W,3]): feature extraction on
+        the device (orb.OrbDetector or, for a "sift" loop, sift.SiftDetector; reference
+        src/frame_generator.py:25) writes straight into the pipeline's frame arrays, then the hot
+        path and the per-frame map stage as in `run`."""
         b = self.pipe.run_images(images, detector)
         return [self.step(k) for k in range(b)]
 
