@@ -247,11 +247,17 @@ __device__ __forceinline__ float thr2_from_K(const double* __restrict__ K, doubl
 }
 
 constexpr int SCORE_WARPS = 8;
+constexpr int SCORE_TILE = 1024;       // correspondences staged in shared memory at a time
+// One block = one pair and 8 of its samples (warp per sample).  The pair's correspondences go
+// through shared memory as float4 tiles shared by the 8 warps; per tile and model the nine
+// coefficients sit in registers, so a test is one 16-byte shared-memory load and ~20 fp32
+// operations.
 __global__ void __launch_bounds__(SCORE_WARPS * 32)
 ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_pairs, int chunk,
                     int chunk_stride, const double* __restrict__ K, double thr_px, RansacWs w) {
   __shared__ double Es[SCORE_WARPS][90];
   __shared__ float Ef[SCORE_WARPS][90];
+  __shared__ float4 tile[SCORE_TILE];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_act = w.n_active[round];
   const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
@@ -263,28 +269,49 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
   for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
     const int p = list[item / per_pair];
     const int s = (int)(item % per_pair) * SCORE_WARPS + warp;
-    if (s >= chunk) continue;
-    const int nm = w.nmodels[(size_t)p * chunk_stride + s];
-    if (nm == 0) continue;
-    const double* src = w.models + ((size_t)p * chunk_stride + s) * 90;
-    __syncwarp();
+    const int nm = s < chunk ? w.nmodels[(size_t)p * chunk_stride + s] : 0;
+    if (!__syncthreads_or(nm > 0)) continue;      // samples beyond the pair's bound: nothing to score
+    const double* src = w.models + ((size_t)p * chunk_stride + (s < chunk ? s : 0)) * 90;
     for (int e = lane; e < nm * 9; e += 32) { const double v = src[e]; Es[warp][e] = v; Ef[warp][e] = (float)v; }
-    __syncwarp();
     const int mp = m[p];
     const double4* pts = reinterpret_cast<const double4*>(w.ptsn) + (size_t)p * n_cap;
     int cnt = 0;
-    for (int i0 = 0; i0 < mp; i0 += 32) {
-      const int i = i0 + lane;
-      const bool act = i < mp;
-      double4 v = make_double4(0, 0, 0, 0);
-      if (act) v = ldg_d4(pts + i);
-      const float fx1 = (float)v.x, fy1 = (float)v.y, fx2 = (float)v.z, fy2 = (float)v.w;
+    for (int t0 = 0; t0 < mp; t0 += SCORE_TILE) {
+      const int tn = mp - t0 < SCORE_TILE ? mp - t0 : SCORE_TILE;
+      __syncthreads();                       // the previous tile (or item) is no longer read
+      for (int i = threadIdx.x; i < tn; i += SCORE_WARPS * 32) {
+        const double4 v = ldg_d4(pts + t0 + i);
+        tile[i] = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+      }
+      __syncthreads();
       for (int k = 0; k < nm; ++k) {
-        int dec = act ? sampson_sieve_f32(&Ef[warp][9 * k], fx1, fy1, fx2, fy2, tf_lo, tf_hi) : 0;
-        if (dec < 0) dec = sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
-        const bool inl = dec != 0;
-        const unsigned b = __ballot_sync(0xffffffffu, inl);
-        if (lane == k) cnt += __popc(b);
+        float e[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) e[q] = Ef[warp][9 * k + q];
+        int local = 0;
+        // two correspondences per trip (independent FMA chains); the fp64 decision of the rare
+        // undecided ones sits behind one branch per trip
+        for (int i = lane; i < tn; i += 64) {
+          const int i2 = i + 32;
+          const bool has2 = i2 < tn;
+          const float4 f = tile[i];
+          const float4 g = tile[has2 ? i2 : i];
+          int dec = sampson_sieve_f32(e, f.x, f.y, f.z, f.w, tf_lo, tf_hi);
+          int dec2 = has2 ? sampson_sieve_f32(e, g.x, g.y, g.z, g.w, tf_lo, tf_hi) : 0;
+          if ((dec | dec2) < 0) {
+            if (dec < 0) {
+              const double4 v = ldg_d4(pts + t0 + i);
+              dec = sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+            }
+            if (dec2 < 0) {
+              const double4 v = ldg_d4(pts + t0 + i2);
+              dec2 = sampson_inlier(&Es[warp][9 * k], v.x, v.y, v.z, v.w, thr2f, t_lo, t_hi);
+            }
+          }
+          local += dec + dec2;
+        }
+        for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+        if (lane == k) cnt += local;
       }
     }
     if (lane < nm) w.counts[((size_t)p * chunk_stride + s) * 10 + lane] = cnt;
