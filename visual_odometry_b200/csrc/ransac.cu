@@ -127,7 +127,7 @@ __global__ void ransac_init_kernel(const double* __restrict__ pts, const int32_t
 // Every kernel of a round walks the list of pairs that are still iterating (built by the init
 // kernel, rebuilt by every scan), with a fixed small grid: a round in which all pairs have
 // already stopped costs a few microseconds instead of tens of thousands of empty blocks.
-__global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int round, int n_pairs,
+__global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int round, int n_pairs, int it0,
                                      int chunk, int chunk_stride, RansacWs w) {
   const int n_act = w.n_active[round];
   const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
@@ -137,7 +137,11 @@ __global__ void ransac_sample_kernel(const int32_t* __restrict__ m, int round, i
     const int count = m[p];
     const uint64_t M = 0xffffffffffffffffull / (uint32_t)count + 1ull;
     int32_t* out = w.samples + (size_t)p * chunk_stride * 5;
-    for (int it = 0; it < chunk; ++it) {
+    // only the samples the pair's bound still allows: a pair whose bound ends inside this round
+    // stops after it (the bound never grows), so its generator state is not needed again
+    const int left = w.niters[p] - it0;
+    const int need = left < chunk ? left : chunk;
+    for (int it = 0; it < need; ++it) {
       int32_t idx[5];
       draw_sample(s, count, M, idx);
 #pragma unroll
@@ -538,7 +542,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
     const int chunk = sched[round];
     {
       ProfScope prof(9, st);
-      ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, chunk, C, w);
+      ransac_sample_kernel<<<list_blocks, 64, 0, st>>>(m, round, n_pairs, it0, chunk, C, w);
     }
     {
       // grid sized for the first (full) round; later rounds loop over what is left
