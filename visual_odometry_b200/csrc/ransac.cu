@@ -553,6 +553,7 @@ extern "C" int vo_essential_ransac_batch(const double* pts, const int32_t* m, in
       switch (g_solve_minb) {
         case 2: ransac_solve_kernel<2><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
         case 3: ransac_solve_kernel<3><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
+        case 5: ransac_solve_kernel<5><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
         case 6: ransac_solve_kernel<6><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
         case 8: ransac_solve_kernel<8><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
         default: ransac_solve_kernel<4><<<sg, SOLVE_WARPS * 32, 0, st>>>(n_cap, round, n_pairs, it0, chunk, C, w); break;
