@@ -57,6 +57,10 @@ def test_reference_visual_slam_runs_on_compat_modules(compat_path):
     assert isinstance(slam.detector, SiftDetector)
     with pytest.raises(NotImplementedError):
         vs.cv2.SIFT_create(nfeatures=500)
+    # the kNN matcher of src/feature_detection.py:20 (FLANN there) is the exact brute-force one here
+    knn = vs.cv2.DescriptorMatcher_create(vs.cv2.DESCRIPTOR_MATCHER_FLANNBASED)
+    assert isinstance(knn, B200Matcher) and knn.normType == NORM_L2 and not knn.crossCheck
+    assert vs.cv2.DescriptorMatcher_create("BruteForce-Hamming").normType != NORM_L2
     # namedtuples keep the reference's field order
     assert initials.Match._fields == ('featureid1', 'featureid2', 'keypoint1', 'keypoint2',
                                       'descriptor1', 'descriptor2', 'distance', 'color')

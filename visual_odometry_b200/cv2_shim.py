@@ -37,6 +37,22 @@ class _Cv2Namespace:
         return matcher.B200Matcher(matcher.NORM_HAMMING if normType == _real.NORM_HAMMING
                                    else matcher.NORM_L2, crossCheck=crossCheck)
 
+    def DescriptorMatcher_create(self, matcherType):
+        """src/feature_detection.py:20 builds its kNN matcher this way (FLANN, approximate); the
+        B200 path answers with the EXACT brute-force matcher north_star specifies for the ratio
+        test: FLANNBASED and BRUTEFORCE / _L2 -> NORM_L2, BRUTEFORCE_HAMMING -> NORM_HAMMING."""
+        from . import matcher
+        names = {"FlannBased": matcher.NORM_L2, "BruteForce": matcher.NORM_L2,
+                 "BruteForce-Hamming": matcher.NORM_HAMMING}
+        ids = {_real.DESCRIPTOR_MATCHER_FLANNBASED: matcher.NORM_L2,
+               _real.DESCRIPTOR_MATCHER_BRUTEFORCE: matcher.NORM_L2,
+               _real.DESCRIPTOR_MATCHER_BRUTEFORCE_HAMMING: matcher.NORM_HAMMING}
+        norm = names.get(matcherType) if isinstance(matcherType, str) else ids.get(matcherType)
+        if norm is None:
+            raise NotImplementedError("B200 path: DescriptorMatcher_create supports FLANNBASED (as "
+                                      "exact brute force), BRUTEFORCE and BRUTEFORCE_HAMMING")
+        return matcher.B200Matcher(norm, crossCheck=False)
+
     def ORB_create(self, nfeatures=500, scaleFactor=1.2, nlevels=8, edgeThreshold=31, firstLevel=0,
                    WTA_K=2, scoreType=0, patchSize=31, fastThreshold=20):
         if firstLevel != 0 or WTA_K != 2 or scoreType != _real.ORB_HARRIS_SCORE or patchSize != 31:
