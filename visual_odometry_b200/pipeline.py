@@ -73,15 +73,19 @@ class PairPipeline:
         self.q, self.t_idx = e(P, N, dt=I32), e(P, N, dt=I32)
         self.dist = e(P, N, dt=F32)
         self.pts = e(P, N, 4, dt=F64)
-        self.n_match = e(P, dt=I32)
         self.E = e(P, 3, 3, dt=F64)
         self.mask = e(P, N, dt=U8)
-        self.n_inl, self.n_iters, self.status = e(P, dt=I32), e(P, dt=I32), e(P, dt=I32)
-        self.R, self.t = e(P, 3, 3, dt=F64), e(P, 3, dt=F64)
+        self.n_iters = e(P, dt=I32)
+        # what a caller reads back per batch (poses, counts) lies in ONE block so that the
+        # streaming entry brings it to the host with one copy
+        self._res_layout = self._result_layout(P)
+        self._res = e(self._res_layout["bytes"], dt=U8)
+        v = self._result_views(self._res, P)
+        self.R, self.t, self.poses = v["R"], v["t"], v["poses"]
+        self.n_inl, self.n_match, self.status = v["n_inl"], v["n_match"], v["status"]
         self.n_good = e(P, dt=I32)
         self.X = e(P, N, 4, dt=F64) if triangulate else None
         self.n_x = e(P, dt=I32)
-        self.poses = e(P + 1, 4, 4, dt=F64)
         # workspaces
         if descriptor == "orb":
             self.ws_match = e(max(self.lib.vo_match_workspace_bytes(F, P, N), 256), dt=U8)
@@ -94,6 +98,22 @@ class PairPipeline:
         self._copy_stream = None
         # kernels launched per run (for bench.py's gpu_launches claim; see launches_per_run)
         self.launches = 0
+
+    @staticmethod
+    def _result_layout(P):
+        off, out = 0, {}
+        for name, nbytes in (("R", P * 72), ("t", P * 24), ("poses", (P + 1) * 128),
+                             ("n_inl", P * 4), ("n_match", P * 4), ("status", P * 4)):
+            out[name] = (off, nbytes)
+            off += (nbytes + 255) // 256 * 256      # sections stay 256-byte aligned like own allocations
+        out["bytes"] = off
+        return out
+
+    def _result_views(self, raw, P):
+        L = self._res_layout
+        f = lambda n, dt, *shape: raw[L[n][0]:L[n][0] + L[n][1]].view(dt).view(*shape)
+        return dict(R=f("R", F64, P, 3, 3), t=f("t", F64, P, 3), poses=f("poses", F64, P + 1, 4, 4),
+                    n_inl=f("n_inl", I32, P), n_match=f("n_match", I32, P), status=f("status", I32, P))
 
     def _use_slot(self, k):
         while len(self._slots) <= k:
@@ -292,11 +312,10 @@ class PairPipeline:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
         cs = self._copy_stream
         if getattr(self, "_pin_out", None) is None:
-            mk = lambda *s, dt: torch.empty(*s, dtype=dt, pin_memory=True)
-            self._pin_out = [dict(R=mk(self.P, 3, 3, dt=F64), t=mk(self.P, 3, dt=F64),
-                                  n_inl=mk(self.P, dt=I32), n_match=mk(self.P, dt=I32),
-                                  status=mk(self.P, dt=I32), poses=mk(self.P + 1, 4, 4, dt=F64))
-                             for _ in range(2)]
+            self._pin_out = []
+            for _ in range(2):
+                raw = torch.empty(self._res_layout["bytes"], dtype=U8, pin_memory=True)
+                self._pin_out.append(dict(self._result_views(raw, self.P), raw=raw))
         self._use_slot(1)
         self._use_slot(0)
         uploaded = [None, None]       # event: inputs of the batch in this slot are on the device
@@ -341,10 +360,13 @@ class PairPipeline:
             if after_compute is not None:
                 after_compute(k)
             o = self._pin_out[k & 1]
-            for name, src in (("R", self.R), ("t", self.t), ("n_inl", self.n_inl),
-                              ("n_match", self.n_match), ("status", self.status)):
-                o[name][:b].copy_(src[:b], non_blocking=True)
-            o["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
+            if b == self.P:
+                o["raw"].copy_(self._res, non_blocking=True)        # one copy: poses and counts
+            else:
+                for name, src in (("R", self.R), ("t", self.t), ("n_inl", self.n_inl),
+                                  ("n_match", self.n_match), ("status", self.status)):
+                    o[name][:b].copy_(src[:b], non_blocking=True)
+                o["poses"][:b + 1].copy_(self.poses[:b + 1], non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(main)
             done[k & 1] = ev
@@ -356,6 +378,8 @@ class PairPipeline:
         h2d = sum(pin[n][:f].numel() * pin[n].element_size() for n in ("desc", "kp", "nkp")) + \
             pin["pairs"][:b].numel() * 4
         d2h = b * (9 + 3) * 8 + b * 3 * 4 + (b + 1) * 16 * 8
+        if b == self.P:
+            d2h = int(self._res_layout["bytes"])       # the block as copied (sections padded to 256 B)
         return h2d, d2h
 
     def run_host(self, desc, kp, nkp, pairs):
