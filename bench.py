@@ -495,12 +495,20 @@ def run_ours(args, rank, world, local_rank):
             pipe.run_device(B)
             return pipe.poses
         main = torch.cuda.current_stream()
-        if pending:
-            idx, ev = pending.pop()
-            with torch.cuda.stream(side):
-                side.wait_event(ev)
-                gathers[idx].collect()
-        pipe.run_device(B)
+
+        def gather_previous():
+            # the all-gather of step k - 1 starts when THIS step's matching kernel has finished:
+            # it then runs beside the RANSAC / pose kernels, whose grids do not mind a busy SM
+            if pending:
+                idx, ev = pending.pop()
+                evm = torch.cuda.Event()
+                evm.record(main)
+                with torch.cuda.stream(side):
+                    side.wait_event(ev)
+                    side.wait_event(evm)
+                    gathers[idx].collect()
+
+        pipe.run_device(B, after_match=gather_previous)
         g = gathers[k & 1]
         g.pack(pipe.R, pipe.t)
         ev = torch.cuda.Event()
@@ -560,10 +568,24 @@ def run_ours(args, rank, world, local_rank):
     # uploads its frames from pinned memory, runs the chain, downloads poses / counts; the upload
     # of step k+1 overlaps the compute of step k (two device input slots) ----
     done_ev = [None, None]
+    packed = []                      # (buffer set, event after its pack) of the batch not yet gathered
+
+    def gather_packed(after_event=None):
+        # all-gather + chaining + read-back of the last pose on the side stream
+        if packed:
+            idx, ev = packed.pop()
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                if after_event is not None:
+                    side.wait_event(after_event)
+                poses = gathers[idx].collect(time_it=True)
+                last_pose.copy_(poses[-1], non_blocking=True)
+                done_ev[idx] = torch.cuda.Event()
+                done_ev[idx].record(side)
 
     def after(k):
-        # multi-GPU: pack on the compute stream, all-gather + chaining + read-back of the last pose
-        # on the side stream, beside the next batch
+        # multi-GPU: pack batch k's poses on the compute stream; its all-gather is enqueued when
+        # batch k + 1's matching kernel is in the stream (after_match) and starts when it has ended
         if world > 1:
             main = torch.cuda.current_stream()
             g = gathers[k & 1]
@@ -572,18 +594,20 @@ def run_ours(args, rank, world, local_rank):
             g.pack(pipe.R, pipe.t)
             ev = torch.cuda.Event()
             ev.record(main)
-            with torch.cuda.stream(side):
-                side.wait_event(ev)
-                poses = g.collect(time_it=True)
-                last_pose.copy_(poses[-1], non_blocking=True)
-                done_ev[k & 1] = torch.cuda.Event()
-                done_ev[k & 1].record(side)
+            packed.append((k & 1, ev))
+
+    def after_match(k):
+        if world > 1 and packed:
+            evm = torch.cuda.Event()
+            evm.record(torch.cuda.current_stream())
+            gather_packed(evm)
 
     def join_side():
         if world > 1:
+            gather_packed()                              # the last batch: nothing left to wait for
             torch.cuda.current_stream().wait_stream(side)
 
-    pipe.run_stream(N_FRAMES, B, 3, after_compute=after)
+    pipe.run_stream(N_FRAMES, B, 3, after_compute=after, after_match=after_match)
     join_side()
     sync_all()
     if gathers:
@@ -600,7 +624,7 @@ def run_ours(args, rank, world, local_rank):
     h2d_alone_ms = h0.elapsed_time(h1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    h2d, d2h = pipe.run_stream(N_FRAMES, B, args.steps, after_compute=after)
+    h2d, d2h = pipe.run_stream(N_FRAMES, B, args.steps, after_compute=after, after_match=after_match)
     join_side()
     e1.record()
     sync_all()

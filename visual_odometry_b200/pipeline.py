@@ -124,9 +124,13 @@ class PairPipeline:
         self.slot = k
 
     # ------------------------------------------------------------------ device-resident run
-    def run_device(self, n_pairs, stream=None, p0=0, chain=None, slot=None):
+    def run_device(self, n_pairs, stream=None, p0=0, chain=None, slot=None, after_match=None):
         """Inputs already in self.desc/kp/nkp/pairs. Asynchronous; results in the attributes.
-        Processes pairs [p0, p0 + n_pairs) (outputs land in the same rows)."""
+        Processes pairs [p0, p0 + n_pairs) (outputs land in the same rows).  `after_match()` is
+        called once the matching kernels are enqueued: the place to hang work on another stream
+        that must not share the GPU with the persistent matching kernel (multi-GPU: the previous
+        batch's all-gather — an NCCL kernel resident while the matching kernel starts keeps one
+        of its 148 blocks waiting, and with it the kernel's end)."""
         if slot is not None and slot != self.slot:
             self._use_slot(slot)
         lib = self.lib
@@ -146,6 +150,8 @@ class PairPipeline:
                 g(self.desc), g(self.nkp), g(self.kp), N, self.D, self.F, p(self.pairs), B,
                 self.match_mode, self.ratio, p(self.q), p(self.t_idx), p(self.dist), None, None,
                 p(self.pts), p(self.n_match), g(self.ws_match), self.ws_match.numel(), st))
+        if after_match is not None:
+            after_match()
         _lib.check(lib.vo_essential_ransac_batch(
             p(self.pts), p(self.n_match), N, B, g(self.K), self.prob, self.threshold,
             self.max_iters, int(self.adaptive), p(self.E), p(self.mask), p(self.n_inl),
@@ -297,7 +303,8 @@ class PairPipeline:
         return h2d, d2h
 
     # ------------------------------------------------------------------ streamed batches (e2e)
-    def run_stream(self, n_frames, n_pairs, steps, fill=None, consume=None, after_compute=None):
+    def run_stream(self, n_frames, n_pairs, steps, fill=None, consume=None, after_compute=None,
+                   after_match=None):
         """`steps` batches through the whole chain with the upload of batch k+1 running on a copy
         stream while batch k computes (two input slots on the device, two pinned result slots on
         the host).  Every batch: H2D of its frames from the pinned staging area, the chain, D2H of
@@ -305,7 +312,8 @@ class PairPipeline:
         once the previous upload has left them; default: the staged inputs are reused),
         `consume(k, res)` receives batch k's host results (views of a pinned slot, valid until
         batch k+2 is submitted), `after_compute(k)` may enqueue more work on the compute stream
-        (multi-GPU: the pose all-gather).  Returns (h2d_bytes, d2h_bytes) per batch."""
+        (multi-GPU: packing the poses), `after_match(k)` is passed to run_device (multi-GPU: the
+        all-gather of batch k - 1).  Returns (h2d_bytes, d2h_bytes) per batch."""
         pin, f, b = self._pinned(), int(n_frames), int(n_pairs)
         main = torch.cuda.current_stream()
         if self._copy_stream is None:
@@ -353,7 +361,8 @@ class PairPipeline:
             if k + 1 < steps:
                 upload(k + 1)
             main.wait_event(uploaded[k & 1])
-            self.run_device(b, slot=k & 1)
+            self.run_device(b, slot=k & 1,
+                            after_match=(lambda kk=k: after_match(kk)) if after_match is not None else None)
             ev = torch.cuda.Event()
             ev.record(main)
             computed[k & 1] = ev
