@@ -219,3 +219,32 @@ def test_slam_loop_from_images_with_sift(cuda_dev):
     assert sum(bool(e["pnp_ok"]) for e in log[1:]) >= 3, log
     assert log[-1]["n_points"] > log[0]["n_points"] // 2
     assert len(log[-1]["cameras"]) >= 4
+
+
+def test_c_abi_argument_errors(cuda_dev):
+    """vo_sift_detect_batch / vo_sift_workspace_bytes reject what they cannot run (error codes, no
+    exception across the ABI, nothing launched)."""
+    from visual_odometry_b200 import _lib
+    lib = _lib.load()
+    assert lib.vo_sift_workspace_bytes(0, 64, 64, 100) == 0
+    assert lib.vo_sift_workspace_bytes(1, 1, 64, 100) == 0
+    assert lib.vo_sift_octaves(64, 48, None, None) == 5
+    img = torch.zeros((1, 48, 64), dtype=torch.uint8, device=cuda_dev)
+    cap = 64
+    kp = torch.zeros((1, cap, 6), dtype=torch.float32, device=cuda_dev)
+    desc = torch.zeros((1, cap, 128), dtype=torch.uint8, device=cuda_dev)
+    n = torch.zeros(1, dtype=torch.int32, device=cuda_dev)
+    st = torch.zeros(1, dtype=torch.int32, device=cuda_dev)
+    need = lib.vo_sift_workspace_bytes(1, 64, 48, cap)
+    ws = torch.empty(need, dtype=torch.uint8, device=cuda_dev)
+    args = lambda wsb, c=cap, w=64: (_lib.ptr(img), 1, w, 48, c, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
+                                     _lib.ptr(st), None, _lib.ptr(ws), wsb, _lib.cur_stream())
+    assert lib.vo_sift_detect_batch(*args(need)) == 0
+    assert lib.vo_sift_detect_batch(*args(need - 1)) == _lib.VO_ERR_WORKSPACE
+    assert b"workspace" in lib.vo_last_error_string()
+    assert lib.vo_sift_detect_batch(*args(need, c=0)) == _lib.VO_ERR_INVALID_ARG
+    assert lib.vo_sift_detect_batch(*args(need, w=1)) == _lib.VO_ERR_INVALID_ARG
+    assert lib.vo_sift_detect_batch(None, 1, 64, 48, cap, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
+                                    _lib.ptr(st), None, _lib.ptr(ws), need, _lib.cur_stream()) == _lib.VO_ERR_INVALID_ARG
+    torch.cuda.synchronize()
+    assert int(n.item()) == 0 and int(st.item()) == 0
