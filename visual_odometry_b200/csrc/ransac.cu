@@ -244,6 +244,47 @@ __device__ __forceinline__ int sampson_sieve_f32(const float* __restrict__ E, fl
   return -1;
 }
 
+// The same sieve for TWO correspondences at once in packed fp32 (FFMA2 / FMUL2, sm_100): every
+// lane of the pair is rounded exactly like the scalar form above (same nesting of the fused
+// operations), so the decisions are identical; it halves the issue slots of the arithmetic.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ void sampson_sieve_f32x2(const f32x2* __restrict__ E, f32x2 x1, f32x2 y1,
+                                                    f32x2 x2, f32x2 y2, f32x2 t_lo, f32x2 t_hi,
+                                                    int& dec_lo, int& dec_hi) {
+  const f32x2 ex0 = fma2(E[0], x1, fma2(E[1], y1, E[2]));
+  const f32x2 ex1 = fma2(E[3], x1, fma2(E[4], y1, E[5]));
+  const f32x2 ex2 = fma2(E[6], x1, fma2(E[7], y1, E[8]));
+  const f32x2 et0 = fma2(E[0], x2, fma2(E[3], y2, E[6]));
+  const f32x2 et1 = fma2(E[1], x2, fma2(E[4], y2, E[7]));
+  const f32x2 xe = fma2(x2, ex0, fma2(y2, ex1, ex2));
+  const f32x2 den = fma2(ex0, ex0, fma2(ex1, ex1, fma2(et0, et0, mul2(et1, et1))));
+  const f32x2 num = mul2(xe, xe);
+  float n0, n1, l0, l1, h0, h1;
+  unpack2(num, n0, n1);
+  unpack2(mul2(t_lo, den), l0, l1);
+  unpack2(mul2(t_hi, den), h0, h1);
+  dec_lo = n0 < l0 ? 1 : (n0 > h0 ? 0 : -1);
+  dec_hi = n1 < l1 ? 1 : (n1 > h1 ? 0 : -1);
+}
+
 // findEssentialMat: threshold /= (fx+fy)/2 ; findInliers compares with float(thr*thr)
 __device__ __forceinline__ float thr2_from_K(const double* __restrict__ K, double thr_px) {
   const double thr = thr_px / ((K[0] + K[4]) / 2.0);
@@ -261,7 +302,9 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
                     int chunk_stride, const double* __restrict__ K, double thr_px, RansacWs w) {
   __shared__ double Es[SCORE_WARPS][90];
   __shared__ float Ef[SCORE_WARPS][90];
-  __shared__ float4 tile[SCORE_TILE];
+  // correspondences i and i + 32 of every group of 64 side by side: one 8-byte load per coordinate
+  // yields the packed pair the FFMA2 sieve works on
+  __shared__ float2 tx1[SCORE_TILE / 2], ty1[SCORE_TILE / 2], tx2[SCORE_TILE / 2], ty2[SCORE_TILE / 2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_act = w.n_active[round];
   const int32_t* list = w.active + (size_t)(round & 1) * n_pairs;
@@ -283,25 +326,33 @@ ransac_score_kernel(const int32_t* __restrict__ m, int n_cap, int round, int n_p
     for (int t0 = 0; t0 < mp; t0 += SCORE_TILE) {
       const int tn = mp - t0 < SCORE_TILE ? mp - t0 : SCORE_TILE;
       __syncthreads();                       // the previous tile (or item) is no longer read
-      for (int i = threadIdx.x; i < tn; i += SCORE_WARPS * 32) {
-        const double4 v = ldg_d4(pts + t0 + i);
-        tile[i] = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+      for (int i = threadIdx.x; i < ((tn + 63) & ~63); i += SCORE_WARPS * 32) {
+        double4 v = make_double4(0, 0, 0, 0);
+        if (i < tn) v = ldg_d4(pts + t0 + i);
+        const int j = (i >> 6) * 32 + (i & 31), half = (i >> 5) & 1;
+        reinterpret_cast<float*>(&tx1[j])[half] = (float)v.x;
+        reinterpret_cast<float*>(&ty1[j])[half] = (float)v.y;
+        reinterpret_cast<float*>(&tx2[j])[half] = (float)v.z;
+        reinterpret_cast<float*>(&ty2[j])[half] = (float)v.w;
       }
       __syncthreads();
+      const f32x2 tlo2 = pack2(tf_lo, tf_lo), thi2 = pack2(tf_hi, tf_hi);
       for (int k = 0; k < nm; ++k) {
-        float e[9];
+        f32x2 e[9];
 #pragma unroll
-        for (int q = 0; q < 9; ++q) e[q] = Ef[warp][9 * k + q];
+        for (int q = 0; q < 9; ++q) { const float c = Ef[warp][9 * k + q]; e[q] = pack2(c, c); }
         int local = 0;
-        // two correspondences per trip (independent FMA chains); the fp64 decision of the rare
-        // undecided ones sits behind one branch per trip
+        // two correspondences per trip in packed fp32; the fp64 decision of the rare undecided
+        // ones sits behind one branch per trip
         for (int i = lane; i < tn; i += 64) {
           const int i2 = i + 32;
           const bool has2 = i2 < tn;
-          const float4 f = tile[i];
-          const float4 g = tile[has2 ? i2 : i];
-          int dec = sampson_sieve_f32(e, f.x, f.y, f.z, f.w, tf_lo, tf_hi);
-          int dec2 = has2 ? sampson_sieve_f32(e, g.x, g.y, g.z, g.w, tf_lo, tf_hi) : 0;
+          const int j = (i >> 6) * 32 + lane;
+          int dec, dec2;
+          sampson_sieve_f32x2(e, *reinterpret_cast<const f32x2*>(&tx1[j]), *reinterpret_cast<const f32x2*>(&ty1[j]),
+                              *reinterpret_cast<const f32x2*>(&tx2[j]), *reinterpret_cast<const f32x2*>(&ty2[j]),
+                              tlo2, thi2, dec, dec2);
+          if (!has2) dec2 = 0;
           if ((dec | dec2) < 0) {
             if (dec < 0) {
               const double4 v = ldg_d4(pts + t0 + i);
