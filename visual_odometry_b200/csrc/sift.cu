@@ -134,6 +134,27 @@ __global__ void upsample_kernel(const uint8_t* __restrict__ img, int h, int w, f
   out[(size_t)f * out_stride + (size_t)y * 2 * w + x] = r0 * (1.f - ay) + r1 * ay;
 }
 
+// packed fp32 (sm_100: FFMA2 / FMUL2): two independent IEEE operations per instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
 // ------------------------------------------------------------------ S2: separable Gaussian blur
 // One block = a 64 x 32 output tile: the row pass of the tile's rows plus r halo rows goes to
 // shared memory, the column pass reads it.  Operation order = cv2's (see oracle/cv_sift.py blur):
@@ -150,8 +171,11 @@ __global__ void __launch_bounds__(256)
 blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w, long long stride,
             Kernels K, int ki) {
   constexpr int ROWS = TH + 2 * R, COLS = TW + 2 * R, IS = COLS | 1, RS = TW + 1;
-  __shared__ float in[ROWS][IS];
+  // rows 2p and 2p + 1 of the staged tile side by side: one 8-byte load is the operand pair of a
+  // packed fp32 operation (FFMA2) that filters both rows at once
+  __shared__ float2 in2[ROWS / 2][IS];
   __shared__ float rowp[ROWS][RS];
+#define SIFT_IN(ry, cx) (reinterpret_cast<float*>(&in2[(ry) >> 1][cx])[(ry) & 1])
   __shared__ float fk[2 * R + 1];
   const int tid = threadIdx.x;
   if (tid <= 2 * R) fk[tid] = K.f[ki][tid];
@@ -172,7 +196,7 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
         const int cx = lane + 32 * it;
         if (cx < COLS) {
           const int x = inside ? x0 - R + cx : reflect_once(x0 - R + cx, w);
-          cp_async4(&in[ry][cx], line + x);
+          cp_async4(&SIFT_IN(ry, cx), line + x);
         }
       }
     }
@@ -180,22 +204,31 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
   }
   __syncthreads();
   if (!tails) {
-    for (int task = tid; task < 8 * 64; task += 256) {
-      const int g = task >> 6, row = task & 63;
-      if (row >= ROWS) continue;
-      float win[8 + 2 * R], acc[8];
+    {
+      // row pass: warp g = columns 8g .. 8g + 7, lane = row pair; both rows of a pair go through
+      // the same packed multiply-adds (each half rounds like the scalar operation)
+      const int g = tid >> 5, rp = tid & 31;
+      if (rp < ROWS / 2) {
+        f32x2 win[8 + 2 * R], acc[8];
 #pragma unroll
-      for (int m = 0; m < 8 + 2 * R; ++m) win[m] = in[row][8 * g + m];
+        for (int m = 0; m < 8 + 2 * R; ++m) win[m] = *reinterpret_cast<const f32x2*>(&in2[rp][8 * g + m]);
+        const f32x2 f0 = pack2(fk[0], fk[0]);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = __fmul_rn(win[j], fk[0]);
+        for (int j = 0; j < 8; ++j) acc[j] = mul2(win[j], f0);
 #pragma unroll
-      for (int k = 1; k <= 2 * R; ++k) {
-        const float f = fk[k];
+        for (int k = 1; k <= 2 * R; ++k) {
+          const f32x2 f = pack2(fk[k], fk[k]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = __fmaf_rn(win[j + k], f, acc[j]);
+          for (int j = 0; j < 8; ++j) acc[j] = fma2(win[j + k], f, acc[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float lo, hi;
+          unpack2(acc[j], lo, hi);
+          rowp[2 * rp][8 * g + j] = lo;
+          rowp[2 * rp + 1][8 * g + j] = hi;
+        }
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) rowp[row][8 * g + j] = acc[j];
     }
     __syncthreads();
     const int col = tid & 63, q = tid >> 6;
@@ -224,12 +257,11 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
     const int ry = i / TW, cx = i % TW;
     const int x = x0 + cx;
     if (x >= w) continue;
-    const float* p = &in[ry][cx];
-    float acc = __fmul_rn(p[0], fk[0]);
+    float acc = __fmul_rn(SIFT_IN(ry, cx), fk[0]);
     if (x < row_tail) {
-      for (int k = 1; k <= 2 * R; ++k) acc = __fmaf_rn(p[k], fk[k], acc);
+      for (int k = 1; k <= 2 * R; ++k) acc = __fmaf_rn(SIFT_IN(ry, cx + k), fk[k], acc);
     } else {
-      for (int k = 1; k <= 2 * R; ++k) acc = __fadd_rn(__fmul_rn(p[k], fk[k]), acc);
+      for (int k = 1; k <= 2 * R; ++k) acc = __fadd_rn(__fmul_rn(SIFT_IN(ry, cx + k), fk[k]), acc);
     }
     rowp[ry][cx] = acc;
   }
@@ -249,6 +281,8 @@ blur_kernel(const float* __restrict__ src, float* __restrict__ dst, int h, int w
     d[(size_t)y * w + x] = acc;
   }
 }
+
+#undef SIFT_IN
 
 static int launch_blur(const float* src, float* dst, int h, int w, long long stride, const Kernels& K,
                        int ki, int n_frames, cudaStream_t st) {
