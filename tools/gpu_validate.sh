@@ -25,9 +25,10 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --lo
 if [ "$1" = "full" ]; then
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:describe_kernel -c 1 -s 1 -o gpurun_out/sift_describe_full -f python tools/gpu_sift_bench.py 480 640 32 1 > gpurun_out/ncu_sift_describe.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:blur_kernel -c 1 -s 46 -o gpurun_out/sift_blur_full -f python tools/gpu_sift_bench.py 480 640 32 1 > gpurun_out/ncu_sift_blur.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 3 -c 1 -o gpurun_out/k1t_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1t.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 40 -c 1 -o gpurun_out/k6i_full python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 3 -c 1 -o gpurun_out/k1t_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1t.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 40 -c 1 -o gpurun_out/k6i_full -f python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_score -s 12 -c 1 -o gpurun_out/k2_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
 fi
 ls -la gpurun_out | head -60
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; head -c 3000 gpurun_out/bench.json
