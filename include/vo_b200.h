@@ -307,8 +307,10 @@ int vo_orb_fast_score_map(const uint8_t* images, int n_frames, int width, int he
 /* ---- N4: SIFT extraction, replaces `cv2.SIFT_create()` (/root/reference/src/visual_slam.py:17,
  * src/image_and_keypoints.py:12) + `detectAndCompute(image, None)` (src/frame_generator.py:25,
  * src/image_and_keypoints.py:46) for a batch of equally sized gray frames, with cv2's default
- * parameters (nfeatures 0 = all key points, 3 octave layers, contrast 0.04, edge 10, sigma 1.6,
- * image doubled).  images uint8 [n_frames, height, width] on the device.
+ * parameters (3 octave layers, contrast 0.04, edge 10, sigma 1.6, image doubled) and cv2's
+ * `nfeatures` (0 = all key points; n > 0 = KeyPointsFilter::retainBest: every key point whose
+ * response is >= the n-th largest one, ties kept — cv2 leaves those in std::nth_element's order,
+ * here they stay in the sorted order, so the two are equal as sets).  images uint8 [n_frames, height, width] on the device.
  * kp float32 [n_frames, cap, 6] = (x, y, size, angle, response, octave word — the int cv2 packs
  * octave / layer / sub-layer into, < 2^24 so exact as float), in cv2's output order
  * (KeyPoint12_LessThan, duplicates removed); desc uint8 [n_frames, cap, 128] (cv2 returns the same
@@ -320,7 +322,7 @@ int vo_orb_fast_score_map(const uint8_t* images, int n_frames, int width, int he
 int vo_sift_octaves(int width, int height, int32_t* w_h, int32_t* h_h);
 size_t vo_sift_workspace_bytes(int n_frames, int width, int height, int cap);
 int vo_sift_detect_batch(const uint8_t* images, int n_frames, int width, int height, int cap,
-                         float* kp, uint8_t* desc, int32_t* n_out, int32_t* status,
+                         int nfeatures, float* kp, uint8_t* desc, int32_t* n_out, int32_t* status,
                          float* pyramid_out, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- measurement hooks (bench.py): CUDA-event timing of the dominant kernel on its own stream,

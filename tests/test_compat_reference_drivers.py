@@ -55,8 +55,9 @@ def test_reference_visual_slam_runs_on_compat_modules(compat_path):
         vs.cv2.ORB_create(WTA_K=3)
     from visual_odometry_b200.sift import SiftDetector
     assert isinstance(slam.detector, SiftDetector)
+    assert vs.cv2.SIFT_create(nfeatures=500).nfeatures == 500
     with pytest.raises(NotImplementedError):
-        vs.cv2.SIFT_create(nfeatures=500)
+        vs.cv2.SIFT_create(contrastThreshold=0.02)
     # the kNN matcher of src/feature_detection.py:20 (FLANN there) is the exact brute-force one here
     knn = vs.cv2.DescriptorMatcher_create(vs.cv2.DESCRIPTOR_MATCHER_FLANNBASED)
     assert isinstance(knn, B200Matcher) and knn.normType == NORM_L2 and not knn.crossCheck

@@ -152,7 +152,7 @@ def test_capacity_overflow_is_reported_and_detect_and_compute_retries(cuda_dev):
     assert desc.dtype == np.float32 and desc.shape == (len(kps), 128)
     check(mine, desc, ref, rdesc)
     with pytest.raises(NotImplementedError):
-        SiftDetector(nfeatures=100)
+        SiftDetector(nOctaveLayers=4)
 
 
 def test_images_to_matches_through_the_reference_surface(cuda_dev):
@@ -237,14 +237,41 @@ def test_c_abi_argument_errors(cuda_dev):
     st = torch.zeros(1, dtype=torch.int32, device=cuda_dev)
     need = lib.vo_sift_workspace_bytes(1, 64, 48, cap)
     ws = torch.empty(need, dtype=torch.uint8, device=cuda_dev)
-    args = lambda wsb, c=cap, w=64: (_lib.ptr(img), 1, w, 48, c, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
+    args = lambda wsb, c=cap, w=64, nf=0: (_lib.ptr(img), 1, w, 48, c, nf, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
                                      _lib.ptr(st), None, _lib.ptr(ws), wsb, _lib.cur_stream())
     assert lib.vo_sift_detect_batch(*args(need)) == 0
     assert lib.vo_sift_detect_batch(*args(need - 1)) == _lib.VO_ERR_WORKSPACE
     assert b"workspace" in lib.vo_last_error_string()
     assert lib.vo_sift_detect_batch(*args(need, c=0)) == _lib.VO_ERR_INVALID_ARG
     assert lib.vo_sift_detect_batch(*args(need, w=1)) == _lib.VO_ERR_INVALID_ARG
-    assert lib.vo_sift_detect_batch(None, 1, 64, 48, cap, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
+    assert lib.vo_sift_detect_batch(*args(need, nf=-1)) == _lib.VO_ERR_INVALID_ARG
+    assert lib.vo_sift_detect_batch(None, 1, 64, 48, cap, 0, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
                                     _lib.ptr(st), None, _lib.ptr(ws), need, _lib.cur_stream()) == _lib.VO_ERR_INVALID_ARG
     torch.cuda.synchronize()
     assert int(n.item()) == 0 and int(st.item()) == 0
+
+
+@pytest.mark.parametrize("nfeatures", [1, 50, 300, 100000])
+def test_nfeatures_equals_cv2_retain_best_as_a_set(cuda_dev, nfeatures):
+    """cv2.SIFT_create(nfeatures): KeyPointsFilter::retainBest keeps every key point whose response
+    is >= the n-th largest one (ties kept) and leaves them in std::nth_element's order; here they
+    stay in the sorted order: equal as sets, descriptors row by row."""
+    cv2 = pytest.importorskip("cv2")
+    img = synth.textured_image(300, 400, 77)
+    kps, rdesc = cv2.SIFT_create(nfeatures=nfeatures).detectAndCompute(img, None)
+    ref = np.array([(k.pt[0], k.pt[1], k.size, k.angle, k.response, k.octave) for k in kps],
+                   np.float64).reshape(-1, 6)
+    res, status, _ = run(SiftDetector(nfeatures=nfeatures), img[None])
+    assert status[0] == 0
+    kp, desc = res[0]
+    assert len(kp) == len(ref) and (nfeatures > 1000 or len(kp) <= nfeatures + 3)
+    # pair as sets: sort both by (x, y, size, angle)
+    oa = np.lexsort((kp[:, 3], kp[:, 2], kp[:, 1], kp[:, 0]))
+    ob = np.lexsort((ref[:, 3], ref[:, 2], ref[:, 1], ref[:, 0]))
+    d = np.abs(kp[oa][:, :5] - ref[ob][:, :5])
+    assert d[:, :2].max() <= 2e-3 and d[:, 2].max() <= 1e-3 and d[:, 4].max() <= 1e-6
+    assert np.array_equal(kp[oa][:, 5], ref[ob][:, 5])
+    dd = np.abs(desc[oa].astype(np.int32) - rdesc[ob].astype(np.int32))
+    assert dd.max() <= 1 and (dd > 0).mean() <= 0.01
+    # and the survivors are in cv2's sorted order among themselves
+    assert np.all(np.diff(kp[:, 0]) >= 0)

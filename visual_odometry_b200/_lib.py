@@ -63,7 +63,7 @@ SIGNATURES = {
     "vo_measure_popc_peak": (_i, [_p, _p]),
     "vo_sift_octaves": (_i, [_i, _i, _p, _p]),
     "vo_sift_workspace_bytes": (_sz, [_i, _i, _i, _i]),
-    "vo_sift_detect_batch": (_i, [_p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vo_sift_detect_batch": (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_host_alloc": (_i, [_p, _sz, _i]),
     "vo_host_free": (_i, [_p]),
     "vo_pnp_workspace_bytes": (_sz, [_i, _i]),

@@ -627,29 +627,71 @@ rank_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restrict_
   }
 }
 
-// removeDuplicatedSorted (equal x, y, size, angle as the predecessor), then the firstOctave = -1
-// correction: octave byte - 1, point and size halved.  One block per frame.
+// removeDuplicatedSorted (equal x, y, size, angle as the predecessor), KeyPointsFilter::retainBest
+// for nfeatures > 0 (everything whose response is >= the nfeatures-th largest one, ties kept: a
+// radix select over the response bits), then the firstOctave = -1 correction: octave byte - 1,
+// point and size halved.  One block per frame.
+__device__ __forceinline__ bool sift_not_duplicate(const float* __restrict__ s, int i) {
+  if (i == 0) return true;
+  const float* a = s + (size_t)(i - 1) * KP_WORDS;
+  const float* b = s + (size_t)i * KP_WORDS;
+  return !(a[0] == b[0] && a[1] == b[1] && a[2] == b[2] && a[3] == b[3]);
+}
+
 __global__ void __launch_bounds__(256)
-finalize_kernel(int cap, const int32_t* __restrict__ n_raw, const float* __restrict__ sorted,
-                float* __restrict__ kp, int32_t* __restrict__ n_out) {
+finalize_kernel(int cap, int nfeatures, const int32_t* __restrict__ n_raw,
+                const float* __restrict__ sorted, float* __restrict__ kp, int32_t* __restrict__ n_out) {
   const int f = blockIdx.x;
   const int n = n_raw[f] < cap ? n_raw[f] : cap;
   const float* s = sorted + (size_t)f * cap * KP_WORDS;
   __shared__ int warp_sums[8];
   __shared__ int carry;
+  __shared__ int hist[256];
+  __shared__ unsigned sel_prefix, sel_mask;
+  __shared__ int sel_want;
+  unsigned thr_bits = 0u;                      // responses are >= 0: their bit patterns order them
+  if (nfeatures > 0) {
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int i = threadIdx.x; i < n; i += 256) mine += sift_not_duplicate(s, i) ? 1 : 0;
+    atomicAdd(&carry, mine);
+    __syncthreads();
+    const int n_unique = carry;
+    __syncthreads();
+    if (n_unique > nfeatures) {
+      if (threadIdx.x == 0) { sel_prefix = 0u; sel_mask = 0u; sel_want = nfeatures; }
+      for (int shift = 24; shift >= 0; shift -= 8) {
+        hist[threadIdx.x] = 0;
+        __syncthreads();
+        const unsigned prefix = sel_prefix, mask = sel_mask;
+        for (int i = threadIdx.x; i < n; i += 256) {
+          const unsigned bits = (unsigned)__float_as_int(s[(size_t)i * KP_WORDS + 4]);
+          if ((bits & mask) == prefix && sift_not_duplicate(s, i)) atomicAdd(&hist[(bits >> shift) & 255u], 1);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          int want = sel_want, b = 255;
+          for (; b > 0; --b) {
+            if (hist[b] >= want) break;
+            want -= hist[b];
+          }
+          sel_want = want;
+          sel_prefix = prefix | ((unsigned)b << shift);
+          sel_mask = mask | (255u << shift);
+        }
+        __syncthreads();
+      }
+      thr_bits = sel_prefix;
+    }
+  }
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   for (int i0 = 0; i0 < n; i0 += 256) {
     const int i = i0 + threadIdx.x;
     int keep = 0;
-    if (i < n) {
-      keep = 1;
-      if (i > 0) {
-        const float* a = s + (size_t)(i - 1) * KP_WORDS;
-        const float* b = s + (size_t)i * KP_WORDS;
-        if (a[0] == b[0] && a[1] == b[1] && a[2] == b[2] && a[3] == b[3]) keep = 0;
-      }
-    }
+    if (i < n)
+      keep = sift_not_duplicate(s, i) && (unsigned)__float_as_int(s[(size_t)i * KP_WORDS + 4]) >= thr_bits;
     const unsigned ball = __ballot_sync(0xffffffffu, keep);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (lane == 0) warp_sums[wid] = __popc(ball);
@@ -898,7 +940,7 @@ extern "C" size_t vo_sift_workspace_bytes(int n_frames, int width, int height, i
 }
 
 extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int width, int height,
-                                    int cap, float* kp, uint8_t* desc, int32_t* n_out,
+                                    int cap, int nfeatures, float* kp, uint8_t* desc, int32_t* n_out,
                                     int32_t* status, float* pyramid_out, void* ws, size_t ws_bytes,
                                     void* stream) {
   VO_REQUIRE(images && kp && desc && n_out && status && ws, VO_ERR_INVALID_ARG,
@@ -906,6 +948,7 @@ extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int wid
   VO_REQUIRE(n_frames >= 1 && cap >= 1 && width >= 2 && height >= 2, VO_ERR_INVALID_ARG,
              "vo_sift_detect_batch: bad sizes (%d frames, %d x %d, cap %d)", n_frames, width, height, cap);
   VO_REQUIRE(n_frames <= 65535, VO_ERR_INVALID_ARG, "vo_sift_detect_batch: at most 65535 frames per call");
+  VO_REQUIRE(nfeatures >= 0, VO_ERR_INVALID_ARG, "vo_sift_detect_batch: nfeatures %d < 0", nfeatures);
   Geom G;
   VO_REQUIRE(make_geom(width, height, &G) == 0, VO_ERR_INVALID_ARG,
              "vo_sift_detect_batch: image size %d x %d gives no valid octave count", width, height);
@@ -954,7 +997,7 @@ extern "C" int vo_sift_detect_batch(const uint8_t* images, int n_frames, int wid
     orient_kernel<<<dim3(bx, F), 64, 0, st>>>(w.pyr, G, cap, w.n_cand, w.cand, w.n_raw, w.raw, status);
     rank_kernel<<<dim3((cap + 255) / 256 < 16 ? (cap + 255) / 256 : 16, F), 256, 0, st>>>(cap, w.n_raw, w.raw,
                                                                                          w.sorted);
-    finalize_kernel<<<F, 256, 0, st>>>(cap, w.n_raw, w.sorted, kp, n_out);
+    finalize_kernel<<<F, 256, 0, st>>>(cap, nfeatures, w.n_raw, w.sorted, kp, n_out);
   }
   {
     vo::ProfScope prof(12, st);

@@ -65,7 +65,8 @@ class _Cv2Namespace:
                     sigma=1.6, *a, **k):
         """the live detector of src/visual_slam.py:17 / src/image_and_keypoints.py:12"""
         if a or k:
-            raise NotImplementedError("B200 path: SIFT with cv2.SIFT_create()'s default parameters only")
+            raise NotImplementedError("B200 path: SIFT_create(nfeatures, nOctaveLayers, contrastThreshold, "
+                                      "edgeThreshold, sigma) only")
         from . import sift
         return sift.SiftDetector(nfeatures, nOctaveLayers, contrastThreshold, edgeThreshold, sigma)
 

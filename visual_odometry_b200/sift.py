@@ -3,8 +3,8 @@ uses: `cv2.SIFT_create()` (src/visual_slam.py:17, src/image_and_keypoints.py:12)
 `self.detector.detectAndCompute(frame.image, None)` (src/frame_generator.py:25,
 src/image_and_keypoints.py:46).
 
-`SiftDetector()` mirrors `cv2.SIFT_create()` with its default parameters (nfeatures 0,
-nOctaveLayers 3, contrastThreshold 0.04, edgeThreshold 10, sigma 1.6); pass it to FrameGenerator
+`SiftDetector(nfeatures=0)` mirrors `cv2.SIFT_create(nfeatures)` with its default nOctaveLayers 3,
+contrastThreshold 0.04, edgeThreshold 10, sigma 1.6; pass it to FrameGenerator
 in place of the cv2 detector.  `detect_batch` takes all frames of a sequence at once and leaves
 key points and descriptors on the device in the layout the L2 matcher reads (desc uint8
 [F, cap, 128] — cv2's float32 descriptors hold exactly these integers —, kp float32 [F, cap, 6]).
@@ -25,10 +25,11 @@ U8, I32, F32 = torch.uint8, torch.int32, torch.float32
 class SiftDetector:
     def __init__(self, nfeatures=0, nOctaveLayers=3, contrastThreshold=0.04, edgeThreshold=10,
                  sigma=1.6, device="cuda", cap=8192):
-        if (int(nfeatures), int(nOctaveLayers), float(contrastThreshold), float(edgeThreshold),
-                float(sigma)) != (0, 3, 0.04, 10.0, 1.6):
-            raise NotImplementedError("SiftDetector: only cv2.SIFT_create()'s default parameters "
-                                      "(the reference uses no others)")
+        if (int(nOctaveLayers), float(contrastThreshold), float(edgeThreshold),
+                float(sigma)) != (3, 0.04, 10.0, 1.6) or int(nfeatures) < 0:
+            raise NotImplementedError("SiftDetector: cv2.SIFT_create()'s default nOctaveLayers, "
+                                      "thresholds and sigma only (the reference uses no others)")
+        self.nfeatures = int(nfeatures)       # 0 = all; n > 0 = retainBest (response >= n-th largest)
         self.device = torch.device(device)
         self.cap = int(cap)
         self._ws = None
@@ -74,7 +75,7 @@ class SiftDetector:
             pyr = torch.empty((F, floats), dtype=F32, device=self.device)
         with torch.cuda.device(self.device):
             _lib.check(lib.vo_sift_detect_batch(
-                _lib.ptr(images), F, W, H, cap, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
+                _lib.ptr(images), F, W, H, cap, self.nfeatures, _lib.ptr(kp), _lib.ptr(desc), _lib.ptr(n),
                 _lib.ptr(status), _lib.ptr(pyr), _lib.ptr(self._ws), wsb, _lib.cur_stream()))
         out = dict(kp=kp, desc=desc, n=n, status=status, cap=cap)
         if with_pyramid:
