@@ -57,6 +57,11 @@ int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float*
                            int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                            double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 int vo_debug_hamming(int flags);
+/* debug: raw fp32 accumulator of the fp4 kernel (csrc/hamming_f4.cuh) for the pair pairs[0..1] of
+ * desc uint8 [2, n_cap, 32]: acc float32 [128, 240] = rows 0..127 x columns 0..239,
+ * 36 * (256 - 2 * Hamming) + (239 - column) / 4 when the contraction is right */
+int vo_debug_hamming_f4_acc(const uint8_t* desc, const int32_t* nkp, int n_cap, const int32_t* pairs,
+                            float* acc, void* ws, size_t ws_bytes, void* stream);
 /* single pair convenience: d1 [n1,32], d2 [n2,32]; outputs sized n1 */
 int vo_match_hamming(const uint8_t* d1, int n1, const uint8_t* d2, int n2, int mode, double ratio,
                      int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,

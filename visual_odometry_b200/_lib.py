@@ -38,6 +38,7 @@ SIGNATURES = {
     "vo_match_hamming_batch": (_i, [_p, _p, _p, _i, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p,
                                     _p, _p, _sz, _p]),
     "vo_debug_hamming": (_i, [_i]),
+    "vo_debug_hamming_f4_acc": (_i, [_p, _p, _i, _p, _p, _p, _sz, _p]),
     "vo_match_hamming": (_i, [_p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vo_match_hamming_static_max_keypoints": (_i, []),
     "vo_match_hamming_static": (_i, [_p, _i, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _p]),

@@ -14,6 +14,7 @@
 // column, so forward NN, second NN and backward NN all come out of ONE pass (cv2 does two).
 #include "common.cuh"
 #include "hamming_tc.cuh"
+#include "hamming_f4.cuh"
 
 namespace vo {
 
@@ -296,6 +297,7 @@ static size_t popc_workspace_bytes(int n_pairs, int n_cap) {
 // bits 0..1: 0 = choose by batch size, 1 = always the popc kernel, 2 = always the tensor-core
 // kernel (needs n_frames > 0); bits 3..4: timing-experiment instantiations of the tensor kernel
 static int g_hamming_debug = 0;
+static int g_hamming_tensor_default = 2;   // 2 = K1t (int8), 3 = K1f (fp4)
 extern "C" int vo_debug_hamming(int flags) {
   g_hamming_debug = flags;
   return VO_OK;
@@ -314,19 +316,20 @@ static int device_sms() {
 
 // The tensor-core path pays a per-frame operand expansion and works in (pair, direction, 256-row
 // block) items of ~10 us each: worth it once the items give every SM something to do.
-static bool use_tensor_path(int n_frames, int n_pairs, int n_cap, int mode) {
+static int use_tensor_path(int n_frames, int n_pairs, int n_cap, int mode) {
   const int path = g_hamming_debug & 3;
-  if (n_frames <= 0 || path == 1) return false;
-  if (path == 2) return true;
+  if (n_frames <= 0 || path == 1) return 0;
+  if (path >= 2) return path;
   const long items = (long)n_pairs * (mode == VO_MATCH_MUTUAL ? 2 : 1) * ((n_cap + htc::ROWS - 1) / htc::ROWS);
-  return n_cap >= 512 && items >= device_sms() / 2;
+  return (n_cap >= 512 && items >= device_sms() / 2) ? g_hamming_tensor_default : 0;
 }
 
 extern "C" size_t vo_match_workspace_bytes(int n_frames, int n_pairs, int n_cap) {
   if (n_pairs <= 0 || n_cap <= 0) return 0;
   const size_t a = popc_workspace_bytes(n_pairs, n_cap);
   const size_t b = n_frames > 0 ? htc::carve(nullptr, n_frames, n_pairs, n_cap).bytes : 0;
-  return a > b ? a : b;
+  const size_t c = n_frames > 0 ? hf4::carve(nullptr, n_frames, n_pairs, n_cap).bytes : 0;
+  return a > b ? (a > c ? a : c) : (b > c ? b : c);
 }
 
 // Train-range splits serve two purposes: filling the SMs when there are few (pair, query tile)
@@ -461,6 +464,87 @@ static int launch_hamming_tc(const uint8_t* desc, const int32_t* nkp, const floa
   return check_launch("vo_match_hamming_batch(tensor)");
 }
 
+// fp4 tensor-core path (K1f): both operand forms of every frame once, then as K1t
+static int launch_hamming_f4(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
+                             int n_frames, const int32_t* pairs, int n_pairs, int mode, double ratio,
+                             int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
+                             double* pts, int32_t* n_out, void* ws, cudaStream_t st, float* probe_acc) {
+  const int nta = (n_cap + hf4::ROWS_A - 1) / hf4::ROWS_A, ntb = (n_cap + hf4::ROWS_B - 1) / hf4::ROWS_B;
+  const hf4::Ws w = hf4::carve(ws, n_frames, n_pairs, n_cap);
+  const int smem = (int)sizeof(hf4::Smem) + 1024;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!attr_set[dev]) {
+    if (cudaFuncSetAttribute(hf4::match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<false, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+        cudaFuncSetAttribute(hf4::match_kernel<false, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+      return check_launch("vo_match_hamming_batch(smem attribute, fp4)");
+    attr_set[dev] = true;
+  }
+  {
+    ProfScope prof(4, st);
+    const int rows = nta * hf4::ROWS_A > ntb * hf4::ROWS_B ? nta * hf4::ROWS_A : ntb * hf4::ROWS_B;
+    hf4::expand_kernel<<<dim3((rows + 255) / 256, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nta, ntb,
+                                                                           w.tiles_a, w.tiles_b);
+  }
+  const int ndir = mode == VO_MATCH_MUTUAL ? 2 : 1;
+  const long n_items = (long)n_pairs * ndir * nta;
+  const int grid = (int)(n_items < device_sms() ? n_items : device_sms());
+  {
+    ProfScope prof(0, st);
+    if (probe_acc)
+      hf4::match_kernel<false, true><<<1, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                    ntb, 1, 1, w.rowbest, w.colmin, probe_acc);
+    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 1)
+      hf4::match_kernel<false, false, 1><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 2)
+      hf4::match_kernel<false, false, 2><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 3)
+      hf4::match_kernel<false, false, 3><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 4)
+      hf4::match_kernel<false, false, 4><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else if (mode == VO_MATCH_MUTUAL)
+      hf4::match_kernel<false><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                                ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else
+      hf4::match_kernel<true><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
+                                                               ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+  }
+  if (probe_acc) return check_launch("vo_debug_hamming_f4_acc");
+  for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
+    const int np = n_pairs - p0 < 65535 ? n_pairs - p0 : 65535;
+    const size_t ob = (size_t)p0 * n_cap;
+    ProfScope prof_c(8, st);
+    match_compact_kernel<<<np, CP_THREADS, 0, st>>>(
+        w.rowbest + ob * 2, w.colmin + ob, nkp, kp, n_cap, pairs + 2 * p0, 0, 0, 1, mode, ratio, q + ob,
+        t + ob, dist + ob, t2 ? t2 + ob : nullptr, dist2 ? dist2 + ob : nullptr,
+        pts ? pts + ob * 4 : nullptr, n_out + p0);
+  }
+  return check_launch("vo_match_hamming_batch(fp4 tensor)");
+}
+
+// debug: the raw fp32 accumulator of K1f for frames (0, 1) of `desc`, rows 0..127 x columns 0..239:
+// acc[i][j] = 36 * (256 - 2 * Hamming(i, j)) + (239 - j) / 4 when the contraction is right
+extern "C" int vo_debug_hamming_f4_acc(const uint8_t* desc, const int32_t* nkp, int n_cap,
+                                       const int32_t* pairs, float* acc, void* ws, size_t ws_bytes,
+                                       void* stream) {
+  VO_REQUIRE(desc && nkp && pairs && acc && ws, VO_ERR_INVALID_ARG, "vo_debug_hamming_f4_acc: null pointer");
+  VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(2, 1, n_cap), VO_ERR_WORKSPACE,
+             "vo_debug_hamming_f4_acc: workspace too small");
+  return launch_hamming_f4(desc, nkp, nullptr, n_cap, 2, pairs, 1, VO_MATCH_MUTUAL, 0.0, nullptr, nullptr,
+                           nullptr, nullptr, nullptr, nullptr, nullptr, ws, (cudaStream_t)stream, acc);
+}
+
 extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp,
                                       int n_cap, int n_frames, const int32_t* pairs, int n_pairs,
                                       int mode, double ratio, int32_t* q, int32_t* t, float* dist,
@@ -475,7 +559,11 @@ extern "C" int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, c
   VO_REQUIRE(ws_bytes >= vo_match_workspace_bytes(n_frames, n_pairs, n_cap), VO_ERR_WORKSPACE,
              "vo_match_hamming_batch: workspace too small");
   if (n_pairs == 0) return VO_OK;
-  if (use_tensor_path(n_frames, n_pairs, n_cap, mode))
+  const int path = use_tensor_path(n_frames, n_pairs, n_cap, mode);
+  if (path == 3)
+    return launch_hamming_f4(desc, nkp, kp, n_cap, n_frames, pairs, n_pairs, mode, ratio, q, t, dist,
+                             t2, dist2, pts, n_out, ws, (cudaStream_t)stream, nullptr);
+  if (path == 2)
     return launch_hamming_tc(desc, nkp, kp, n_cap, n_frames, pairs, n_pairs, mode, ratio, q, t, dist,
                              t2, dist2, pts, n_out, ws, (cudaStream_t)stream);
   return launch_hamming(desc, nullptr, 0, 0, nkp, kp, n_cap, pairs, n_pairs, mode, ratio, q, t,
