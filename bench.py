@@ -25,12 +25,13 @@ if ROOT not in sys.path:
 N_FRAMES = 1000
 N_KP = 2000
 SEED = 20261104 + 1     # seed = 20261104 + config index
-# dram__bytes_read.sum + dram__bytes_write.sum of the 999-pair K1t launch (ncu --set full,
-# profiles/r2b_k1t_ncu_full_raw.csv: 655.41 MB read + 25.50 MB written)
-K1T_DRAM_BYTES_PER_LAUNCH = 680907264
-K1T_TRAFFIC_SOURCE = "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch " \
-                     "(profiles/r2b_k1t_ncu_full_raw.csv); algorithmic: 1000 frames x 8 operand tiles x " \
-                     "80 KB = 655.4 MB read once + 24 MB of row / column keys written: no re-reads from DRAM"
+# dram__bytes_read.sum + dram__bytes_write.sum of the 999-pair K1f launch (ncu --set full,
+# profiles/r2t_k1f_full_ncu_raw.csv); None until a capture of the current kernel is committed
+K1F_DRAM_BYTES_PER_LAUNCH = None
+K1F_TRAFFIC_SOURCE = "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch " \
+                     "(profiles/r2t_k1f_full_ncu_raw.csv); algorithmic: 1000 frames x (2048 rows x 128 B " \
+                     "+ 10 column tiles x 33 280 B) = 595 MB of operands read once + 24 MB of row / column " \
+                     "keys written"
 METRIC = "frame-pairs/sec (match+E-RANSAC+pose)"
 WORKLOAD = "configs[1]: 1000-frame synthetic drone sequence, ORB 2000 kp, consecutive-pair VO " \
            "with trajectory chaining"
@@ -156,7 +157,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * wall / max(args.steps, 1), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int8 tensor-core Hamming (exact) + f64 geometry",
+        "scaling": "weak", "vs_baseline": None, "dtype": "fp4 (e2m1) tensor-core Hamming (exact) + f64 geometry",
         "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": workers, "kind": "port",
                          "sample": sample},
@@ -289,8 +290,8 @@ def bench_configs(dev, peaks):
         res["C3"] = r
         r = pipeline_case(65, 4000, 256, SEED + 2)
         ops = 2.0 * 4000 * 4000 * 256 * 256
-        r["what"] = "configs[3] per-GPU work: ORB 4000 kp, 256 pairs (of the 4096), tcgen05 int8 matching"
-        r["match_int8_tops_algorithmic"] = ops / (r["match_kernel_ms"] * 1e-3) / 1e12 if r["match_kernel_ms"] else None
+        r["what"] = "configs[3] per-GPU work: ORB 4000 kp, 256 pairs (of the 4096), tcgen05 fp4 matching"
+        r["match_tops_algorithmic"] = ops / (r["match_kernel_ms"] * 1e-3) / 1e12 if r["match_kernel_ms"] else None
         r["match_popc32_per_s_algorithmic"] = 8.0 * 4000 * 4000 * 256 / (r["match_kernel_ms"] * 1e-3) if r["match_kernel_ms"] else None
         res["C4"] = r
     except Exception as ex:   # a config that fails must not take the headline down
@@ -541,7 +542,7 @@ def run_ours(args, rank, world, local_rank):
     finish_device()
     sync_all()
 
-    # ---- device-resident steps (the `value`): K1t is timed in-stream (two event records) ----
+    # ---- device-resident steps (the `value`): K1f is timed in-stream (two event records) ----
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -638,7 +639,7 @@ def run_ours(args, rank, world, local_rank):
         step_device(k)
     finish_device()
     torch.cuda.synchronize(dev)
-    names = {0: "hamming_tc_match (K1t)", 4: "hamming_tc_expand", 8: "match_compact", 9: "ransac_control",
+    names = {0: "hamming_f4_match (K1f)", 4: "hamming_f4_expand", 8: "match_compact", 9: "ransac_control",
              3: "ransac_solve (K3)", 1: "ransac_score (K2)", 5: "recover_pose (K5)", 6: "triangulate_pairs (K4)",
              7: "chain"}
     kernels_ms = {nm: prof(k)[0] / 3 for k, nm in names.items()}
@@ -671,12 +672,12 @@ def run_ours(args, rank, world, local_rank):
     value = total_pairs / (dev_ms * 1e-3)
     k1_avg_s = (k1_ms / max(k1_n, 1)) * 1e-3
     peaks, peak_src = measured_peaks()
-    # K1t: algorithmic work = every pair distance once = 2 * N1 * N2 * 256 integer ops per pair
+    # K1f: algorithmic work = every pair distance once = 2 * N1 * N2 * 256 ops per pair
     # (SURVEY 8d's N1*N2*8 popc32, one multiply-add per bit); the kernel EXECUTES both directions
-    # over K = 288 and rows padded to 2048: 2 * 2 * 2048^2 * 288.
+    # over K = 320, rows padded to 2048 and columns to 10 tiles of 208: 2 * 2 * 2048 * 2080 * 320.
     alg_ops = 2.0 * N_KP * N_KP * 256 * B
-    exe_ops = 2.0 * 2 * 2048 * 2048 * 288 * B
-    int8_peak = 2.0 * peaks.get("bf16_tflops", 1590.0)
+    exe_ops = 2.0 * 2 * 2048 * 2080 * 320 * B
+    int8_peak = 4.0 * peaks.get("bf16_tflops", 1590.0)     # (the fp4 peak; name kept)
     alg_tops = alg_ops / k1_avg_s / 1e12 if k1_avg_s > 0 else None
     exe_tops = exe_ops / k1_avg_s / 1e12 if k1_avg_s > 0 else None
     popc_rate = float(B) * N_KP * N_KP * 8.0 / k1_avg_s / 1e12 if k1_avg_s > 0 else None
@@ -684,12 +685,12 @@ def run_ours(args, rank, world, local_rank):
     out = {
         "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps,
         "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int8 tensor-core Hamming (exact) + f64 geometry",
+        "scaling": "weak", "vs_baseline": None, "dtype": "fp4 (e2m1) tensor-core Hamming (exact) + f64 geometry",
         "data": "synthetic",
         "config": {"workload": WORKLOAD, "pairs_per_gpu": B, "keypoints": N_KP,
                    "ransac": "conf 0.99, thr 1 px, max 1000 iters, adaptive (OpenCV semantics)",
                    "l2": "256 MB buffer written between timed steps (L2 flush, outside the events); "
-                         "the e2e steps stream 80 MB of fresh input each (> L2 with the 655 MB of operand tiles)",
+                         "the e2e steps stream 80 MB of fresh input each (> L2 with the 595 MB of operands)",
                    "parallelism": f"pair-sharded x{world}, one all_gather of [R|t] per step (run on a side stream "
                                   f"beside the next step's matching; the last step's inside its own interval)"
                    if world > 1 else "single GPU"},
@@ -706,29 +707,31 @@ def run_ours(args, rank, world, local_rank):
                        "poses and counts; the upload of step k+1 overlaps the compute of step k"},
         "gpu_launches": int((pipe.launches_per_run() + (2 if world > 1 else 0)) * steps),
         "clocks": clocks,
-        "roofline": {"kernel": "htc::match_kernel (K1t: Hamming as a tcgen05 kind::i8 contraction)",
+        "roofline": {"kernel": "hf4::match_kernel (K1f: Hamming as a tcgen05 kind::mxf4 (e2m1) contraction, "
+                               "row operand in TMEM)",
                      "bound": "tensor", "achieved": alg_tops, "peak": int8_peak, "unit": "TOP/s",
                      "frac": (alg_tops / int8_peak) if alg_tops else None,
-                     "traffic": K1T_DRAM_BYTES_PER_LAUNCH,
-                     "algorithmic": "2*N1*N2*256 int8 ops per pair x 999 pairs per launch (each pair "
+                     "traffic": K1F_DRAM_BYTES_PER_LAUNCH,
+                     "algorithmic": "2*N1*N2*256 ops per pair x 999 pairs per launch (each pair "
                                     "distance once = SURVEY 8d's N1*N2*8 popc32)",
                      "executed": exe_tops, "executed_frac": (exe_tops / int8_peak) if exe_tops else None,
-                     "executed_frac_of_nominal_4500": (exe_tops / 4500.0) if exe_tops else None,
-                     "note": "the cross-check needs both directions and the tensor pipe has the "
-                             "headroom the integer pipes lack, so the kernel runs TWO MMA passes "
-                             "(rows of each side), K padded 256 -> 288 for the index step, rows "
-                             "2000 -> 2048: executed = 2.42 x algorithmic. Timing variants with the "
-                             "epilogue removed run at the same speed: the kernel is MMA-issue bound",
-                     "peak_source": f"2 x bf16_tflops of {peak_src} (tcgen05 kind::i8 runs K = 32 per "
-                                    "instruction in the cycles kind::f16 needs for K = 16; no int8 "
-                                    "entry is measured by the driver); nominal dense int8 = 4500",
-                     "traffic_source": K1T_TRAFFIC_SOURCE,
+                     "executed_frac_of_nominal_9000": (exe_tops / 9000.0) if exe_tops else None,
+                     "note": "the cross-check needs both directions, so the kernel runs TWO MMA passes "
+                             "(rows of each side), K padded 256 -> 320 for the index step, rows "
+                             "2000 -> 2048, columns 2000 -> 2080: executed = 2.66 x algorithmic. "
+                             "Timing variants (profiles/r2t_k1f_check_and_timing_variants.log): every "
+                             "128x208x64 MMA takes ~139 clk against a 104 clk floor with the epilogue "
+                             "removed; the ranking adds ~20 %",
+                     "peak_source": f"4 x bf16_tflops of {peak_src} (tcgen05 kind::mxf4 runs K = 64 per "
+                                    "instruction in the cycles kind::f16 needs for K = 16; no fp4 "
+                                    "entry is measured by the driver); nominal dense fp4 = 9000",
+                     "traffic_source": K1F_TRAFFIC_SOURCE,
                      "avg_launch_ms": k1_avg_s * 1e3, "launches_timed": k1_n,
                      "share_of_step": (k1_ms / dev_ms) if dev_ms else None,
                      "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": peak_src},
         "roofline_popc": {"what": "the same launch in SURVEY 8d's popc accounting (N1*N2*8 popc32 per "
                                   "pair): the round-1 popc kernel reached 1.37x the POPC issue peak with "
-                                  "a carry-save tree; the contraction now runs on the tensor pipe",
+                                  "a carry-save tree; the contraction now runs on the tensor pipe (int8 in K1t, fp4 in K1f)",
                           "achieved": popc_rate, "peak": popc_peak.value / 1e12, "unit": "Tpopc32/s",
                           "frac": (popc_rate / (popc_peak.value / 1e12)) if popc_rate and popc_peak.value else None},
         "kernels_ms_per_step": kernels_ms,

@@ -46,10 +46,12 @@ const char* vo_last_error_string(void);
  *         t2/dist2 second neighbour (mode KNN2_RATIO; may be NULL);
  *         pts float64 [n_pairs, n_cap, 4] = (x1,y1,x2,y2) of each match (image_pair.py:294-299);
  *         n_out int32 [n_pairs] number of matches, rows sorted by queryIdx.
- * Two kernels behind one entry, identical results (bit-exact): small batches run the popc kernel
- * (csrc/hamming.cu); large ones expand every frame 0..n_frames-1 once into int8 operand tiles
- * and rank both directions with tcgen05 kind::i8 MMAs (csrc/hamming_tc.cuh).  n_frames = 0
- * (frame count unknown) keeps the popc kernel.  vo_debug_hamming(1 | 2) forces one of the two.
+ * Three kernels behind one entry, identical results (bit-exact): small batches run the popc
+ * kernel (csrc/hamming.cu); large ones expand every frame 0..n_frames-1 once into 4-bit (e2m1)
+ * operands and rank both directions with tcgen05 kind::mxf4 MMAs, the row operand in TMEM
+ * (csrc/hamming_f4.cuh); the int8 kind::i8 form of round 2 (csrc/hamming_tc.cuh) stays as a
+ * cross-check.  n_frames = 0 (frame count unknown) keeps the popc kernel.
+ * vo_debug_hamming(1 | 2 | 3) forces popc / int8 / fp4.
  */
 size_t vo_match_workspace_bytes(int n_frames, int n_pairs, int n_cap);
 int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float* kp, int n_cap,
@@ -58,8 +60,8 @@ int vo_match_hamming_batch(const uint8_t* desc, const int32_t* nkp, const float*
                            double* pts, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 int vo_debug_hamming(int flags);
 /* debug: raw fp32 accumulator of the fp4 kernel (csrc/hamming_f4.cuh) for the pair pairs[0..1] of
- * desc uint8 [2, n_cap, 32]: acc float32 [128, 240] = rows 0..127 x columns 0..239,
- * 36 * (256 - 2 * Hamming) + (239 - column) / 4 when the contraction is right */
+ * desc uint8 [2, n_cap, 32]: acc float32 [128, 208] = rows 0..127 x columns 0..207,
+ * 36 * (256 - 2 * Hamming) + (207 - column) / 4 when the contraction is right */
 int vo_debug_hamming_f4_acc(const uint8_t* desc, const int32_t* nkp, int n_cap, const int32_t* pairs,
                             float* acc, void* ws, size_t ws_bytes, void* stream);
 /* single pair convenience: d1 [n1,32], d2 [n2,32]; outputs sized n1 */

@@ -35,12 +35,12 @@ if stage in ("probe", "all"):
     rng = np.random.default_rng(3)
     N = 1000
     d = rng.integers(0, 256, (2, N, 32), dtype=np.uint8)
-    d[0, :64] = d[1, rng.permutation(240)[:64]]          # some near neighbours
+    d[0, :64] = d[1, rng.permutation(208)[:64]]          # some near neighbours
     d[0, :64, :2] ^= rng.integers(0, 256, (64, 2), dtype=np.uint8)
     desc = torch.from_numpy(d).cuda()
     nkp = torch.tensor([N, N], dtype=torch.int32, device="cuda")
     pairs = torch.tensor([[0, 1]], dtype=torch.int32, device="cuda")
-    acc = torch.full((128, 240), -12345.0, dtype=torch.float32, device="cuda")
+    acc = torch.full((128, 208), -12345.0, dtype=torch.float32, device="cuda")
     wsb = lib.vo_match_workspace_bytes(2, 1, N)
     ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
     _lib.check(lib.vo_debug_hamming_f4_acc(_lib.ptr(desc), _lib.ptr(nkp), N, _lib.ptr(pairs), _lib.ptr(acc),
@@ -48,9 +48,9 @@ if stage in ("probe", "all"):
     torch.cuda.synchronize()
     a = acc.cpu().numpy().astype(np.float64)
     bits = np.unpackbits(d, axis=2).astype(np.int32)
-    H = (bits[0, :128, None, :] != bits[1, None, :240, :]).sum(-1)
+    H = (bits[0, :128, None, :] != bits[1, None, :208, :]).sum(-1)
     dot36 = 36.0 * (256 - 2 * H)
-    idx = 0.25 * (239 - np.arange(240))[None, :]
+    idx = 0.25 * (207 - np.arange(208))[None, :]
     exp = dot36 + idx
     diff = np.abs(a - exp).max()
     print("probe: max |acc - expected| =", diff, flush=True)
@@ -58,7 +58,7 @@ if stage in ("probe", "all"):
         ok = False
         np.set_printoptions(linewidth=200, precision=3, suppress=True)
         print(" acc[0,:8]     ", a[0, :8]); print(" exp[0,:8]     ", exp[0, :8])
-        print(" acc[0,232:240]", a[0, 232:]); print(" exp[0,232:240]", exp[0, 232:])
+        print(" acc[0,200:208]", a[0, 200:]); print(" exp[0,200:208]", exp[0, 200:])
         print(" acc[1,:4], acc[32,:4], acc[127,:4]", a[1, :4], a[32, :4], a[127, :4])
         print(" exp[1,:4], exp[32,:4], exp[127,:4]", exp[1, :4], exp[32, :4], exp[127, :4])
         X = np.stack([dot36.ravel(), np.broadcast_to(idx, a.shape).ravel(), np.ones(a.size)], 1)
@@ -69,7 +69,7 @@ if stage in ("probe", "all"):
               " non-finite:", int((~np.isfinite(a)).sum()))
         # per K group: which of the 8 bit groups contribute (correlation with the per-group dots)
         for g in range(8):
-            Hg = (bits[0, :128, None, 32 * g:32 * g + 32] != bits[1, None, :240, 32 * g:32 * g + 32]).sum(-1)
+            Hg = (bits[0, :128, None, 32 * g:32 * g + 32] != bits[1, None, :208, 32 * g:32 * g + 32]).sum(-1)
             dg = 36.0 * (32 - 2 * Hg)
             print("  corr(acc - idx, dot of K group %d) = %.3f" % (g, np.corrcoef((a - idx).ravel(), dg.ravel())[0, 1]))
 
@@ -88,7 +88,7 @@ if stage in ("check", "all"):
             d[f, 5] = d[f, 3]; d[f, N - 1] = d[f, 3]
         nk = np.full(F, N, np.int32)
         if kind == "ragged":
-            special = [0, 1, 239, 240, 241, 255, 256, 257, 479, 480, 481, N - 1]
+            special = [0, 1, 103, 104, 105, 207, 208, 209, 255, 256, 257, 415, 416, 417, N - 1]
             for i in range(F):
                 nk[i] = min(N, special[i % len(special)]) if i % 2 else rng.integers(N // 2, N + 1)
         desc = torch.from_numpy(d).cuda(); nkp = torch.from_numpy(nk).cuda()
@@ -132,8 +132,7 @@ if stage in ("time", "all"):
         ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
         res = {}
         for label, flags, mode in [("popc", 1, 0), ("int8", 2, 0), ("fp4", 3, 0), ("int8_knn2", 2, 1), ("fp4_knn2", 3, 1),
-                                   ("fp4_noload", 3 | (1 << 3), 0), ("fp4_norank", 3 | (2 << 3), 0),
-                                   ("fp4_x128", 3 | (3 << 3), 0), ("fp4_16x256b", 3 | (4 << 3), 0)]:
+                                   ("fp4_noload", 3 | (1 << 3), 0), ("fp4_norank", 3 | (2 << 3), 0)]:
             lib.vo_debug_hamming(flags)
             def run():
                 _lib.check(lib.vo_match_hamming_batch(_lib.ptr(desc), _lib.ptr(nkp), _lib.ptr(kp), N, F,

@@ -294,10 +294,10 @@ static size_t popc_workspace_bytes(int n_pairs, int n_cap) {
   return (size_t)n_pairs * n_cap * (16 * 2 + 1) * sizeof(uint32_t);
 }
 
-// bits 0..1: 0 = choose by batch size, 1 = always the popc kernel, 2 = always the tensor-core
-// kernel (needs n_frames > 0); bits 3..4: timing-experiment instantiations of the tensor kernel
+// bits 0..1: 0 = choose by batch size, 1 = always the popc kernel, 2 / 3 = always the int8 / fp4
+// tensor-core kernel (need n_frames > 0); bits 3..5: timing-experiment instantiations of those
 static int g_hamming_debug = 0;
-static int g_hamming_tensor_default = 2;   // 2 = K1t (int8), 3 = K1f (fp4)
+static int g_hamming_tensor_default = 3;   // 2 = K1t (int8), 3 = K1f (fp4)
 extern "C" int vo_debug_hamming(int flags) {
   g_hamming_debug = flags;
   return VO_OK;
@@ -470,6 +470,7 @@ static int launch_hamming_f4(const uint8_t* desc, const int32_t* nkp, const floa
                              int32_t* q, int32_t* t, float* dist, int32_t* t2, float* dist2,
                              double* pts, int32_t* n_out, void* ws, cudaStream_t st, float* probe_acc) {
   const int nta = (n_cap + hf4::ROWS_A - 1) / hf4::ROWS_A, ntb = (n_cap + hf4::ROWS_B - 1) / hf4::ROWS_B;
+  const int rows_a = nta * hf4::ROWS_A;
   const hf4::Ws w = hf4::carve(ws, n_frames, n_pairs, n_cap);
   const int smem = (int)sizeof(hf4::Smem) + 1024;
   static bool attr_set[64] = {false};
@@ -481,44 +482,34 @@ static int launch_hamming_f4(const uint8_t* desc, const int32_t* nkp, const floa
         cudaFuncSetAttribute(hf4::match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
         cudaFuncSetAttribute(hf4::match_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
         cudaFuncSetAttribute(hf4::match_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
-        cudaFuncSetAttribute(hf4::match_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
-        cudaFuncSetAttribute(hf4::match_kernel<false, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
-        cudaFuncSetAttribute(hf4::match_kernel<false, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+        cudaFuncSetAttribute(hf4::match_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
       return check_launch("vo_match_hamming_batch(smem attribute, fp4)");
     attr_set[dev] = true;
   }
   {
     ProfScope prof(4, st);
-    const int rows = nta * hf4::ROWS_A > ntb * hf4::ROWS_B ? nta * hf4::ROWS_A : ntb * hf4::ROWS_B;
-    hf4::expand_kernel<<<dim3((rows + 255) / 256, n_frames), 256, 0, st>>>(desc, nkp, n_cap, nta, ntb,
-                                                                           w.tiles_a, w.tiles_b);
+    const int rows = rows_a > ntb * hf4::ROWS_B ? rows_a : ntb * hf4::ROWS_B;
+    hf4::expand_kernel<<<dim3((rows + 31) / 32, n_frames), 256, 0, st>>>(desc, nkp, n_cap, rows_a, ntb,
+                                                                           w.a_rows, w.tiles_b);
   }
   const int ndir = mode == VO_MATCH_MUTUAL ? 2 : 1;
   const long n_items = (long)n_pairs * ndir * nta;
   const int grid = (int)(n_items < device_sms() ? n_items : device_sms());
   {
     ProfScope prof(0, st);
+    const int kd = (g_hamming_debug >> 3) & 7;     // timing experiments: compile-time instantiations
+#define VO_F4_ARGS w.a_rows, w.tiles_b, nkp, pairs, n_cap, rows_a, ntb
     if (probe_acc)
-      hf4::match_kernel<false, true><<<1, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                    ntb, 1, 1, w.rowbest, w.colmin, probe_acc);
-    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 1)
-      hf4::match_kernel<false, false, 1><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
-    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 2)
-      hf4::match_kernel<false, false, 2><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
-    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 3)
-      hf4::match_kernel<false, false, 3><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
-    else if (mode == VO_MATCH_MUTUAL && ((g_hamming_debug >> 3) & 7) == 4)
-      hf4::match_kernel<false, false, 4><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                          ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+      hf4::match_kernel<false, true><<<1, hf4::THREADS, smem, st>>>(VO_F4_ARGS, 1, 1, w.rowbest, w.colmin, probe_acc);
+    else if (mode == VO_MATCH_MUTUAL && kd == 1)
+      hf4::match_kernel<false, false, 1><<<grid, hf4::THREADS, smem, st>>>(VO_F4_ARGS, ndir, n_items, w.rowbest, w.colmin, nullptr);
+    else if (mode == VO_MATCH_MUTUAL && kd == 2)
+      hf4::match_kernel<false, false, 2><<<grid, hf4::THREADS, smem, st>>>(VO_F4_ARGS, ndir, n_items, w.rowbest, w.colmin, nullptr);
     else if (mode == VO_MATCH_MUTUAL)
-      hf4::match_kernel<false><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                                ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+      hf4::match_kernel<false><<<grid, hf4::THREADS, smem, st>>>(VO_F4_ARGS, ndir, n_items, w.rowbest, w.colmin, nullptr);
     else
-      hf4::match_kernel<true><<<grid, hf4::THREADS, smem, st>>>(w.tiles_a, w.tiles_b, nkp, pairs, n_cap, nta,
-                                                               ntb, ndir, n_items, w.rowbest, w.colmin, nullptr);
+      hf4::match_kernel<true><<<grid, hf4::THREADS, smem, st>>>(VO_F4_ARGS, ndir, n_items, w.rowbest, w.colmin, nullptr);
+#undef VO_F4_ARGS
   }
   if (probe_acc) return check_launch("vo_debug_hamming_f4_acc");
   for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
@@ -533,8 +524,8 @@ static int launch_hamming_f4(const uint8_t* desc, const int32_t* nkp, const floa
   return check_launch("vo_match_hamming_batch(fp4 tensor)");
 }
 
-// debug: the raw fp32 accumulator of K1f for frames (0, 1) of `desc`, rows 0..127 x columns 0..239:
-// acc[i][j] = 36 * (256 - 2 * Hamming(i, j)) + (239 - j) / 4 when the contraction is right
+// debug: the raw fp32 accumulator of K1f for frames (0, 1) of `desc`, rows 0..127 x columns 0..207:
+// acc[i][j] = 36 * (256 - 2 * Hamming(i, j)) + (207 - j) / 4 when the contraction is right
 extern "C" int vo_debug_hamming_f4_acc(const uint8_t* desc, const int32_t* nkp, int n_cap,
                                        const int32_t* pairs, float* acc, void* ws, size_t ws_bytes,
                                        void* stream) {
