@@ -26,8 +26,8 @@ N_FRAMES = 1000
 N_KP = 2000
 SEED = 20261104 + 1     # seed = 20261104 + config index
 # dram__bytes_read.sum + dram__bytes_write.sum of the 999-pair K1f launch (ncu --set full,
-# profiles/r2t_k1f_full_ncu_raw.csv); None until a capture of the current kernel is committed
-K1F_DRAM_BYTES_PER_LAUNCH = None
+# profiles/r2t_k1f_full_ncu_raw.csv: 595.19 MB read + 24.75 MB written)
+K1F_DRAM_BYTES_PER_LAUNCH = 619940352   # 595.19 MB read + 24.75 MB written
 K1F_TRAFFIC_SOURCE = "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of this launch " \
                      "(profiles/r2t_k1f_full_ncu_raw.csv); algorithmic: 1000 frames x (2048 rows x 128 B " \
                      "+ 10 column tiles x 33 280 B) = 595 MB of operands read once + 24 MB of row / column " \

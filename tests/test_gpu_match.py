@@ -74,7 +74,8 @@ def test_all_identical_descriptors_tie_break(cuda_dev):
 
 
 def _batch(lib, dev, desc, kp, nkp, pairs, N, mode=0, ratio=0.0, path=0):
-    """vo_match_hamming_batch on host arrays; path 1 = popc kernel, 2 = tensor-core kernel"""
+    """vo_match_hamming_batch on host arrays; path 1 = popc kernel, 2 = int8 tensor-core kernel
+    (K1t), 3 = fp4 tensor-core kernel (K1f, what large batches run by default)"""
     B, F = len(pairs), desc.shape[0]
     d_desc, d_kp = torch.from_numpy(desc).to(dev), torch.from_numpy(kp).to(dev)
     q = torch.full((B, N), -7, dtype=torch.int32, device=dev)
@@ -99,10 +100,10 @@ def _batch(lib, dev, desc, kp, nkp, pairs, N, mode=0, ratio=0.0, path=0):
     return [x.cpu().numpy() for x in (q, t, dist, t2, dist2, pts, n_out)]
 
 
-@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("path", [1, 2, 3])
 def test_batched_ragged_frames_and_gathered_points(cuda_dev, path):
-    """batched entry: ragged keypoint counts, arbitrary pair list, fused point gather; both the
-    popc kernel and the tcgen05 int8 kernel (row-block / tile boundaries at 128, 256, 512)."""
+    """batched entry: ragged keypoint counts, arbitrary pair list, fused point gather; the popc
+    kernel and the two tcgen05 kernels (row-block / tile boundaries at 128, 208, 256, 416, 512)."""
     lib = _lib.load()
     seq = make_sequence(5, 600, 42)
     nkp = np.array([600, 512, 1, 333, 600], np.int32)
@@ -137,18 +138,20 @@ def _tie_heavy_frames(rng, F, N):
     return desc
 
 
-@pytest.mark.parametrize("N,nk", [(700, [700, 699, 257, 256, 255, 1, 700, 128, 129]),
-                                  (2000, [2000, 1777, 2000, 1025])])
-def test_tensor_core_path_equals_cv2_and_popc_path(cuda_dev, N, nk):
-    """K1t (tcgen05 kind::i8) against live cv2 AND against the popc kernel: mutual matches and
-    knn(k=2) + ratio, indices and distances bit-exact, ragged counts on every tile boundary."""
+@pytest.mark.parametrize("tc_path", [2, 3])
+@pytest.mark.parametrize("N,nk", [(700, [700, 699, 257, 256, 255, 1, 700, 128, 129, 207, 208, 209, 416, 417, 624]),
+                                  (2000, [2000, 1777, 2000, 1025, 1872, 1873])])
+def test_tensor_core_path_equals_cv2_and_popc_path(cuda_dev, N, nk, tc_path):
+    """K1t (tcgen05 kind::i8) and K1f (kind::mxf4, e2m1) against live cv2 AND against the popc
+    kernel: mutual matches and knn(k=2) + ratio, indices and distances bit-exact, ragged counts on
+    every tile boundary of both kernels (256-row blocks; 256- / 208-column tiles)."""
     lib = _lib.load()
     rng = np.random.default_rng(N)
     F = len(nk)
     desc = _tie_heavy_frames(rng, F, N)
     kp = rng.random((F, N, 2), dtype=np.float32) * 1000
     pairs = np.array([[f, f + 1] for f in range(F - 1)] + [[F - 1, 0], [0, 0]], np.int32)
-    out_tc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, path=2)
+    out_tc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, path=tc_path)
     out_pc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, path=1)
     bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)
     for b, (fa, fb) in enumerate(pairs):
@@ -162,7 +165,7 @@ def test_tensor_core_path_equals_cv2_and_popc_path(cuda_dev, N, nk):
         assert [m.distance for m in ref] == out_tc[2][b, :n].tolist()
     # knn(k=2) + ratio 0.8, and ratio < 0 = every query with both neighbours
     for ratio in (0.8, -1.0):
-        k_tc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, mode=1, ratio=ratio, path=2)
+        k_tc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, mode=1, ratio=ratio, path=tc_path)
         k_pc = _batch(lib, cuda_dev, desc, kp, nk, pairs, N, mode=1, ratio=ratio, path=1)
         for b, (fa, fb) in enumerate(pairs):
             n = k_tc[6][b]
@@ -177,13 +180,14 @@ def test_tensor_core_path_equals_cv2_and_popc_path(cuda_dev, N, nk):
                 assert [r[1].distance for r in refk] == k_tc[4][b, :n].tolist()
 
 
-def test_tensor_core_path_full_size_c4_properties(cuda_dev):
-    """config C4 size through K1t: 6 pairs x 4000 kp, results equal to the popc kernel's and every
-    distance equal to the recomputed Hamming distance."""
+@pytest.mark.parametrize("tc_path", [2, 3])
+def test_tensor_core_path_full_size_c4_properties(cuda_dev, tc_path):
+    """config C4 size through K1t / K1f: 6 pairs x 4000 kp, results equal to the popc kernel's and
+    every distance equal to the recomputed Hamming distance."""
     lib = _lib.load()
     seq = make_sequence(7, 4000, 77)
     pairs = seq.consecutive_pairs()
-    a = _batch(lib, cuda_dev, seq.desc, seq.kp, seq.nkp, pairs, 4000, path=2)
+    a = _batch(lib, cuda_dev, seq.desc, seq.kp, seq.nkp, pairs, 4000, path=tc_path)
     b = _batch(lib, cuda_dev, seq.desc, seq.kp, seq.nkp, pairs, 4000, path=1)
     assert np.array_equal(a[6], b[6])
     for p in range(len(pairs)):

@@ -4,7 +4,10 @@
 `cuobjdump -sass` + `cuobjdump -res-usage` on the in-tree library (sm_100a); for every kernel the
 counts of the instructions that prove which hardware path it uses:
   UTCHMMA / UTCIMMA / UTCQMMA  tcgen05.mma kind::f16 / kind::i8 / kind::f8f6f4
-  LDTM                         tcgen05.ld  (TMEM -> registers)
+  UTCOMMA                      tcgen05.mma kind::mxf4 .block_scale (K1f; its first source is tmem[..]:
+                               the row operand is read from TMEM)
+  LDTM / STTM                  tcgen05.ld / tcgen05.st  (TMEM <-> registers)
+  FMNMX3                       3-input fp32 max (K1f's whole ranking)
   UTCBAR                       tcgen05.commit
   UBLKCP                       cp.async.bulk (1-D bulk copy; no tensor-map TMA is used: UTMALDG = 0)
   SYNCS                        mbarrier operations
@@ -19,7 +22,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "visual_odometry_b200", "csrc", "libvo_b200.so")
-PATTERNS = ["UTCHMMA", "UTCIMMA", "UTCQMMA", "LDTM", "UTCBAR", "UBLKCP", "UTMALDG", "SYNCS", "POPC",
+PATTERNS = ["UTCHMMA", "UTCIMMA", "UTCQMMA", "UTCOMMA", "LDTM", "STTM", "FMNMX3", "UTCBAR", "UBLKCP", "UTMALDG", "SYNCS", "POPC",
             "LOP3", "VIMNMX", "REDUX", "SHFL", "DFMA", "DMUL", "DADD", "MUFU", "IMAD", "BAR.SYNC", "ATOM", "RED."]
 
 
