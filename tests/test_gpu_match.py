@@ -229,3 +229,29 @@ def test_descriptor_buffer_refilled_in_place_is_not_served_stale(cuda_dev):
     frozen = buf.copy()
     frozen.flags.writeable = False                                    # opt in to the cache
     assert _triples(m.match(frozen, other)) == ref == _triples(m.match(frozen, other))
+
+
+def test_fp4_accumulator_is_the_exact_key(cuda_dev):
+    """K1f's raw fp32 accumulator (vo_debug_hamming_f4_acc) of one 128 x 208 block equals
+    36 * (256 - 2 * Hamming) + (207 - column) / 4 exactly: the e2m1 operand forms, the all-ones
+    block scales and the index step of the kind::mxf4 contraction, checked against numpy."""
+    lib = _lib.load()
+    rng = np.random.default_rng(3)
+    N = 1000
+    d = rng.integers(0, 256, (2, N, 32), dtype=np.uint8)
+    d[0, :64] = d[1, rng.permutation(208)[:64]]
+    d[0, :64, :2] ^= rng.integers(0, 256, (64, 2), dtype=np.uint8)
+    d[0, 100] = 0; d[1, 7] = 255; d[0, 101] = 255                      # distances 256 and 0
+    desc = torch.from_numpy(d).to(cuda_dev)
+    nkp = torch.tensor([N, N], dtype=torch.int32, device=cuda_dev)
+    pairs = torch.tensor([[0, 1]], dtype=torch.int32, device=cuda_dev)
+    acc = torch.full((128, 208), -12345.0, dtype=torch.float32, device=cuda_dev)
+    wsb = lib.vo_match_workspace_bytes(2, 1, N)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=cuda_dev)
+    _lib.check(lib.vo_debug_hamming_f4_acc(_lib.ptr(desc), _lib.ptr(nkp), N, _lib.ptr(pairs), _lib.ptr(acc),
+                                           _lib.ptr(ws), wsb, _lib.cur_stream()))
+    torch.cuda.synchronize()
+    bits = np.unpackbits(d, axis=2).astype(np.int32)
+    H = (bits[0, :128, None, :] != bits[1, None, :208, :]).sum(-1)
+    want = 36.0 * (256 - 2 * H) + 0.25 * (207 - np.arange(208))[None, :]
+    assert np.array_equal(acc.cpu().numpy().astype(np.float64), want)
