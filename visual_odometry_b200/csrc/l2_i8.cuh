@@ -34,7 +34,7 @@ constexpr int B_BYTES = 10 * KG_BYTES;              // data + ext
 constexpr uint32_t LBO = KG_BYTES, SBO = 128;
 constexpr int NSTAGE = 4;
 constexpr int NCC = 4;                              // ring of per-tile column constants
-constexpr int EPI_WARPS = 8;                     // warp & 3 = TMEM lane quarter, warp >> 2 = 128-column half
+constexpr int EPI_WARPS = 8;                     // warp & 3 = TMEM lane quarter, warp >> 2 = accumulator
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr int H_MAX = 127 * 127 * 31 + 126;         // largest floor(|b|^2/2) the ext group can hold
 constexpr int KEY_NONE_BELOW = -(H_MAX + 1) * 512;  // keys of padded columns lie below this
@@ -119,7 +119,6 @@ struct __align__(1024) Smem {
   uint8_t A[A_BYTES];
   uint8_t B[NSTAGE][B_BYTES];
   int32_t cc[NCC][ROWS];
-  uint4 part[2][1][2][128];      // [item parity][column half - 1][row block][row]: (k1, t1, k2, t2)
   uint64_t full_a, empty_a;
   uint64_t full_b[NSTAGE], empty_b[NSTAGE];
   uint64_t full_c[NCC], empty_c[NCC];
@@ -173,9 +172,8 @@ __device__ __forceinline__ int imad_i(int a, int b, int c) {
 // rowbest layout of l2.cu: float4 (d2_1, idx_1 bits, d2_2, idx_2 bits) at
 // [((pair * 2 + dir) * n_splits + split) * row_stride + row]
 // VARIANT (compile time: a RUN-time switch around the TMEM loads costs 15-25 % by itself, measured):
-// 0 = TMEM loads pipelined with the ranking, accumulator released after the last load;
-// 1 = the same with explicit ld.shared for the per-column constants;
-// 2 = four loads back to back, release, then ranking (128 live value registers).
+// 0 = the per-column constants through the generic load the compiler emits;
+// 1, 2 = explicit ld.shared for them (the default).
 template <bool TOP2, int VARIANT>
 __global__ void __launch_bounds__(THREADS, 1)
 match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
@@ -193,7 +191,7 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
     mbar_init(&S.empty_a, 1);
     for (int s = 0; s < NSTAGE; ++s) { mbar_init(&S.full_b[s], 1); mbar_init(&S.empty_b[s], 1); }
     for (int s = 0; s < NCC; ++s) { mbar_init(&S.full_c[s], 1); mbar_init(&S.empty_c[s], EPI_WARPS); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&S.tmem_full[s], 1); mbar_init(&S.tmem_empty[s], EPI_WARPS); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&S.tmem_full[s], 1); mbar_init(&S.tmem_empty[s], EPI_WARPS / 2); }
     fence_barrier_init();
   }
   if (warp == EPI_WARPS) tc::tmem_alloc(&S.tmem_base, 512);
@@ -261,135 +259,94 @@ match_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ nkp,
       }
     }
   } else {
-    // ===== epilogue warps =====
-    const int quarter = warp & 3, cq = warp >> 2;
+    // ===== epilogue warps: thread = TMEM lane = row; warps 0..3 drain accumulator 0 (row block 0),
+    // warps 4..7 accumulator 1, independently: the barrier / TMEM-load / ranking chain of one
+    // accumulator overlaps the other's, and nothing is merged through shared memory =====
+    const int quarter = warp & 3, rb = warp >> 2;
     const int rl = quarter * 32 + lane;
     const int mul = 512 + (int)(n_items < 0);      // = 512, opaque: keeps the IMAD form
-    uint32_t use[2] = {0u, 0u}, n_it = 0, g = 0;
+    uint32_t use = 0, g = 0;
     for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
       const htc::Item it = htc::get_item(item, nkp, pairs, n_cap, nrbp, ndir);
       if (it.ntile == 0) continue;
-      Top st[2];
-#pragma unroll
-      for (int rb = 0; rb < 2; ++rb) { st[rb].k1 = st[rb].k2 = MININT; st[rb].t1 = st[rb].t2 = -1; }
+      Top st;
+      st.k1 = st.k2 = MININT; st.t1 = st.t2 = -1;
       for (int t = 0; t < it.ntile; ++t, ++g) {
         const int sc = g % NCC;
         mbar_wait(&S.full_c[sc], (g / NCC) & 1);
-        const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][cq * 128]);
-        const uint32_t ccs = smem_u32(&S.cc[sc][cq * 128]);
-#pragma unroll
-        for (int rb = 0; rb < 2; ++rb) {
-          if (rb >= it.nrb) break;
-          mbar_wait(&S.tmem_full[rb], use[rb] & 1);
-          ++use[rb];
+        if (rb < it.nrb) {
+          const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[sc][0]);
+          const uint32_t ccs = smem_u32(&S.cc[sc][0]);
+          mbar_wait(&S.tmem_full[rb], use & 1);
+          ++use;
           tc::fence_after_sync();
-          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS + cq * 128;
-          uint32_t va[32], vb[32];
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS;
+          uint32_t v[2][32];
           int h = MININT, l = MININT;
-          auto rank = [&](uint32_t (&v)[32], int chunk) {
+          auto rank = [&](uint32_t (&x)[32], int chunk) {
 #pragma unroll
             for (int c4 = 0; c4 < 8; ++c4) {
               // broadcast shared-memory read of four column constants
               const uint4 cc = VARIANT >= 1 ? lds128(ccs + (chunk * 8 + c4) * 16) : ccp[chunk * 8 + c4];
-              v[4 * c4 + 0] = (uint32_t)imad_i((int)v[4 * c4 + 0], mul, (int)cc.x);
-              v[4 * c4 + 1] = (uint32_t)imad_i((int)v[4 * c4 + 1], mul, (int)cc.y);
-              v[4 * c4 + 2] = (uint32_t)imad_i((int)v[4 * c4 + 2], mul, (int)cc.z);
-              v[4 * c4 + 3] = (uint32_t)imad_i((int)v[4 * c4 + 3], mul, (int)cc.w);
+              x[4 * c4 + 0] = (uint32_t)imad_i((int)x[4 * c4 + 0], mul, (int)cc.x);
+              x[4 * c4 + 1] = (uint32_t)imad_i((int)x[4 * c4 + 1], mul, (int)cc.y);
+              x[4 * c4 + 2] = (uint32_t)imad_i((int)x[4 * c4 + 2], mul, (int)cc.z);
+              x[4 * c4 + 3] = (uint32_t)imad_i((int)x[4 * c4 + 3], mul, (int)cc.w);
             }
             if (TOP2) {
               int ch, cl;
-              htc::top2_32(v, ch, cl);
+              htc::top2_32(x, ch, cl);
               htc::merge2(h, l, ch, cl);
             } else {
-              h = max(h, htc::max32(v));
+              h = max(h, htc::max32(x));
             }
           };
-          if constexpr (VARIANT == 2) {
-            uint32_t vc[32], vd[32];
-            tc::ld_32x32_issue(taddr, va);
-            tc::ld_32x32_issue(taddr + 32, vb);
-            tc::ld_32x32_issue(taddr + 64, vc);
-            tc::ld_32x32_issue(taddr + 96, vd);
-            tc::ld_wait(va);
-            tc::ld_wait(vb);
-            tc::ld_wait(vc);
-            tc::ld_wait(vd);
-            tc::fence_before_sync();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);   // the accumulator is in registers
-            rank(va, 0);
-            rank(vb, 1);
-            rank(vc, 2);
-            rank(vd, 3);
-            fold_tile<TOP2>(st[rb], h, l, t);
-            continue;
+          tc::ld_32x32_issue(taddr, v[0]);
+          tc::ld_wait(v[0]);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            if (c + 1 < 8) tc::ld_32x32_issue(taddr + 32 * (c + 1), v[(c + 1) & 1]);
+            if (c == 7) {             // every load has been waited for: the accumulator is in registers
+              tc::fence_before_sync();
+              __syncwarp();
+              if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);
+            }
+            rank(v[c & 1], c);
+            if (c + 1 < 8) tc::ld_wait(v[(c + 1) & 1]);
           }
-          tc::ld_32x32_issue(taddr, va);
-          tc::ld_wait(va);
-          tc::ld_32x32_issue(taddr + 32, vb);
-          rank(va, 0);
-          tc::ld_wait(vb);
-          tc::ld_32x32_issue(taddr + 64, va);
-          rank(vb, 1);
-          tc::ld_wait(va);
-          tc::ld_32x32_issue(taddr + 96, vb);
-          rank(va, 2);
-          tc::ld_wait(vb);
-          tc::fence_before_sync();
-          __syncwarp();
-          if (lane == 0) tc::mbar_arrive(&S.tmem_empty[rb]);
-          rank(vb, 3);
-          fold_tile<TOP2>(st[rb], h, l, t);
+          fold_tile<TOP2>(st, h, l, t);
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&S.empty_c[sc]);     // this warp is done with the tile's constants
       }
-      // ---- merge the two column halves, convert to squared distances, write ----
-      if (cq > 0) {
-#pragma unroll
-        for (int rb = 0; rb < 2; ++rb)
-          S.part[n_it & 1][cq - 1][rb][rl] = make_uint4((uint32_t)st[rb].k1, (uint32_t)st[rb].t1,
-                                                        (uint32_t)st[rb].k2, (uint32_t)st[rb].t2);
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (cq == 0) {
-#pragma unroll
-        for (int rb = 0; rb < 2; ++rb) {
-          if (rb >= it.nrb) break;
-          Top m = st[rb];
-          if (m.t1 < 0 && m.t2 >= 0) { m.k1 = m.k2; m.t1 = m.t2; m.t2 = -1; }
-#pragma unroll
-          for (int pq = 0; pq < 1; ++pq) {
-            const uint4 o = S.part[n_it & 1][pq][rb][rl];
-            insert(m, (int)o.x, (int)o.y);
-            if (TOP2) insert(m, (int)o.z, (int)o.w);
-          }
-          const int row = it.rbp * ROWS + rb * 128 + rl;
-          if (row < it.nq) {
-            const int na = (int)norms[(size_t)it.fq * norm_stride + row];
-            const float INF = __int_as_float(0x7f800000);
-            auto decode = [&](int key, int tile, float& d2, int& col) {
-              col = -1; d2 = INF;
-              if (tile < 0 || key < KEY_NONE_BELOW) return;
-              col = tile * ROWS + 255 - (key & 255);
-              if (col >= it.nt) { col = -1; return; }
-              const int acc = key >> 9, e = 1 - ((key >> 8) & 1);
-              d2 = (float)max(na - 2 * acc + e, 0);
-            };
-            float4 r;
-            int c1, c2 = -1;
-            float d1, d2v = INF;
-            decode(m.k1, m.t1, d1, c1);
-            if (TOP2) decode(m.k2, m.t2, d2v, c2);
-            r.x = d1; r.y = __int_as_float(c1); r.z = d2v; r.w = __int_as_float(c2);
-            float4* dst = rowbest + (((size_t)it.pair * 2 + it.dir) * n_splits) * row_stride + row;
-            dst[0] = r;
-            for (int s = 1; s < n_splits; ++s)      // the merge in l2_compact_kernel reads every split
-              dst[(size_t)s * row_stride] = make_float4(INF, __int_as_float(-1), INF, __int_as_float(-1));
-          }
+      // ---- convert to squared distances, write ----
+      if (rb < it.nrb) {
+        Top m = st;
+        if (m.t1 < 0 && m.t2 >= 0) { m.k1 = m.k2; m.t1 = m.t2; m.t2 = -1; }
+        const int row = it.rbp * ROWS + rb * 128 + rl;
+        if (row < it.nq) {
+          const int na = (int)norms[(size_t)it.fq * norm_stride + row];
+          const float INF = __int_as_float(0x7f800000);
+          auto decode = [&](int key, int tile, float& d2, int& col) {
+            col = -1; d2 = INF;
+            if (tile < 0 || key < KEY_NONE_BELOW) return;
+            col = tile * ROWS + 255 - (key & 255);
+            if (col >= it.nt) { col = -1; return; }
+            const int acc = key >> 9, e = 1 - ((key >> 8) & 1);
+            d2 = (float)max(na - 2 * acc + e, 0);
+          };
+          float4 r;
+          int c1, c2 = -1;
+          float d1, d2v = INF;
+          decode(m.k1, m.t1, d1, c1);
+          if (TOP2) decode(m.k2, m.t2, d2v, c2);
+          r.x = d1; r.y = __int_as_float(c1); r.z = d2v; r.w = __int_as_float(c2);
+          float4* dst = rowbest + (((size_t)it.pair * 2 + it.dir) * n_splits) * row_stride + row;
+          dst[0] = r;
+          for (int s = 1; s < n_splits; ++s)      // the merge in l2_compact_kernel reads every split
+            dst[(size_t)s * row_stride] = make_float4(INF, __int_as_float(-1), INF, __int_as_float(-1));
         }
       }
-      ++n_it;
     }
   }
   tc::fence_before_sync();
