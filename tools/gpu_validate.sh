@@ -10,6 +10,7 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "s
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
 timeout 600 python tools/gpu_check_hamming.py > gpurun_out/hamming_check.log 2>&1; echo "rc=$?" >> gpurun_out/hamming_check.log
+timeout 600 python tools/gpu_check_hamming_f4.py all > gpurun_out/hamming_f4_check.log 2>&1; echo "rc=$?" >> gpurun_out/hamming_f4_check.log
 timeout 600 python tools/gpu_check_l2.py > gpurun_out/l2_check_int8.log 2>&1; echo "rc=$?" >> gpurun_out/l2_check_int8.log
 timeout 600 python tools/gpu_check_l2.py 128 > gpurun_out/l2_check_bf16.log 2>&1; echo "rc=$?" >> gpurun_out/l2_check_bf16.log
 timeout 600 python tools/gpu_reference_loop.py > gpurun_out/reference_loop.log 2>&1; echo "rc=$?" >> gpurun_out/reference_loop.log
@@ -25,7 +26,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --lo
 if [ "$1" = "full" ]; then
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:describe_kernel -c 1 -s 1 -o gpurun_out/sift_describe_full -f python tools/gpu_sift_bench.py 480 640 32 1 > gpurun_out/ncu_sift_describe.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:blur_kernel -c 1 -s 46 -o gpurun_out/sift_blur_full -f python tools/gpu_sift_bench.py 480 640 32 1 > gpurun_out/ncu_sift_blur.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 3 -c 1 -o gpurun_out/k1t_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1t.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 3 -c 1 -o gpurun_out/k1f_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k1f.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:match_kernel -s 40 -c 1 -o gpurun_out/k6i_full -f python tools/gpu_check_l2.py > gpurun_out/ncu_k6i.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_score -s 12 -c 1 -o gpurun_out/k2_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k2.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_solve -s 12 -c 1 -o gpurun_out/k3_full -f python bench.py --steps 1 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu_k3.log 2>&1
