@@ -18,11 +18,12 @@
 // columns (beyond the frame's key points) are all-zero operands (key 0); the epilogue masks them
 // in the last column tile only.
 //
-// What bounds a one-CTA tcgen05.mma with both operands in shared memory is the operand read
-// ((128 + N) x 32 bytes per instruction at ~80 B/clk: ~150 clk per MMA for int8 and fp4 alike,
-// measured: profiles/r2t_k1f_check_and_timing_variants.log), so the ROW operand lives in TMEM here
-// (tcgen05.mma [d], [a_tmem], b_desc): it is constant over a work item, and only the column tile
-// is read from shared memory (N x 32 bytes per instruction).
+// The ROW operand lives in TMEM (tcgen05.mma [d], [a_tmem], b_desc): it is constant over a work
+// item, so the bulk-copy producer never waits for it at an item boundary and every instruction reads
+// only the column tile (N x 32 bytes) from shared memory.  Measured per MMA with the epilogue
+// removed: 156 clk with both operands in shared memory (N = 240), 139 clk with this form (floor
+// 104 clk); of the rest ~80 clk per accumulator are the hand-off between the MMA issuer and the
+// epilogue warps that two accumulators do not cover (profiles/r2t_k1f_one_pass_experiment_negative.log).
 //
 // TMEM (512 columns): two 128 x 208 fp32 accumulators (0..207, 208..415), the row operand of the
 // two row blocks (416..455, 456..495: 40 columns = 320 fp4 values per row) and 16 columns of scale
