@@ -69,19 +69,6 @@ __device__ __forceinline__ void mma_mxf4(uint32_t d_tmem, uint32_t a_tmem, uint6
       "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb)
       : "memory");
 }
-// busy-polling wait (mbarrier.test_wait never suspends the thread) for the two hand-offs that sit
-// on the tensor pipe's critical path: accumulator full -> epilogue, accumulator empty -> MMA issuer
-__device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "SPIN_LOOP:\n"
-      "mbarrier.test_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@!p bra SPIN_LOOP;\n"
-      "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
 // 32 TMEM lanes x 16 columns <- one value (the scale factors: every byte 0x7F = 2^0)
 __device__ __forceinline__ void st_32x16_fill(uint32_t taddr, uint32_t v) {
   asm volatile(
@@ -346,7 +333,7 @@ match_kernel(const uint8_t* __restrict__ a_rows, const uint8_t* __restrict__ til
 #pragma unroll
           for (int rb = 0; rb < 2; ++rb) {
             if (rb >= it.nrb) break;
-            mbar_spin(&S.tmem_empty[rb], (use[rb] & 1) ^ 1);   // the epilogue has drained accumulator rb
+            mbar_wait(&S.tmem_empty[rb], (use[rb] & 1) ^ 1);   // the epilogue has drained accumulator rb
             tc::fence_after_sync();
             const uint32_t a_addr = tmem + A_COL + rb * A_COLS;
             const uint32_t d_addr = tmem + rb * ROWS_B;
@@ -378,7 +365,7 @@ match_kernel(const uint8_t* __restrict__ a_rows, const uint8_t* __restrict__ til
       int b1 = KEY_MININT, b2 = KEY_MININT;
       for (int t = 0; t < it.ntile; ++t) {
         const int nvalid = min(it.nt - t * ROWS_B, ROWS_B);   // valid columns of this tile
-        mbar_spin(&S.tmem_full[rb], use & 1);
+        mbar_wait(&S.tmem_full[rb], use & 1);
         ++use;
         tc::fence_after_sync();
         const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + rb * ROWS_B;
