@@ -179,3 +179,36 @@ def test_full_size_c4_batch_vs_reference_path(cuda_dev):
     record_parity("c4_batch_vs_reference_path", pairs_checked=3, masks_identical=exact,
                   pairs_with_different_mask=off_pairs)
     assert exact == 3                         # measured: masks identical on 3 / 3
+
+
+@pytest.mark.parametrize("use_fill", [True, False])
+def test_run_stream_equals_the_one_call_path(cuda_dev, use_fill):
+    """PairPipeline.run_stream (batch 0 uploaded in two pieces with the chain started on the first,
+    every later batch uploaded whole while its predecessor computes, two input slots) must give,
+    batch by batch, exactly what run_host gives for the same frames."""
+    F, N = 81, 640
+    seqs = [make_sequence(F, N, 300 + s) for s in range(3)]
+    pairs = seqs[0].consecutive_pairs()
+    pipe = PairPipeline(N, F - 1, K=seqs[0].K)
+    want = [pipe.run_host(s.desc, s.kp, s.nkp, pairs) for s in seqs]
+    got = {}
+
+    def fill(k, pin):
+        s = seqs[k % 3]
+        pin["desc"][:F].copy_(torch.from_numpy(s.desc))
+        pin["kp"][:F].copy_(torch.from_numpy(s.kp.astype(np.float32)))
+        pin["nkp"][:F].copy_(torch.from_numpy(np.asarray(s.nkp, np.int32)))
+        pin["pairs"][:F - 1].copy_(torch.from_numpy(np.asarray(pairs, np.int32)))
+
+    def consume(k, res):
+        got[k] = {n: v.numpy().copy() for n, v in res.items()}
+
+    pipe.stage_host(seqs[0].desc, seqs[0].kp, seqs[0].nkp, pairs)
+    pipe.run_stream(F, F - 1, 5, fill=fill if use_fill else None, consume=consume)
+    torch.cuda.synchronize()
+    assert sorted(got) == [0, 1, 2, 3, 4]
+    for k in range(5):
+        w = want[k % 3 if use_fill else 0]
+        assert (w["n_match"] > 0.5 * N).all()
+        for name in ("n_match", "n_inl", "status", "R", "t", "poses"):
+            assert np.array_equal(got[k][name], w[name]), (k, name)

@@ -304,7 +304,7 @@ class PairPipeline:
 
     # ------------------------------------------------------------------ streamed batches (e2e)
     def run_stream(self, n_frames, n_pairs, steps, fill=None, consume=None, after_compute=None,
-                   after_match=None):
+                   after_match=None, first0=0.15):
         """`steps` batches through the whole chain with the upload of batch k+1 running on a copy
         stream while batch k computes (two input slots on the device, two pinned result slots on
         the host).  Every batch: H2D of its frames from the pinned staging area, the chain, D2H of
@@ -313,7 +313,9 @@ class PairPipeline:
         `consume(k, res)` receives batch k's host results (views of a pinned slot, valid until
         batch k+2 is submitted), `after_compute(k)` may enqueue more work on the compute stream
         (multi-GPU: packing the poses), `after_match(k)` is passed to run_device (multi-GPU: the
-        all-gather of batch k - 1).  Returns (h2d_bytes, d2h_bytes) per batch."""
+        all-gather of batch k - 1).  Batch 0 has no predecessor to hide its upload behind: its frames
+        go up in two pieces (the first `first0` of them) and the chain starts on the pairs whose
+        frames have arrived.  Returns (h2d_bytes, d2h_bytes) per batch."""
         pin, f, b = self._pinned(), int(n_frames), int(n_pairs)
         main = torch.cuda.current_stream()
         if self._copy_stream is None:
@@ -333,7 +335,7 @@ class PairPipeline:
 
         def upload(k):
             sl = self._slots[k & 1]
-            if fill is not None:
+            if fill is not None and not (k == 0 and filled0):
                 if k > 0:
                     uploaded[(k - 1) & 1].synchronize()      # the staging area is free again
                 fill(k, pin)
@@ -356,13 +358,54 @@ class PairPipeline:
                                 n_match=o["n_match"][:b], status=o["status"][:b],
                                 poses=o["poses"][:b + 1]))
 
-        upload(0)
+        # Batch 0 has nothing to hide its upload behind: its frames go up in two pieces (the first
+        # `first0` of them) and the chain starts on the pairs whose frames have arrived, as in
+        # run_staged; every later batch is uploaded whole while its predecessor computes.
+        first_cut = None
+        filled0 = False
+        if steps and self.descriptor == "orb" and f >= 64 and b >= 64:
+            if fill is not None:
+                fill(0, pin)               # the cut below reads batch 0's pair list
+                filled0 = True
+            f0 = max(2, round(first0 * f))
+            need = np.maximum.accumulate(pin["pairs"][:b].numpy().max(axis=1))
+            p0_hi = int(np.searchsorted(need, f0, side="left"))
+            if 0 < p0_hi < b:
+                first_cut = (f0, p0_hi)
+
+        def upload_first():
+            f0, _ = first_cut
+            sl = self._slots[0]
+            with torch.cuda.stream(cs):
+                sl["nkp"][:f].copy_(pin["nkp"][:f], non_blocking=True)
+                sl["pairs"][:b].copy_(pin["pairs"][:b], non_blocking=True)
+                sl["desc"][:f0].copy_(pin["desc"][:f0], non_blocking=True)
+                sl["kp"][:f0].copy_(pin["kp"][:f0], non_blocking=True)
+                ev0 = torch.cuda.Event()
+                ev0.record(cs)
+                sl["desc"][f0:f].copy_(pin["desc"][f0:f], non_blocking=True)
+                sl["kp"][f0:f].copy_(pin["kp"][f0:f], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+            uploaded[0] = ev
+            return ev0
+
+        ev_first = upload_first() if first_cut is not None else upload(0)
         for k in range(steps):
             if k + 1 < steps:
                 upload(k + 1)
-            main.wait_event(uploaded[k & 1])
-            self.run_device(b, slot=k & 1,
-                            after_match=(lambda kk=k: after_match(kk)) if after_match is not None else None)
+            am = (lambda kk=k: after_match(kk)) if after_match is not None else None
+            if k == 0 and first_cut is not None:
+                main.wait_event(ev_first)
+                self.run_device(first_cut[1], slot=0, chain=False)
+                main.wait_event(uploaded[0])
+                self.run_device(b - first_cut[1], p0=first_cut[1], slot=0, chain=False, after_match=am)
+                if self.do_chain:
+                    _lib.check(self.lib.vo_chain_poses(_lib.ptr(self.R), _lib.ptr(self.t), b, None,
+                                                       _lib.ptr(self.poses), _lib.cur_stream()))
+            else:
+                main.wait_event(uploaded[k & 1])
+                self.run_device(b, slot=k & 1, after_match=am)
             ev = torch.cuda.Event()
             ev.record(main)
             computed[k & 1] = ev
