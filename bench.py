@@ -157,7 +157,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * wall / max(args.steps, 1), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "fp4 (e2m1) tensor-core Hamming (exact) + f64 geometry",
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8 popcount Hamming + f64 geometry (cv2 on the host cores)",
         "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": workers, "kind": "port",
                          "sample": sample},
