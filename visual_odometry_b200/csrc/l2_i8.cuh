@@ -15,7 +15,8 @@
 //   * the cross-check direction is a second MMA pass with the operands swapped, as in K1t: at
 //     640 tensor cycles per 128 x 256 accumulator the epilogue, not the MMA, is what is scarce.
 // Kernel skeleton = hamming_tc.cuh (persistent, warp-specialised, two 256-column accumulators that
-// double-buffer each other, work item = (pair, direction, 256-row block)).  Measured
+// double-buffer each other, work item = (pair, direction, 256-row block)); the eight epilogue warps
+// work as two independent groups, one per accumulator (as in hamming_f4.cuh).  Measured
 // (profiles/r2_summary.md): with the whole epilogue removed the MMA + bulk-copy side alone needs
 // 1263 clocks per accumulator (640 of MMA): at 41 KB per 1280 tensor clocks the four smem stages
 // do not cover the L2 latency (see profiles/r2_summary.md for the latency model and the variants).
@@ -145,17 +146,6 @@ __device__ __forceinline__ void fold_tile(Top& s, int h, int l, int t) {
     s.t1 = a ? t : s.t1;
   }
 }
-__device__ __forceinline__ bool before(int ka, int ta, int kb, int tb) {   // better = larger (acc, parity), then lower column
-  const int sa = ka >> 8, sb = kb >> 8;
-  if (sa != sb) return sa > sb;
-  return ta * 256 + 255 - (ka & 255) < tb * 256 + 255 - (kb & 255);
-}
-__device__ __forceinline__ void insert(Top& s, int k, int t) {
-  if (t < 0) return;
-  if (s.t1 < 0 || before(k, t, s.k1, s.t1)) { s.k2 = s.k1; s.t2 = s.t1; s.k1 = k; s.t1 = t; }
-  else if (s.t2 < 0 || before(k, t, s.k2, s.t2)) { s.k2 = k; s.t2 = t; }
-}
-
 // 16-byte shared-memory load with an explicit state space; volatile without a memory clobber:
 // ordered against the barrier / TMEM asm statements around it, free against the arithmetic
 __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
