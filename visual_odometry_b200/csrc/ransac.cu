@@ -12,7 +12,6 @@
 // Iterations at or beyond the current bound are skipped, exactly as OpenCV never runs them.
 #include <float.h>
 
-#include <stdlib.h>
 #include "fivept.cuh"
 
 namespace vo {
@@ -520,12 +519,7 @@ using namespace vo;
 // exported so that the host side (launch counts, bench accounting) cannot drift from it.
 static int round_schedule(int max_iters, int C, int adaptive, int* chunks, int max_rounds) {
   int it0 = 0, n = 0;
-  static int chunk0 = 0;
-  if (!chunk0) {      // (experiment hook: VO_B200_RANSAC_CHUNK0 = size of the first round)
-    const char* e = getenv("VO_B200_RANSAC_CHUNK0");
-    chunk0 = e && atoi(e) > 0 ? atoi(e) : RANSAC_CHUNK0;
-  }
-  int chunk = chunk0 < C ? chunk0 : C;
+  int chunk = RANSAC_CHUNK0 < C ? RANSAC_CHUNK0 : C;
   if (!adaptive) chunk = C;
   while (it0 < max_iters && n < max_rounds) {
     if (it0 + chunk > max_iters) chunk = max_iters - it0;
