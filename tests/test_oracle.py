@@ -102,3 +102,31 @@ def test_fivept_restatement_same_solution_count_as_cv2(seed):
         mine = CG.fivept_solve(CG.normalize_points(p1[idx], seq.K),
                                CG.normalize_points(p2[idx], seq.K))
         assert (0 if Ecv is None else Ecv.shape[0] // 3) == len(mine)
+
+
+def test_fp4_key_arithmetic_of_the_tensor_core_hamming_kernel():
+    """The arithmetic csrc/hamming_f4.cuh relies on, restated in numpy (no GPU): bits as +-6 in
+    e2m1 give 36 * (256 - 2 * Hamming); the index step (ones group 4, 4, 4, 4, 4, 1, 0.5 against
+    the base-4 digits of x = 207 - column, d0 stored as d0 / 2) adds exactly x / 4; every key is
+    a multiple of 1/4 below 2^24 (exact in fp32), one Hamming step (72) outweighs the index part
+    (<= 51.75), and 4 * key + 36864 = 288 * (256 - H) + x decodes both."""
+    e2m1 = {0: 0.0, 1: 0.5, 2: 1.0, 3: 1.5, 4: 2.0, 5: 3.0, 6: 4.0, 7: 6.0}
+    val = lambda c: -e2m1[c & 7] if c & 8 else e2m1[c & 7]
+    ones = [6, 6, 6, 6, 6, 2, 1]                       # nibble codes of 0x01266666
+    code = lambda d: 2 * d - (d == 3)                  # values 0, 1, 2, 3 -> codes 0, 2, 4, 5
+    for x in range(208):
+        d3, d2, d1, d0 = x >> 6, (x >> 4) & 3, (x >> 2) & 3, x & 3
+        idx = [code(d3)] * 4 + [code(d2), code(d1), d0]
+        assert sum(val(a) * val(b) for a, b in zip(ones, idx)) == x / 4
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 2, (64, 256)); b = rng.integers(0, 2, (208, 256))
+    a[0] = b[5]; a[1] = 1 - b[7]                        # Hamming 0 and 256
+    enc = lambda bits: np.where(bits == 1, val(0x7), val(0xF))
+    H = (a[:, None, :] != b[None, :, :]).sum(-1)
+    key = (enc(a) @ enc(b).T + 0.25 * (207 - np.arange(208))[None, :]).astype(np.float32)
+    assert np.array_equal(key.astype(np.float64), 36.0 * (256 - 2 * H) + 0.25 * (207 - np.arange(208))[None, :])
+    y = (key * 4).astype(np.int64) + 36864
+    assert np.array_equal(256 - y // 288, H) and np.array_equal(207 - y % 288, np.broadcast_to(np.arange(208), H.shape))
+    # the largest key of a row = its nearest column, lowest column on ties
+    want = np.array([np.flatnonzero(H[i] == H[i].min())[0] for i in range(64)])
+    assert np.array_equal(key.argmax(1), want)
